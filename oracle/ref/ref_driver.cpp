@@ -1,0 +1,578 @@
+// TEST INFRASTRUCTURE — NOT PRODUCT CODE.
+//
+// Headless driver around the UNMODIFIED reference sources (compiled in place from
+// /root/reference/src by oracle/Makefile into oracle/_ref/).  It replaces only what the
+// reference keeps in src/main.cpp and src/window/window.cpp (CLI + SDL/ImGui window, not
+// buildable here: no SDL2, no graphics stack) and exposes the reference's own hot path
+//   setupRay -> findIntersection -> {findBVHIntesection | intersectGrid | intersectSubBeamGrid}
+//   -> triangleIntersection -> shade -> accumulate            (src/tracer.cpp:113-160)
+// for parity vectors and for the CPU baseline timing.
+//
+// Triangle ids, ray counts and the `max_depth` cap are obtained WITHOUT editing the
+// reference, with the linker's --wrap on three symbols:
+//   _Z20triangleIntersectionR3RayR8Triangle   (src/primitives/triangle.cpp:7)
+//   _Z16findIntersectionR3Ray                 (src/scene/scene.cpp:64)
+//   _Z5shadeR3Ray                             (src/shader/shader.cpp:239)
+#include <atomic>
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <unistd.h>
+#include <vector>
+
+#include "accelerationStructures/bvh.h"
+#include "accelerationStructures/lightFieldGrid.h"
+#include "accelerationStructures/lightFieldGridSubBeams.h"
+#include "common.h"
+#include "primitives/object.h"
+#include "primitives/triangle.h"
+#include "scene/SceneFile.h"
+#include "scene/scene.h"
+#include "shader/shader.h"
+#include "tracer.h"
+#include "types/camera.h"
+#include "window/window.h"
+
+#include "ptbs_format.h"
+
+// ---- the three window symbols the rest of the reference links against -------------------
+// (src/window/window.h:11-15; callReset is used by src/types/camera.cpp:101,134)
+static bool g_tone = true;
+bool &getToneMapping() { return g_tone; }
+void callReset() { reset(); }
+void createWindow(bool) {}
+
+void setupRay(Ray &ray, int x, int y); // external linkage in src/tracer.cpp:72
+
+// ---- --wrap instrumentation --------------------------------------------------------------
+struct ThreadStats {
+    uint64_t calls = 0;     // findIntersection calls with a live ray
+    uint64_t traversed = 0; // ... that actually ran a structure traversal
+    uint64_t unique = 0;    // ... whose (origin,direction) differ from this thread's previous one
+    float last[6] = {0, 0, 0, 0, 0, 0};
+};
+static std::mutex g_statsMtx;
+static std::vector<ThreadStats *> g_allStats;
+static thread_local ThreadStats *tl_stats = nullptr;
+static thread_local int tl_lastTri = -1;
+static int g_maxDepth = 0;        // 0 = unbounded (reference behaviour)
+static bool g_countRays = true;
+
+static ThreadStats *stats() {
+    if (!tl_stats) {
+        tl_stats = new ThreadStats();
+        std::lock_guard<std::mutex> l(g_statsMtx);
+        g_allStats.push_back(tl_stats);
+    }
+    return tl_stats;
+}
+
+extern "C" {
+bool __real__Z20triangleIntersectionR3RayR8Triangle(Ray &, Triangle &);
+bool __wrap__Z20triangleIntersectionR3RayR8Triangle(Ray &r, Triangle &t) {
+    bool hit = __real__Z20triangleIntersectionR3RayR8Triangle(r, t);
+    if (hit) tl_lastTri = (int)(&t - getTris().data());
+    return hit;
+}
+
+void __real__Z16findIntersectionR3Ray(Ray &);
+void __wrap__Z16findIntersectionR3Ray(Ray &r) {
+    if (!g_countRays) {
+        __real__Z16findIntersectionR3Ray(r);
+        return;
+    }
+    bool live = !r.terminated;
+    float cur[6] = {r.origin[0], r.origin[1], r.origin[2], r.direction[0], r.direction[1], r.direction[2]};
+    __real__Z16findIntersectionR3Ray(r);
+    if (!live) return;
+    ThreadStats *s = stats();
+    s->calls++;
+    // BVH / ALL / SUB_BEAMS return before traversing when roulette killed the ray
+    // (bvh.cpp:51, scene.cpp:80, lightFieldGridSubBeams.cpp:131); TWO_PLANE traverses anyway.
+    bool traversed = !r.terminated || getIntersectMode() == TWO_PLANE;
+    if (!traversed) return;
+    s->traversed++;
+    if (memcmp(cur, s->last, sizeof cur) != 0) {
+        s->unique++;
+        memcpy(s->last, cur, sizeof cur);
+    }
+}
+
+Vector3 __real__Z5shadeR3Ray(Ray &);
+Vector3 __wrap__Z5shadeR3Ray(Ray &r) {
+    Vector3 v = __real__Z5shadeR3Ray(r);
+    // max_depth (absent in the reference): "after depth++, if depth >= max_depth
+    // terminate".  traceWF increments depth right after shade (src/tracer.cpp:133-134).
+    if (g_maxDepth > 0 && r.depth + 1 >= g_maxDepth) r.terminated = true;
+    return v;
+}
+}
+
+// ---- options -----------------------------------------------------------------------------
+struct Opts {
+    std::string sceneFile, base, ptbs;
+    int mode = 1;
+    unsigned gs = 10, os = 5, m = 40;
+    bool grid = false, beams = false;
+    int W = 512, H = 512, spp = 1, maxDepth = 0, nee = 0, threads = 0;
+    unsigned bgs = 10, bm = 40;
+};
+
+static void die(const char *msg) {
+    fprintf(stderr, "ptref: %s\n", msg);
+    exit(2);
+}
+
+static double nowMs() {
+    return std::chrono::duration<double, std::milli>(std::chrono::high_resolution_clock::now().time_since_epoch()).count();
+}
+
+// ---- scene set-up: the steps of initScene (src/scene/scene.cpp:97-133) ---------------------
+static void loadFromFiles(const Opts &o) {
+    if (!o.base.empty() && chdir(o.base.c_str()) != 0) die("chdir(base) failed");
+    loadScene(o.sceneFile);
+    Material none{.pbr = {}, .weights = {}, .name = std::string("None")};
+    for (auto m : getSceneFile().models) loadObject(m.file.c_str(), m.pos, m.scale, addMaterial(none));
+    for (auto m : getSceneFile().materials)
+        for (auto &mat : *getMaterials()) {
+            if (mat.name != m.name) continue;
+            mat.weights = m.mat.weights;
+            mat.pbr = m.mat.pbr;
+        }
+}
+
+static void loadFromPtbs(const Opts &o, ptbs_header &hdr) {
+    FILE *f = fopen(o.ptbs.c_str(), "rb");
+    if (!f) die("cannot open ptbs");
+    if (fread(&hdr, sizeof hdr, 1, f) != 1 || hdr.magic != PTBS_MAGIC) die("bad ptbs");
+    size_t n = hdr.n_tris;
+    std::vector<float> pos(n * 9), nrm(n * 9), uv(n * 6);
+    std::vector<int32_t> mat(n);
+    std::vector<ptbs_object> objs(hdr.n_objects);
+    std::vector<ptbs_material> mats(hdr.n_materials);
+    bool ok = fread(pos.data(), 4, n * 9, f) == n * 9 && fread(nrm.data(), 4, n * 9, f) == n * 9 &&
+              fread(uv.data(), 4, n * 6, f) == n * 6 && fread(mat.data(), 4, n, f) == n &&
+              fread(objs.data(), sizeof(ptbs_object), objs.size(), f) == objs.size() &&
+              fread(mats.data(), sizeof(ptbs_material), mats.size(), f) == mats.size();
+    fclose(f);
+    if (!ok) die("short ptbs");
+    for (auto &m : mats) {
+        Material mm{.pbr = {.albedo = {m.albedo[0], m.albedo[1], m.albedo[2]},
+                            .refractiveIdx1 = m.ior1,
+                            .refractiveIdx2 = m.ior2,
+                            .emmision = m.emission,
+                            .roughness = m.roughness},
+                    .weights = {.lambert = m.w_lambert, .reflection = m.w_reflection, .refraction = m.w_refraction},
+                    .name = std::string(m.name)};
+        addMaterial(mm);
+    }
+    auto &tris = getTris();
+    tris.reserve(n);
+    for (size_t i = 0; i < n; ++i) {
+        const float *p = &pos[i * 9], *q = &nrm[i * 9], *t = &uv[i * 6];
+        tris.push_back(createTriangle({p[0], p[1], p[2]}, {p[3], p[4], p[5]}, {p[6], p[7], p[8]}, {q[0], q[1], q[2]},
+                                      {q[3], q[4], q[5]}, {q[6], q[7], q[8]}, {t[0], t[1]}, {t[2], t[3]}, {t[4], t[5]},
+                                      mat[i]));
+    }
+    for (auto &po : objs) {
+        Vector3 mn{INFINITY, INFINITY, INFINITY}, mx{-INFINITY, -INFINITY, -INFINITY};
+        for (int i = po.start_idx; i < po.end_idx; ++i) {
+            Vector3 a = minBounds(tris[i]), b = maxBounds(tris[i]);
+            for (int k = 0; k < 3; ++k) {
+                if (a[k] < mn[k]) mn[k] = a[k];
+                if (b[k] > mx[k]) mx[k] = b[k];
+            }
+        }
+        Object ob{.type = OBJECT,
+                  .startIdx = po.start_idx,
+                  .endIdx = po.end_idx,
+                  .boundingBox = {.min = mn, .max = mx},
+                  .active = true,
+                  .surfaceArea = po.surface_area,
+                  .name = std::string(po.name),
+                  .materials = std::vector<u32>(po.materials, po.materials + po.n_materials)};
+        getObjects().push_back(ob);
+    }
+}
+
+static double g_bvhMs = 0, g_gridMs = 0, g_beamMs = 0;
+
+static void buildStructures(const Opts &o, const float camPos[3], const float camFwd[3], float focus, float dof) {
+    auto &objects = getObjects();
+    double t0 = nowMs();
+    constructBVH(0, objects.size()); // node 0 == scene root (scene.cpp:113; `root` there is 0)
+    for (size_t i = 0; i < objects.size(); i++) objects[i].root = constructBVH(objects[i].startIdx, objects[i].endIdx, -1, true);
+    g_bvhMs = nowMs() - t0;
+    if (o.grid) {
+        t0 = nowMs();
+        constructGrid();
+        g_gridMs = nowMs() - t0;
+    }
+    if (o.beams) {
+        t0 = nowMs();
+        buildGridsWithSubBeams(); // commented out at scene.cpp:125; called here for mode 3
+        g_beamMs = nowMs() - t0;
+    }
+    Vector3 fwd{camFwd[0], camFwd[1], camFwd[2]};
+    cameraSetForward(fwd);
+    getCamera()->origin = {camPos[0], camPos[1], camPos[2]};
+    getCamera()->dof = dof;
+    getCamera()->focus = focus;
+    resetScene();
+}
+
+static void dumpScene(const char *path) {
+    auto &tris = getTris();
+    auto &objs = getObjects();
+    auto &mats = *getMaterials();
+    ptbs_header h{};
+    h.magic = PTBS_MAGIC;
+    h.version = PTBS_VERSION;
+    h.n_tris = tris.size();
+    h.n_objects = objs.size();
+    h.n_materials = mats.size();
+    auto &cam = getSceneFile().cam;
+    for (int k = 0; k < 3; ++k) {
+        h.cam_pos[k] = cam.pos[k];
+        h.cam_forward[k] = cam.forward[k];
+    }
+    h.cam_focus = cam.focus;
+    h.cam_dof = cam.dof;
+    FILE *f = fopen(path, "wb");
+    if (!f) die("cannot write scene dump");
+    fwrite(&h, sizeof h, 1, f);
+    for (auto &t : tris)
+        for (int v = 0; v < 3; ++v) {
+            float p[3] = {t.vertices[v][0], t.vertices[v][1], t.vertices[v][2]};
+            fwrite(p, 4, 3, f);
+        }
+    for (auto &t : tris)
+        for (int v = 0; v < 3; ++v) {
+            float p[3] = {t.normal[v][0], t.normal[v][1], t.normal[v][2]};
+            fwrite(p, 4, 3, f);
+        }
+    for (auto &t : tris)
+        for (int v = 0; v < 3; ++v) {
+            float p[2] = {t.uv[v].x, t.uv[v].y};
+            fwrite(p, 4, 2, f);
+        }
+    for (auto &t : tris) {
+        int32_t m = t.materialIdx;
+        fwrite(&m, 4, 1, f);
+    }
+    for (auto &ob : objs) {
+        ptbs_object po{};
+        po.start_idx = ob.startIdx;
+        po.end_idx = ob.endIdx;
+        po.surface_area = ob.surfaceArea;
+        po.n_materials = std::min<size_t>(ob.materials.size(), PTBS_MAX_OBJECT_MATERIALS);
+        for (uint32_t i = 0; i < po.n_materials; ++i) po.materials[i] = ob.materials[i];
+        strncpy(po.name, ob.name.c_str(), sizeof po.name - 1);
+        fwrite(&po, sizeof po, 1, f);
+    }
+    for (auto &m : mats) {
+        ptbs_material pm{};
+        for (int k = 0; k < 3; ++k) pm.albedo[k] = m.pbr.albedo[k];
+        pm.ior1 = m.pbr.refractiveIdx1;
+        pm.ior2 = m.pbr.refractiveIdx2;
+        pm.emission = m.pbr.emmision;
+        pm.roughness = m.pbr.roughness;
+        pm.w_lambert = m.weights.lambert;
+        pm.w_reflection = m.weights.reflection;
+        pm.w_refraction = m.weights.refraction;
+        strncpy(pm.name, m.name.c_str(), sizeof pm.name - 1);
+        fwrite(&pm, sizeof pm, 1, f);
+    }
+    fclose(f);
+}
+
+// ---- commands ----------------------------------------------------------------------------
+static void sumStats(uint64_t &calls, uint64_t &trav, uint64_t &uniq) {
+    calls = trav = uniq = 0;
+    std::lock_guard<std::mutex> l(g_statsMtx);
+    for (auto *s : g_allStats) {
+        calls += s->calls;
+        trav += s->traversed;
+        uniq += s->unique;
+    }
+}
+
+// Primary-ray hit records with the exact rays traceWF would generate for the first sample
+// (setupRay, src/tracer.cpp:72-88, seeded by initTracer :236-242).  Pixel index = y*W + x.
+static void cmdPrimaryHits(const Opts &o, const char *out) {
+    setWindowSize(o.W, o.H);
+    initTracer();
+    size_t n = (size_t)o.W * o.H;
+    std::vector<float> t(n), rayOD(n * 6);
+    std::vector<int32_t> tri(n), mat(n);
+    int T = o.threads > 0 ? o.threads : (int)std::thread::hardware_concurrency();
+    double t0 = nowMs();
+    std::vector<std::thread> th;
+    for (int k = 0; k < T; ++k)
+        th.emplace_back([&, k]() {
+            Ray ray{};
+            for (int y = k; y < o.H; y += T)
+                for (int x = 0; x < o.W; ++x) {
+                    ray.terminated = true;
+                    setupRay(ray, x, y);
+                    ray.light = {0, 0, 0};
+                    ray.interSectionAS = ray.interSectionTests = 0;
+                    size_t p = (size_t)y * o.W + x;
+                    for (int c = 0; c < 3; ++c) {
+                        rayOD[p * 6 + c] = ray.origin[c];
+                        rayOD[p * 6 + 3 + c] = ray.direction[c];
+                    }
+                    tl_lastTri = -1;
+                    findIntersection(ray);
+                    bool hit = ray.tmax != INFINITY;
+                    t[p] = ray.tmax;
+                    tri[p] = hit ? tl_lastTri : -1;
+                    mat[p] = hit ? ray.materialIdx : -1;
+                }
+        });
+    for (auto &x : th) x.join();
+    double ms = nowMs() - t0;
+    FILE *f = fopen(out, "wb");
+    if (!f) die("cannot write output");
+    fwrite(t.data(), 4, n, f);
+    fwrite(tri.data(), 4, n, f);
+    fwrite(mat.data(), 4, n, f);
+    fwrite(rayOD.data(), 4, n * 6, f);
+    fclose(f);
+    printf("PTREF_JSON {\"cmd\":\"primary-hits\",\"rays\":%zu,\"ms\":%.3f,\"threads\":%d,\"mode\":%d}\n", n, ms, T, o.mode);
+}
+
+// Closest hit for externally supplied rays (config 5 / traversal-only CPU baseline).
+// Input file: n x 6 floats (origin, direction); direction is used as given.
+static void cmdTraceRays(const Opts &o, const char *in, const char *out) {
+    FILE *f = fopen(in, "rb");
+    if (!f) die("cannot open rays");
+    fseek(f, 0, SEEK_END);
+    size_t n = ftell(f) / 24;
+    fseek(f, 0, SEEK_SET);
+    std::vector<float> od(n * 6);
+    if (fread(od.data(), 4, n * 6, f) != n * 6) die("short rays file");
+    fclose(f);
+    std::vector<float> t(n);
+    std::vector<int32_t> tri(n);
+    int T = o.threads > 0 ? o.threads : (int)std::thread::hardware_concurrency();
+    g_countRays = false;
+    double t0 = nowMs();
+    std::vector<std::thread> th;
+    for (int k = 0; k < T; ++k)
+        th.emplace_back([&, k]() {
+            Ray ray{};
+            size_t lo = n * k / T, hi = n * (k + 1) / T;
+            for (size_t i = lo; i < hi; ++i) {
+                for (int c = 0; c < 3; ++c) {
+                    ray.origin[c] = od[i * 6 + c];
+                    ray.direction[c] = od[i * 6 + 3 + c];
+                    ray.inv_dir[c] = 1.0f / ray.direction[c];
+                }
+                ray.tmin = 0.0f;
+                ray.tmax = INFINITY;
+                ray.depth = 0;
+                ray.randomState = 0;
+                ray.terminated = false;
+                ray.throughPut = {1, 1, 1};
+                tl_lastTri = -1;
+                findIntersection(ray);
+                t[i] = ray.tmax;
+                tri[i] = ray.tmax != INFINITY ? tl_lastTri : -1;
+            }
+        });
+    for (auto &x : th) x.join();
+    double ms = nowMs() - t0;
+    f = fopen(out, "wb");
+    if (!f) die("cannot write output");
+    fwrite(t.data(), 4, n, f);
+    fwrite(tri.data(), 4, n, f);
+    fclose(f);
+    printf("PTREF_JSON {\"cmd\":\"trace-rays\",\"rays\":%zu,\"ms\":%.3f,\"threads\":%d,\"mode\":%d,\"mrays_s\":%.4f}\n", n, ms, T,
+           o.mode, n / ms / 1000.0);
+}
+
+// Full render through the reference's unmodified trace(true): 16 std::threads, 4x4 pixel
+// interleave (src/tracer.cpp:164-185), timed like src/main.cpp:116-125.
+static void cmdRender(const Opts &o, const char *out) {
+    getNEE() = o.nee != 0;
+    g_maxDepth = o.maxDepth;
+    setWindowSize(o.W, o.H);
+    getMaxSampleCount() = o.spp;
+    getDebugView() = false;
+    double t0 = nowMs();
+    initTracer();
+    double t1 = nowMs();
+    trace(true);
+    double t2 = nowMs();
+    uint64_t calls, trav, uniq;
+    sumStats(calls, trav, uniq);
+    size_t n = (size_t)o.W * o.H;
+    if (out && strcmp(out, "-") != 0) {
+        std::vector<float> img(n * 4);
+        for (int y = 0; y < o.H; ++y)
+            for (int x = 0; x < o.W; ++x) {
+                Vector3 c = tracerGetPixel(x, y);
+                size_t p = ((size_t)y * o.W + x) * 4;
+                img[p] = c[0];
+                img[p + 1] = c[1];
+                img[p + 2] = c[2];
+                img[p + 3] = 1.0f;
+            }
+        FILE *f = fopen(out, "wb");
+        if (!f) die("cannot write output");
+        fwrite(img.data(), 4, n * 4, f);
+        fclose(f);
+    }
+    double traceMs = t2 - t1;
+    printf("PTREF_JSON {\"cmd\":\"render\",\"mode\":%d,\"width\":%d,\"height\":%d,\"spp\":%d,\"max_depth\":%d,\"nee\":%d,"
+           "\"init_ms\":%.3f,\"trace_ms\":%.3f,\"paths\":%zu,\"find_calls\":%llu,\"rays_traversed\":%llu,\"rays_unique\":%llu,"
+           "\"tri_tests\":%lu,\"as_tests\":%lu,\"threads\":16,\"hw_threads\":%u,\"mrays_unique_s\":%.4f,\"mrays_traversed_s\":%.4f,"
+           "\"spp_s\":%.5f,\"counted\":%d}\n",
+           o.mode, o.W, o.H, o.spp, o.maxDepth, o.nee, t1 - t0, traceMs, n * (size_t)o.spp, (unsigned long long)calls,
+           (unsigned long long)trav, (unsigned long long)uniq, getIntersectionCount(), getStructureIntersectionCount(),
+           std::thread::hardware_concurrency(), uniq / traceMs / 1000.0, trav / traceMs / 1000.0, o.spp / (traceMs / 1000.0),
+           g_countRays ? 1 : 0);
+}
+
+// Flattened copy of the reference's BVH arrays (bvh.cpp:18-20) for structure-level checks.
+static void cmdDumpBvh(const char *out) {
+    FILE *f = fopen(out, "wb");
+    if (!f) die("cannot write output");
+    std::vector<int32_t> rec;
+    std::vector<float> box;
+    uint32_t nNodes = 0;
+    // nodes are contiguous from 0; probe until getNode would run past the end: count via memory size
+    unsigned long bytes = getMemoryBVH();
+    (void)bytes;
+    // getNode has no size accessor: the node count equals the box count; walk from every root.
+    std::vector<int> stack;
+    std::vector<char> seen;
+    auto visit = [&](int root) {
+        stack.push_back(root);
+        while (!stack.empty()) {
+            int i = stack.back();
+            stack.pop_back();
+            if ((size_t)i >= seen.size()) seen.resize(i + 1, 0);
+            seen[i] = 1;
+            BvhNode &n = getNode(i);
+            if (!isLeaf(n)) {
+                stack.push_back(n.childLeft);
+                stack.push_back(n.childRight);
+            }
+        }
+    };
+    visit(0);
+    for (auto &ob : getObjects()) visit(ob.root);
+    nNodes = seen.size();
+    fwrite(&nNodes, 4, 1, f);
+    for (uint32_t i = 0; i < nNodes; ++i) {
+        BvhNode &n = getNode(i);
+        AABB &b = getNodeAABB(n.AABBIdx);
+        int32_t r[6] = {n.startIdx, n.endIdx, n.childLeft, n.childRight, n.hasTris ? 1 : 0, n.depth};
+        float bb[6] = {b.min[0], b.min[1], b.min[2], b.max[0], b.max[1], b.max[2]};
+        fwrite(r, 4, 6, f);
+        fwrite(bb, 4, 6, f);
+    }
+    fclose(f);
+    printf("PTREF_JSON {\"cmd\":\"dump-bvh\",\"nodes\":%u,\"bytes\":%lu}\n", nNodes, getMemoryBVH());
+}
+
+int main(int argc, char **argv) {
+    Opts o;
+    std::vector<std::string> pos;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto next = [&]() -> const char * {
+            if (i + 1 >= argc) die("missing value");
+            return argv[++i];
+        };
+        if (a == "--scene-file") o.sceneFile = next();
+        else if (a == "--base") o.base = next();
+        else if (a == "--ptbs") o.ptbs = next();
+        else if (a == "--mode") o.mode = atoi(next());
+        else if (a == "--gs") o.gs = atoi(next());
+        else if (a == "--os") o.os = atoi(next());
+        else if (a == "--m") o.m = atoi(next());
+        else if (a == "--bgs") o.bgs = atoi(next());
+        else if (a == "--bm") o.bm = atoi(next());
+        else if (a == "--grid") o.grid = true;
+        else if (a == "--beams") o.beams = true;
+        else if (a == "--width") o.W = atoi(next());
+        else if (a == "--height") o.H = atoi(next());
+        else if (a == "--spp") o.spp = atoi(next());
+        else if (a == "--max-depth") o.maxDepth = atoi(next());
+        else if (a == "--nee") o.nee = atoi(next());
+        else if (a == "--threads") o.threads = atoi(next());
+        else if (a == "--no-count") g_countRays = false;
+        else pos.push_back(a);
+    }
+    if (pos.empty()) die("usage: ptref [options] <dump-scene|primary-hits|trace-rays|render|dump-bvh|info> [files]");
+    if (o.mode == 2) o.grid = true;
+    if (o.mode == 3) o.beams = true;
+    // absolute output paths before any chdir
+    char cwd[4096];
+    if (!getcwd(cwd, sizeof cwd)) die("getcwd");
+    for (size_t i = 1; i < pos.size(); ++i)
+        if (pos[i][0] != '/' && pos[i] != "-") pos[i] = std::string(cwd) + "/" + pos[i];
+    if (!o.ptbs.empty() && o.ptbs[0] != '/') o.ptbs = std::string(cwd) + "/" + o.ptbs;
+
+    setGridSettings(o.gs, o.os, o.m);
+    setGridBeamsSettings(o.bgs, o.bm);
+    setIntersectMode(o.mode);
+    double t0 = nowMs();
+    if (!o.ptbs.empty()) {
+        ptbs_header h;
+        loadFromPtbs(o, h);
+        // keep the scene-file camera around for dump-scene round trips
+        auto &cam = getSceneFile().cam;
+        cam.pos = {h.cam_pos[0], h.cam_pos[1], h.cam_pos[2]};
+        cam.forward = {h.cam_forward[0], h.cam_forward[1], h.cam_forward[2]};
+        cam.focus = h.cam_focus;
+        cam.dof = h.cam_dof;
+    } else if (!o.sceneFile.empty()) {
+        loadFromFiles(o);
+    } else
+        die("need --scene-file or --ptbs");
+    double loadMs = nowMs() - t0;
+    auto &cam = getSceneFile().cam;
+    float cp[3] = {cam.pos[0], cam.pos[1], cam.pos[2]}, cf[3] = {cam.forward[0], cam.forward[1], cam.forward[2]};
+
+    const std::string &cmd = pos[0];
+    if (cmd == "dump-scene") {
+        if (pos.size() < 2) die("dump-scene <out.ptbs>");
+        dumpScene(pos[1].c_str());
+        printf("PTREF_JSON {\"cmd\":\"dump-scene\",\"tris\":%zu,\"objects\":%zu,\"materials\":%zu}\n", getTris().size(),
+               getObjects().size(), getMaterials()->size());
+        return 0;
+    }
+    buildStructures(o, cp, cf, cam.focus, cam.dof);
+    fprintf(stderr, "ptref: load %.1f ms, bvh %.1f ms, grid %.1f ms, beams %.1f ms, tris %zu, lights %zu\n", loadMs, g_bvhMs,
+            g_gridMs, g_beamMs, getTris().size(), getLights().size());
+    printf("PTREF_JSON {\"cmd\":\"build\",\"tris\":%zu,\"objects\":%zu,\"lights\":%zu,\"bvh_ms\":%.1f,\"grid_ms\":%.1f,\"beam_ms\":%.1f,"
+           "\"bvh_bytes\":%lu,\"grid_bytes\":%lu}\n",
+           getTris().size(), getObjects().size(), getLights().size(), g_bvhMs, g_gridMs, g_beamMs, getMemoryBVH(),
+           o.grid ? getMemory2Plane() : 0ul);
+    if (cmd == "primary-hits") {
+        if (pos.size() < 2) die("primary-hits <out.bin>");
+        cmdPrimaryHits(o, pos[1].c_str());
+    } else if (cmd == "trace-rays") {
+        if (pos.size() < 3) die("trace-rays <rays.bin> <out.bin>");
+        cmdTraceRays(o, pos[1].c_str(), pos[2].c_str());
+    } else if (cmd == "render") {
+        cmdRender(o, pos.size() > 1 ? pos[1].c_str() : "-");
+    } else if (cmd == "dump-bvh") {
+        if (pos.size() < 2) die("dump-bvh <out.bin>");
+        cmdDumpBvh(pos[1].c_str());
+    } else if (cmd == "info") {
+    } else
+        die("unknown command");
+    fflush(stdout);
+    // the reference's globals (threads array, big static image) have no orderly teardown
+    _exit(0);
+}
