@@ -1,0 +1,229 @@
+"""ctypes binding of libptb.so (include/ptb.h).  Thin by design: every call forwards to the C ABI;
+there is no Python or CPU rendering path here.  If the shared library is missing this module
+raises at import of `PathTracer` use — nothing falls back."""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libptb.so")
+
+MODE_ALL, MODE_BVH, MODE_TWO_PLANE, MODE_SUB_BEAMS = 0, 1, 2, 3
+MODE_NAMES = {0: "ALL", 1: "BVH", 2: "TWO_PLANE", 3: "SUB_BEAMS"}
+
+CNT_RAYS, CNT_PATHS, CNT_TRI_TESTS, CNT_AS_TESTS, CNT_SHADOW_RAYS, CNT_ITERATIONS, CNT_KERNELS, CNT_REF_RAYS = range(8)
+COUNTER_NAMES = ("rays", "paths", "tri_tests", "as_tests", "shadow_rays", "iterations", "kernels", "ref_rays")
+
+# every symbol include/ptb.h declares
+SYMBOLS = (
+    "ptb_create", "ptb_destroy", "ptb_last_error", "ptb_upload_triangles", "ptb_upload_objects", "ptb_upload_materials",
+    "ptb_load_ptbs", "ptb_set_camera", "ptb_build_bvh", "ptb_build_subgrid", "ptb_build_subbeams", "ptb_structure_bytes",
+    "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
+    "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
+    "ptb_image_device_ptr", "ptb_last_render_ms",
+)
+
+
+class Camera(ctypes.Structure):
+    _fields_ = [("origin", ctypes.c_float * 3), ("forward", ctypes.c_float * 3), ("focus", ctypes.c_float),
+                ("dof", ctypes.c_float), ("fov_degrees", ctypes.c_float)]
+
+
+class Params(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "width", "height", "mode", "nee", "primary_only", "max_depth", "reference_quirks", "debug_view", "debug_scale",
+        "rank", "world", "tile_w", "tile_h", "count_tests")]
+
+
+class PtbError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libptb.so (built by __graft_entry__.build()); loud failure if it is not there."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise PtbError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(libptb has no Python/CPU fallback)")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, ci, cu64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint64
+    L.ptb_create.argtypes = [ci, ctypes.POINTER(vp)]
+    L.ptb_destroy.argtypes = [vp]
+    L.ptb_destroy.restype = None
+    L.ptb_last_error.argtypes = [vp]
+    L.ptb_last_error.restype = ctypes.c_char_p
+    L.ptb_upload_triangles.argtypes = [vp, vp, vp, vp, vp, cu64]
+    L.ptb_upload_objects.argtypes = [vp, vp, ctypes.c_uint32]
+    L.ptb_upload_materials.argtypes = [vp, vp, ctypes.c_uint32]
+    L.ptb_load_ptbs.argtypes = [vp, ctypes.c_char_p]
+    L.ptb_set_camera.argtypes = [vp, ctypes.POINTER(Camera)]
+    L.ptb_build_bvh.argtypes = [vp]
+    L.ptb_build_subgrid.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
+    L.ptb_build_subbeams.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32]
+    L.ptb_structure_bytes.argtypes = [vp, ci]
+    L.ptb_structure_bytes.restype = cu64
+    L.ptb_set_params.argtypes = [vp, ctypes.POINTER(Params)]
+    L.ptb_reset.argtypes = [vp]
+    L.ptb_render.argtypes = [vp, ci]
+    L.ptb_render_async.argtypes = [vp, ci]
+    L.ptb_sync.argtypes = [vp]
+    L.ptb_primary_hits.argtypes = [vp, vp, vp, vp]
+    L.ptb_trace_rays.argtypes = [vp, vp, cu64, ci, vp, vp]
+    L.ptb_trace_rays_device.argtypes = [vp, vp, cu64, ci, vp, vp]
+    L.ptb_read_image.argtypes = [vp, vp]
+    L.ptb_read_state.argtypes = [vp, vp, vp]
+    L.ptb_write_state.argtypes = [vp, vp, vp, vp]
+    L.ptb_read_rgba8.argtypes = [vp, vp, ci]
+    L.ptb_read_counters.argtypes = [vp, vp]
+    L.ptb_image_device_ptr.argtypes = [vp]
+    L.ptb_image_device_ptr.restype = vp
+    L.ptb_last_render_ms.argtypes = [vp]
+    L.ptb_last_render_ms.restype = ctypes.c_double
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+class PathTracer:
+    """One context on one GPU.  Mirrors the reference's call sequence (src/main.cpp:91-125):
+    settings -> load scene -> build structures -> initTracer -> trace."""
+
+    def __init__(self, device=0):
+        self.L = load_library()
+        h = ctypes.c_void_p()
+        rc = self.L.ptb_create(device, ctypes.byref(h))
+        if rc != 0:
+            raise PtbError(f"ptb_create: {self.L.ptb_last_error(None).decode()} (rc {rc})")
+        self.h = h
+        self.params = Params(reference_quirks=1, world=1, tile_w=32, tile_h=8, mode=MODE_BVH)
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise PtbError(f"{what}: {self.L.ptb_last_error(self.h).decode()} (rc {rc})")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.ptb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- scene -------------------------------------------------------------------------------
+    def load_ptbs(self, path):
+        self._ck(self.L.ptb_load_ptbs(self.h, os.fsencode(path)), "ptb_load_ptbs")
+
+    def upload_triangles(self, pos9, nrm9, uv6, mat):
+        pos9 = np.ascontiguousarray(pos9, np.float32).reshape(-1, 9)
+        n = pos9.shape[0]
+        nrm9 = np.ascontiguousarray(nrm9, np.float32).reshape(n, 9)
+        uv6 = np.ascontiguousarray(uv6, np.float32).reshape(n, 6) if uv6 is not None else None
+        mat = np.ascontiguousarray(mat, np.int32).reshape(n)
+        self._ck(self.L.ptb_upload_triangles(self.h, _ptr(pos9), _ptr(nrm9), _ptr(uv6), _ptr(mat), n), "ptb_upload_triangles")
+
+    def upload_objects(self, objects_bytes, n):
+        buf = (ctypes.c_char * len(objects_bytes)).from_buffer_copy(objects_bytes)
+        self._ck(self.L.ptb_upload_objects(self.h, ctypes.cast(buf, ctypes.c_void_p), n), "ptb_upload_objects")
+
+    def upload_materials(self, materials_bytes, n):
+        buf = (ctypes.c_char * len(materials_bytes)).from_buffer_copy(materials_bytes)
+        self._ck(self.L.ptb_upload_materials(self.h, ctypes.cast(buf, ctypes.c_void_p), n), "ptb_upload_materials")
+
+    def set_camera(self, origin, forward, focus=1.0, dof=0.0, fov_degrees=70.0):
+        cam = Camera((ctypes.c_float * 3)(*origin), (ctypes.c_float * 3)(*forward), focus, dof, fov_degrees)
+        self._ck(self.L.ptb_set_camera(self.h, ctypes.byref(cam)), "ptb_set_camera")
+
+    # ---- structures --------------------------------------------------------------------------
+    def build_bvh(self):
+        self._ck(self.L.ptb_build_bvh(self.h), "ptb_build_bvh")
+
+    def build_subgrid(self, gs=10, os_=5, m=40):
+        self._ck(self.L.ptb_build_subgrid(self.h, gs, os_, m), "ptb_build_subgrid")
+
+    def build_subbeams(self, gs=10, m=40):
+        self._ck(self.L.ptb_build_subbeams(self.h, gs, m), "ptb_build_subbeams")
+
+    def structure_bytes(self, mode):
+        return int(self.L.ptb_structure_bytes(self.h, mode))
+
+    # ---- rendering ---------------------------------------------------------------------------
+    def set_params(self, **kw):
+        for k, v in kw.items():
+            if not hasattr(self.params, k):
+                raise AttributeError(k)
+            setattr(self.params, k, int(v))
+        self._ck(self.L.ptb_set_params(self.h, ctypes.byref(self.params)), "ptb_set_params")
+
+    def reset(self):
+        self._ck(self.L.ptb_reset(self.h), "ptb_reset")
+
+    def render(self, add_samples):
+        self._ck(self.L.ptb_render(self.h, add_samples), "ptb_render")
+        return self.last_ms()
+
+    def last_ms(self):
+        return float(self.L.ptb_last_render_ms(self.h))
+
+    def primary_hits(self):
+        n = self.params.width * self.params.height
+        t = np.empty(n, np.float32)
+        tri = np.empty(n, np.int32)
+        mat = np.empty(n, np.int32)
+        self._ck(self.L.ptb_primary_hits(self.h, _ptr(t), _ptr(tri), _ptr(mat)), "ptb_primary_hits")
+        return t, tri, mat
+
+    def trace_rays(self, od6, mode):
+        od6 = np.ascontiguousarray(od6, np.float32).reshape(-1, 6)
+        n = od6.shape[0]
+        t = np.empty(n, np.float32)
+        tri = np.empty(n, np.int32)
+        self._ck(self.L.ptb_trace_rays(self.h, _ptr(od6), n, mode, _ptr(t), _ptr(tri)), "ptb_trace_rays")
+        return t, tri
+
+    def trace_rays_device(self, od6_ptr, n, mode, t_ptr, tri_ptr):
+        self._ck(self.L.ptb_trace_rays_device(self.h, od6_ptr, n, mode, t_ptr, tri_ptr), "ptb_trace_rays_device")
+        return self.last_ms()
+
+    # ---- read-back ---------------------------------------------------------------------------
+    def read_image(self):
+        img = np.empty((self.params.height, self.params.width, 4), np.float32)
+        self._ck(self.L.ptb_read_image(self.h, _ptr(img)), "ptb_read_image")
+        return img
+
+    def read_state(self):
+        n = self.params.width * self.params.height
+        s = np.empty(n, np.int32)
+        r = np.empty(n, np.uint32)
+        self._ck(self.L.ptb_read_state(self.h, _ptr(s), _ptr(r)), "ptb_read_state")
+        return s, r
+
+    def write_state(self, rgba, samples, rng):
+        rgba = np.ascontiguousarray(rgba, np.float32)
+        samples = np.ascontiguousarray(samples, np.int32)
+        rng = np.ascontiguousarray(rng, np.uint32)
+        self._ck(self.L.ptb_write_state(self.h, _ptr(rgba), _ptr(samples), _ptr(rng)), "ptb_write_state")
+
+    def read_rgba8(self, tone_mapping=True):
+        out = np.empty((self.params.height, self.params.width, 4), np.uint8)
+        self._ck(self.L.ptb_read_rgba8(self.h, _ptr(out), int(tone_mapping)), "ptb_read_rgba8")
+        return out
+
+    def counters(self):
+        c = np.zeros(8, np.uint64)
+        self._ck(self.L.ptb_read_counters(self.h, _ptr(c)), "ptb_read_counters")
+        return dict(zip(COUNTER_NAMES, (int(v) for v in c)))
+
+    def image_device_ptr(self):
+        return int(self.L.ptb_image_device_ptr(self.h) or 0)

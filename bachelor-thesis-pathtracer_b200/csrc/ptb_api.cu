@@ -1,0 +1,869 @@
+// ptb_api.cu — host side of libptb.so: context, uploads, the wavefront scheduler and the
+// extern "C" entry points declared in include/ptb.h.  No CPU rendering path exists here: every
+// result comes from the kernels in ptb_kernels.cuh.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "ptb.h"
+#include "ptb_bvh_build.h"
+#include "ptb_grid_build.h"
+#include "ptb_kernels.cuh"
+
+using namespace ptb;
+
+namespace {
+const int kThreads = 128;      // CTA size of every traversal/logic kernel (__launch_bounds__)
+const int kCtasPerSm = 8;      // persistent grid = SMs x this
+const uint32_t kRing = 1u << 14; // per-iteration queue counters kept on the device (ring)
+} // namespace
+
+struct ptb_ctx {
+    int device = 0;
+    int sms = 148;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    bool poisoned = false;
+
+    // host copy of the scene (what the loader handed over)
+    std::vector<float> pos9, nrm9;
+    std::vector<int32_t> mat;
+    std::vector<ptbs_object> objects;
+    std::vector<ptbs_material> materials;
+    std::vector<LightDev> lights;
+    ptb_camera cam{};
+    bool haveCam = false;
+    ptb_params prm{};
+    bool haveParams = false;
+
+    // structures
+    BvhResult bvh;
+    bool bvhBuilt = false, gridBuilt = false, beamBuilt = false;
+    std::vector<uint32_t> triOfId; // reference id -> leaf position
+    uint64_t gridBytes = 0, beamBytes = 0;
+
+    // device scene
+    SceneDev S{};
+    AttrDev A{};
+    float4 *dTri = nullptr, *dNrm = nullptr, *dNodes = nullptr;
+    uint32_t *dTriOfId = nullptr, *dIdOfTri = nullptr;
+    float *dVtx = nullptr;
+    MatDev *dMats = nullptr;
+    LightDev *dLights = nullptr;
+    float4 *dGridHdr = nullptr;
+    uint2 *dGridLut = nullptr;
+    uint32_t *dGridIdx = nullptr;
+    float4 *dBeam = nullptr;
+    uint32_t *dBeamRoot[3] = {nullptr, nullptr, nullptr};
+    uint32_t *dBeamIdx = nullptr;
+
+    // frame + wavefront state
+    FrameDev F{};
+    int W = 0, H = 0;
+    uint32_t nSlots = 0;
+    uint32_t *dSlotPixel = nullptr;
+    uint32_t *dQueue[2] = {nullptr, nullptr};
+    uint32_t *dShadowQ = nullptr;
+    uint32_t *dCnt = nullptr;   // [kRing] main-queue sizes per iteration
+    uint32_t *dShCnt = nullptr; // [kRing] shadow-queue sizes per iteration
+    uint32_t *hCnt = nullptr, *hShCnt = nullptr; // pinned mirrors
+    unsigned long long *dCounters = nullptr;     // [8] paths, ref rays, tri tests, AS tests, no-extend queue entries
+    int targetSamples = 0;
+    uint64_t queueEntries = 0; // sum of main-queue sizes since reset
+    uint64_t counters[PTB_CNT__N] = {0};
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    double lastMs = 0.0;
+    bool frameDirty = true; // params changed: (re)allocate the frame on next reset
+
+    // scratch for ptb_trace_rays / primary hits
+    float *dScratchF = nullptr;
+    int *dScratchI = nullptr;
+    float *dRays = nullptr;
+    uint64_t scratchN = 0;
+};
+
+static std::string g_createErr = "";
+
+namespace {
+
+int fail(ptb_ctx *c, int code, const std::string &msg) {
+    if (c) c->err = msg;
+    else g_createErr = msg;
+    return code;
+}
+
+#define CK(call)                                                                                           \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            c->poisoned = true;                                                                            \
+            return fail(c, PTB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));              \
+        }                                                                                                  \
+    } while (0)
+
+#define GUARD(c)                                                                      \
+    do {                                                                              \
+        if (!(c)) return PTB_ERR_INVALID;                                             \
+        if ((c)->poisoned) return fail((c), PTB_ERR_CUDA, "context poisoned by an earlier CUDA error: " + (c)->err); \
+        cudaError_t e0_ = cudaSetDevice((c)->device);                                 \
+        if (e0_ != cudaSuccess) return fail((c), PTB_ERR_CUDA, cudaGetErrorString(e0_)); \
+    } while (0)
+
+template <typename T>
+void devFree(T *&p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+int grid_for(const ptb_ctx *c) { return c->sms * kCtasPerSm; }
+
+void normalize3h(float *v) { // Eigen normalize (Dot.h:134-138), host float math, same order as the reference
+    float z = v[0] * v[0] + (v[1] * v[1] + v[2] * v[2]);
+    if (z > 0.0f) {
+        float l = sqrtf(z);
+        v[0] /= l;
+        v[1] /= l;
+        v[2] /= l;
+    }
+}
+float dot3h(const float *a, const float *b) { return a[0] * b[0] + (a[1] * b[1] + a[2] * b[2]); }
+
+// cameraSetForward -> orthoNormalized (camera.cpp:25-32, vector.cpp:22-27) with up=(0,1,0), right=(-1,0,0)
+void make_camera(const ptb_camera &in, CamDev &out) {
+    float f[3] = {in.forward[0], in.forward[1], in.forward[2]};
+    normalize3h(f);
+    float up[3] = {0, 1, 0}, right[3] = {-1, 0, 0};
+    float d = dot3h(f, up);
+    float b1[3] = {up[0] - d * f[0], up[1] - d * f[1], up[2] - d * f[2]};
+    normalize3h(b1);
+    float d0 = dot3h(f, right), d1 = dot3h(b1, right);
+    float b2[3];
+    for (int k = 0; k < 3; ++k) b2[k] = (right[k] - d0 * f[k]) - d1 * b1[k];
+    normalize3h(b2);
+    for (int k = 0; k < 3; ++k) {
+        out.origin[k] = in.origin[k];
+        out.forward[k] = f[k];
+        out.up[k] = b1[k];
+        out.right[k] = b2[k];
+    }
+    out.focus = in.focus;
+    out.dof = in.dof;
+    out.fovScale = tanf((in.fov_degrees * 3.14f / 180.0f) / 2.0f); // camera.cpp:16,43-45
+}
+
+ParamsDev make_params(const ptb_ctx *c) {
+    ParamsDev P{};
+    P.W = c->prm.width;
+    P.H = c->prm.height;
+    P.nee = c->prm.nee;
+    P.primary_only = c->prm.primary_only;
+    P.max_depth = c->prm.max_depth;
+    P.quirks = c->prm.reference_quirks;
+    P.debug_view = c->prm.debug_view;
+    P.debug_scale = c->prm.debug_scale;
+    P.target_samples = c->targetSamples;
+    P.n_lights = (uint32_t)c->lights.size();
+    make_camera(c->cam, P.cam);
+    return P;
+}
+
+} // namespace
+
+// =============================================================================================
+// lifetime
+// =============================================================================================
+extern "C" int ptb_create(int device, ptb_ctx **out) {
+    if (!out) return PTB_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, PTB_ERR_CUDA, std::string("no CUDA device: libptb has no CPU fallback (") + cudaGetErrorString(e) + ")");
+    if (device < 0 || device >= n) return fail(nullptr, PTB_ERR_INVALID, "device index out of range");
+    ptb_ctx *c = new ptb_ctx();
+    c->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) {
+        delete c;
+        return fail(nullptr, PTB_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    c->sms = prop.multiProcessorCount;
+    cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    cudaEventCreate(&c->evStart);
+    cudaEventCreate(&c->evStop);
+    cudaMalloc(&c->dCnt, kRing * sizeof(uint32_t));
+    cudaMalloc(&c->dShCnt, kRing * sizeof(uint32_t));
+    cudaMalloc(&c->dCounters, 8 * sizeof(unsigned long long));
+    cudaMallocHost(&c->hCnt, kRing * sizeof(uint32_t));
+    cudaMallocHost(&c->hShCnt, kRing * sizeof(uint32_t));
+    if ((e = cudaGetLastError()) != cudaSuccess) {
+        std::string m = cudaGetErrorString(e);
+        delete c;
+        return fail(nullptr, PTB_ERR_CUDA, m);
+    }
+    c->cam.fov_degrees = 70.0f;
+    c->cam.focus = 1.0f;
+    c->cam.forward[2] = 1.0f;
+    c->prm.reference_quirks = 1;
+    c->prm.world = 1;
+    c->prm.tile_w = 32;
+    c->prm.tile_h = 8;
+    *out = c;
+    return PTB_OK;
+}
+
+static void free_frame(ptb_ctx *c) {
+    devFree(c->F.image); devFree(c->F.samples); devFree(c->F.rng);
+    devFree(c->dSlotPixel);
+    devFree(c->F.ray_o); devFree(c->F.ray_d); devFree(c->F.hit); devFree(c->F.tp); devFree(c->F.light);
+    devFree(c->F.sh_o); devFree(c->F.sh_d); devFree(c->F.sh_a); devFree(c->F.sh_b); devFree(c->F.sh_c); devFree(c->F.sh_hit);
+    devFree(c->F.cnt_tri); devFree(c->F.cnt_as);
+    devFree(c->dQueue[0]); devFree(c->dQueue[1]); devFree(c->dShadowQ);
+}
+
+extern "C" void ptb_destroy(ptb_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_frame(c);
+    devFree(c->dTri); devFree(c->dNrm); devFree(c->dNodes); devFree(c->dTriOfId); devFree(c->dIdOfTri); devFree(c->dVtx);
+    devFree(c->dMats); devFree(c->dLights);
+    devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
+    devFree(c->dBeam); devFree(c->dBeamIdx);
+    for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
+    devFree(c->dCnt); devFree(c->dShCnt); devFree(c->dCounters);
+    devFree(c->dScratchF); devFree(c->dScratchI); devFree(c->dRays);
+    if (c->hCnt) cudaFreeHost(c->hCnt);
+    if (c->hShCnt) cudaFreeHost(c->hShCnt);
+    if (c->evStart) cudaEventDestroy(c->evStart);
+    if (c->evStop) cudaEventDestroy(c->evStop);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" const char *ptb_last_error(const ptb_ctx *c) { return c ? c->err.c_str() : g_createErr.c_str(); }
+
+// =============================================================================================
+// scene
+// =============================================================================================
+extern "C" int ptb_upload_triangles(ptb_ctx *c, const float *pos9, const float *nrm9, const float *uv6, const int32_t *mat, uint64_t n) {
+    GUARD(c);
+    (void)uv6; // texture lookups are outside the hot-path scope (no textured scene ships)
+    if (n && (!pos9 || !nrm9 || !mat)) return fail(c, PTB_ERR_INVALID, "null triangle arrays");
+    if (n >= (1ull << 27)) return fail(c, PTB_ERR_INVALID, "more than 2^27 triangles");
+    c->pos9.assign(pos9, pos9 + 9 * n);
+    c->nrm9.assign(nrm9, nrm9 + 9 * n);
+    c->mat.assign(mat, mat + n);
+    c->bvhBuilt = c->gridBuilt = c->beamBuilt = false;
+    return PTB_OK;
+}
+
+static int upload_lights(ptb_ctx *c) {
+    // resetScene, scene.cpp:138-148: an object is a light if any of its materials has emission >= EPS
+    c->lights.clear();
+    for (auto &o : c->objects)
+        for (uint32_t i = 0; i < o.n_materials && i < PTBS_MAX_OBJECT_MATERIALS; ++i) {
+            uint32_t mi = o.materials[i];
+            if (mi >= c->materials.size()) continue;
+            if (c->materials[mi].emission < 0.00001f) continue;
+            c->lights.push_back(LightDev{o.start_idx, o.end_idx, o.surface_area, 0});
+            break;
+        }
+    devFree(c->dLights);
+    if (!c->lights.empty()) {
+        CK(cudaMalloc(&c->dLights, c->lights.size() * sizeof(LightDev)));
+        CK(cudaMemcpy(c->dLights, c->lights.data(), c->lights.size() * sizeof(LightDev), cudaMemcpyHostToDevice));
+    }
+    c->A.lights = c->dLights;
+    return PTB_OK;
+}
+
+extern "C" int ptb_upload_objects(ptb_ctx *c, const ptbs_object *objects, uint32_t n) {
+    GUARD(c);
+    if (n && !objects) return fail(c, PTB_ERR_INVALID, "null objects");
+    c->objects.assign(objects, objects + n);
+    return upload_lights(c);
+}
+
+extern "C" int ptb_upload_materials(ptb_ctx *c, const ptbs_material *materials, uint32_t n) {
+    GUARD(c);
+    if (n && !materials) return fail(c, PTB_ERR_INVALID, "null materials");
+    c->materials.assign(materials, materials + n);
+    std::vector<MatDev> md(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        const ptbs_material &m = materials[i];
+        MatDev &d = md[i];
+        memset(&d, 0, sizeof d);
+        for (int k = 0; k < 3; ++k) {
+            d.albedo[k] = m.albedo[k];
+            d.gamma[k] = powf(m.albedo[k], 2.2f); // gammaCorrect, shader.cpp:39-44 (host libm == the reference's)
+        }
+        d.ior1 = m.ior1; d.ior2 = m.ior2; d.emission = m.emission; d.roughness = m.roughness;
+        d.wl = m.w_lambert; d.wr = m.w_reflection; d.wt = m.w_refraction;
+    }
+    devFree(c->dMats);
+    if (n) {
+        CK(cudaMalloc(&c->dMats, n * sizeof(MatDev)));
+        CK(cudaMemcpy(c->dMats, md.data(), n * sizeof(MatDev), cudaMemcpyHostToDevice));
+    }
+    c->A.mats = c->dMats;
+    return upload_lights(c);
+}
+
+extern "C" int ptb_set_camera(ptb_ctx *c, const ptb_camera *cam) {
+    GUARD(c);
+    if (!cam) return fail(c, PTB_ERR_INVALID, "null camera");
+    c->cam = *cam;
+    if (c->cam.fov_degrees == 0.0f) c->cam.fov_degrees = 70.0f;
+    c->haveCam = true;
+    return PTB_OK;
+}
+
+extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
+    GUARD(c);
+    FILE *f = path ? fopen(path, "rb") : nullptr;
+    if (!f) return fail(c, PTB_ERR_IO, std::string("cannot open ") + (path ? path : "(null)"));
+    ptbs_header h;
+    if (fread(&h, sizeof h, 1, f) != 1 || h.magic != PTBS_MAGIC || h.version != PTBS_VERSION) {
+        fclose(f);
+        return fail(c, PTB_ERR_IO, "not a .ptbs v1 container");
+    }
+    size_t n = h.n_tris;
+    std::vector<float> pos(n * 9), nrm(n * 9), uv(n * 6);
+    std::vector<int32_t> mat(n);
+    std::vector<ptbs_object> objs(h.n_objects);
+    std::vector<ptbs_material> mats(h.n_materials);
+    bool ok = fread(pos.data(), 4, n * 9, f) == n * 9 && fread(nrm.data(), 4, n * 9, f) == n * 9 &&
+              fread(uv.data(), 4, n * 6, f) == n * 6 && fread(mat.data(), 4, n, f) == n &&
+              fread(objs.data(), sizeof(ptbs_object), objs.size(), f) == objs.size() &&
+              fread(mats.data(), sizeof(ptbs_material), mats.size(), f) == mats.size();
+    fclose(f);
+    if (!ok) return fail(c, PTB_ERR_IO, "truncated .ptbs container");
+    int r;
+    if ((r = ptb_upload_triangles(c, pos.data(), nrm.data(), uv.data(), mat.data(), n))) return r;
+    if ((r = ptb_upload_materials(c, mats.data(), (uint32_t)mats.size()))) return r;
+    if ((r = ptb_upload_objects(c, objs.data(), (uint32_t)objs.size()))) return r;
+    ptb_camera cam{};
+    for (int k = 0; k < 3; ++k) {
+        cam.origin[k] = h.cam_pos[k];
+        cam.forward[k] = h.cam_forward[k];
+    }
+    cam.focus = h.cam_focus;
+    cam.dof = h.cam_dof;
+    cam.fov_degrees = 70.0f;
+    return ptb_set_camera(c, &cam);
+}
+
+// =============================================================================================
+// structures
+// =============================================================================================
+extern "C" int ptb_build_bvh(ptb_ctx *c) {
+    GUARD(c);
+    const uint64_t n = c->mat.size();
+    build_bvh(c->pos9.data(), n, 4, c->bvh);
+    // leaf-ordered device arrays: positions as (v0, e1, e2) with the reference id in v0.w,
+    // normals as (n0, n1, n2) with the material index in n0.w
+    std::vector<float4> tri(3 * n), nrm(3 * n);
+    c->triOfId.assign(n, 0);
+    for (uint64_t k = 0; k < n; ++k) {
+        const uint32_t id = c->bvh.order[k];
+        c->triOfId[id] = (uint32_t)k;
+        const float *p = &c->pos9[9 * (size_t)id], *q = &c->nrm9[9 * (size_t)id];
+        float idBits, matBits;
+        int32_t idi = (int32_t)id, mi = c->mat[id];
+        memcpy(&idBits, &idi, 4);
+        memcpy(&matBits, &mi, 4);
+        tri[3 * k] = make_float4(p[0], p[1], p[2], idBits);
+        tri[3 * k + 1] = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], 0.0f); // edge1 = v1 - v0 (triangle.cpp:10-11), fp32
+        tri[3 * k + 2] = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.0f); // edge2 = v2 - v0 (triangle.cpp:12-13)
+        nrm[3 * k] = make_float4(q[0], q[1], q[2], matBits);
+        nrm[3 * k + 1] = make_float4(q[3], q[4], q[5], 0.0f);
+        nrm[3 * k + 2] = make_float4(q[6], q[7], q[8], 0.0f);
+    }
+    devFree(c->dTri); devFree(c->dNrm); devFree(c->dNodes); devFree(c->dTriOfId); devFree(c->dIdOfTri); devFree(c->dVtx);
+    if (n) {
+        CK(cudaMalloc(&c->dTri, 3 * n * sizeof(float4)));
+        CK(cudaMalloc(&c->dNrm, 3 * n * sizeof(float4)));
+        CK(cudaMalloc(&c->dTriOfId, n * sizeof(uint32_t)));
+        CK(cudaMalloc(&c->dIdOfTri, n * sizeof(uint32_t)));
+        CK(cudaMalloc(&c->dVtx, 9 * n * sizeof(float)));
+        CK(cudaMemcpy(c->dTri, tri.data(), 3 * n * sizeof(float4), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(c->dNrm, nrm.data(), 3 * n * sizeof(float4), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(c->dTriOfId, c->triOfId.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(c->dIdOfTri, c->bvh.order.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(c->dVtx, c->pos9.data(), 9 * n * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    const size_t nn = std::max<size_t>(1, c->bvh.nodes.size());
+    CK(cudaMalloc(&c->dNodes, nn * sizeof(BvhNode64)));
+    if (!c->bvh.nodes.empty())
+        CK(cudaMemcpy(c->dNodes, c->bvh.nodes.data(), c->bvh.nodes.size() * sizeof(BvhNode64), cudaMemcpyHostToDevice));
+    c->S.tri = c->dTri;
+    c->S.nodes = c->dNodes;
+    c->S.bvh_root = c->bvh.root;
+    c->S.n_tris = (uint32_t)n;
+    c->A.nrm = c->dNrm;
+    c->A.tri_of_id = c->dTriOfId;
+    c->A.id_of_tri = c->dIdOfTri;
+    c->A.vtx = c->dVtx;
+    c->bvhBuilt = true;
+    c->gridBuilt = c->beamBuilt = false;
+    return PTB_OK;
+}
+
+extern "C" uint64_t ptb_structure_bytes(const ptb_ctx *c, int mode) {
+    if (!c) return 0;
+    const uint64_t tris = (uint64_t)c->mat.size() * 48ull;
+    if (mode == PTB_MODE_BVH) return c->bvhBuilt ? c->bvh.nodes.size() * sizeof(BvhNode64) + tris : 0;
+    if (mode == PTB_MODE_TWO_PLANE) return c->gridBuilt ? c->gridBytes + tris : 0;
+    if (mode == PTB_MODE_SUB_BEAMS) return c->beamBuilt ? c->beamBytes + tris : 0;
+    return tris;
+}
+
+// =============================================================================================
+// params / frame
+// =============================================================================================
+extern "C" int ptb_set_params(ptb_ctx *c, const ptb_params *p) {
+    GUARD(c);
+    if (!p) return fail(c, PTB_ERR_INVALID, "null params");
+    if (p->width <= 0 || p->height <= 0 || p->width > 65535 || p->height > 65535)
+        return fail(c, PTB_ERR_INVALID, "width/height out of range (1..65535: the seed packs x<<16|y)");
+    if (p->mode < 0 || p->mode > 3) return fail(c, PTB_ERR_INVALID, "mode must be 0..3");
+    if (p->world < 1 || p->rank < 0 || p->rank >= p->world) return fail(c, PTB_ERR_INVALID, "bad rank/world");
+    if (p->world > 1 && (p->tile_w <= 0 || p->tile_h <= 0)) return fail(c, PTB_ERR_INVALID, "bad tile size");
+    const ptb_params &o = c->prm;
+    if (!c->haveParams || o.width != p->width || o.height != p->height || o.rank != p->rank || o.world != p->world ||
+        o.tile_w != p->tile_w || o.tile_h != p->tile_h || (p->count_tests || p->debug_view) != (o.count_tests || o.debug_view))
+        c->frameDirty = true;
+    c->prm = *p;
+    c->haveParams = true;
+    return PTB_OK;
+}
+
+static int alloc_frame(ptb_ctx *c) {
+    free_frame(c);
+    const ptb_params &p = c->prm;
+    c->W = p.width;
+    c->H = p.height;
+    const size_t n = (size_t)c->W * c->H;
+    // owned pixels: tile (tx,ty) belongs to rank (ty*tiles_x + tx) % world
+    std::vector<uint32_t> sp;
+    sp.reserve(n / (size_t)p.world + 1);
+    if (p.world == 1) {
+        sp.resize(n);
+        for (size_t i = 0; i < n; ++i) sp[i] = (uint32_t)i;
+    } else {
+        const int tilesX = (c->W + p.tile_w - 1) / p.tile_w;
+        for (int y = 0; y < c->H; ++y)
+            for (int x = 0; x < c->W; ++x) {
+                const int t = (y / p.tile_h) * tilesX + (x / p.tile_w);
+                if (t % p.world == p.rank) sp.push_back((uint32_t)((size_t)y * c->W + x));
+            }
+    }
+    c->nSlots = (uint32_t)sp.size();
+    const size_t s = std::max<size_t>(1, c->nSlots);
+    CK(cudaMalloc(&c->F.image, n * sizeof(float4)));
+    CK(cudaMalloc(&c->F.samples, n * sizeof(int)));
+    CK(cudaMalloc(&c->F.rng, n * sizeof(uint32_t)));
+    CK(cudaMalloc(&c->dSlotPixel, s * sizeof(uint32_t)));
+    CK(cudaMemcpy(c->dSlotPixel, sp.data(), c->nSlots * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&c->F.ray_o, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.ray_d, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.hit, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.tp, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.light, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.sh_o, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.sh_d, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.sh_a, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.sh_b, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.sh_c, s * sizeof(float4)));
+    CK(cudaMalloc(&c->F.sh_hit, s * sizeof(float4)));
+    if (p.count_tests || p.debug_view) {
+        CK(cudaMalloc(&c->F.cnt_tri, s * sizeof(uint32_t)));
+        CK(cudaMalloc(&c->F.cnt_as, s * sizeof(uint32_t)));
+    }
+    CK(cudaMalloc(&c->dQueue[0], s * sizeof(uint32_t)));
+    CK(cudaMalloc(&c->dQueue[1], s * sizeof(uint32_t)));
+    CK(cudaMalloc(&c->dShadowQ, s * sizeof(uint32_t)));
+    c->F.slot_pixel = c->dSlotPixel;
+    c->F.n_slots = c->nSlots;
+    c->frameDirty = false;
+    return PTB_OK;
+}
+
+extern "C" int ptb_reset(ptb_ctx *c) {
+    GUARD(c);
+    if (!c->haveParams) return fail(c, PTB_ERR_INVALID, "ptb_set_params first");
+    if (c->frameDirty) {
+        int r = alloc_frame(c);
+        if (r) return r;
+    }
+    k_reset<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, c->F.samples, c->F.rng, c->W, c->H);
+    CK(cudaMemsetAsync(c->dCounters, 0, 8 * sizeof(unsigned long long), c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->targetSamples = 0;
+    c->queueEntries = 0;
+    memset(c->counters, 0, sizeof c->counters);
+    c->counters[PTB_CNT_KERNELS] = 1;
+    return PTB_OK;
+}
+
+static int check_mode_ready(ptb_ctx *c, int mode) {
+    if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (it also lays out the triangles)");
+    if (mode == PTB_MODE_TWO_PLANE && !c->gridBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_subgrid first");
+    if (mode == PTB_MODE_SUB_BEAMS && !c->beamBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_subbeams first");
+    return PTB_OK;
+}
+
+// =============================================================================================
+// the wavefront scheduler
+// =============================================================================================
+namespace {
+
+template <int MODE, bool COUNT>
+void launch_iteration(ptb_ctx *c, const ParamsDev &P, uint32_t it, bool nee) {
+    // iteration `it`: extend rays of queue[it&1] (sizes dCnt[it], dShCnt[it]), then logic -> queue[(it+1)&1]
+    const int g = grid_for(c);
+    k_extend<MODE, COUNT><<<g, kThreads, 0, c->stream>>>(c->S, c->F, c->dQueue[it & 1], c->dShadowQ, c->dCnt + it,
+                                                         nee ? c->dShCnt + it : nullptr);
+    k_logic<MODE, false, COUNT><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, c->dQueue[it & 1], c->dCnt + it,
+                                                               c->dQueue[(it + 1) & 1], c->dCnt + it + 1,
+                                                               nee ? c->dShadowQ : nullptr, nee ? c->dShCnt + it + 1 : nullptr,
+                                                               c->dCounters);
+}
+
+template <int MODE, bool COUNT>
+int render_mode(ptb_ctx *c, int add) {
+    c->targetSamples += add;
+    const ParamsDev P = make_params(c);
+    const bool nee = P.nee && P.n_lights > 0;
+    const int g = grid_for(c);
+    CK(cudaEventRecord(c->evStart, c->stream));
+    uint64_t kernels = 0, iterations = 0, rays = 0, shadowRays = 0;
+    uint32_t carry = 0, carryShadow = 0; // live queue sizes entering a ring pass (the first pass is filled by START)
+    bool first = true;
+    int batch = 8;
+    for (;;) {
+        // one ring pass: counters [0..kRing) zeroed, slot 1 (or 0) seeded
+        CK(cudaMemsetAsync(c->dCnt, 0, kRing * sizeof(uint32_t), c->stream));
+        if (nee) CK(cudaMemsetAsync(c->dShCnt, 0, kRing * sizeof(uint32_t), c->stream));
+        uint32_t it = 0;
+        if (first) {
+            // START: every owned pixel that needs samples gets its primary ray -> queue[1], count dCnt[1]
+            k_logic<MODE, true, COUNT><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, nullptr, nullptr, c->dQueue[1], c->dCnt + 1,
+                                                                      nullptr, nullptr, c->dCounters);
+            kernels++;
+            it = 1;
+            first = false;
+        } else {
+            // continue a previous pass: the live queue is queue[0] by construction (see below)
+            CK(cudaMemcpyAsync(c->dCnt, &carry, sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+            if (nee) CK(cudaMemcpyAsync(c->dShCnt, &carryShadow, sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+            it = 0;
+        }
+        bool done = false;
+        uint32_t checked = it;
+        while (!done && it + (uint32_t)batch + 2 < kRing) {
+            for (int b = 0; b < batch; ++b, ++it) launch_iteration<MODE, COUNT>(c, P, it, nee);
+            kernels += 2ull * batch;
+            CK(cudaMemcpyAsync(c->hCnt + checked, c->dCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+            if (nee) CK(cudaMemcpyAsync(c->hShCnt + checked, c->dShCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+            CK(cudaStreamSynchronize(c->stream));
+            for (uint32_t k = checked; k < it; ++k) {
+                rays += c->hCnt[k];
+                if (nee) shadowRays += c->hShCnt[k];
+                if (c->hCnt[k]) iterations++;
+            }
+            checked = it;
+            if (c->hCnt[it] == 0 && (!nee || c->hShCnt[it] == 0)) done = true;
+            if (batch < 64) batch *= 2;
+        }
+        if (done) break;
+        // ring exhausted: make the live queue queue[0] for the next pass
+        carry = c->hCnt[it];
+        if (it & 1) {
+            CK(cudaMemcpyAsync(c->dQueue[0], c->dQueue[1], (size_t)carry * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
+        }
+        carryShadow = nee ? c->hShCnt[it] : 0u; // the single shadow queue buffer is position independent
+        CK(cudaStreamSynchronize(c->stream));
+    }
+    CK(cudaEventRecord(c->evStop, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, c->evStart, c->evStop);
+    c->lastMs = ms;
+    unsigned long long dc[8];
+    CK(cudaMemcpy(dc, c->dCounters, sizeof dc, cudaMemcpyDeviceToHost));
+    c->queueEntries += rays;
+    c->counters[PTB_CNT_SHADOW_RAYS] += shadowRays;
+    c->counters[PTB_CNT_RAYS] = c->queueEntries - dc[4] + c->counters[PTB_CNT_SHADOW_RAYS];
+    c->counters[PTB_CNT_ITERATIONS] += iterations;
+    c->counters[PTB_CNT_KERNELS] += kernels;
+    c->counters[PTB_CNT_PATHS] = dc[0];
+    c->counters[PTB_CNT_REF_RAYS] = dc[1] + c->counters[PTB_CNT_SHADOW_RAYS];
+    c->counters[PTB_CNT_TRI_TESTS] = dc[2];
+    c->counters[PTB_CNT_AS_TESTS] = dc[3];
+    return PTB_OK;
+}
+
+template <bool COUNT>
+int render_dispatch(ptb_ctx *c, int add) {
+    switch (c->prm.mode) {
+    case PTB_MODE_ALL: return render_mode<0, COUNT>(c, add);
+    case PTB_MODE_BVH: return render_mode<1, COUNT>(c, add);
+    case PTB_MODE_TWO_PLANE: return render_mode<2, COUNT>(c, add);
+    default: return render_mode<3, COUNT>(c, add);
+    }
+}
+
+} // namespace
+
+extern "C" int ptb_render(ptb_ctx *c, int add_samples) {
+    GUARD(c);
+    if (!c->haveParams) return fail(c, PTB_ERR_INVALID, "ptb_set_params first");
+    if (add_samples <= 0) return fail(c, PTB_ERR_INVALID, "add_samples must be positive");
+    int r = check_mode_ready(c, c->prm.mode);
+    if (r) return r;
+    if (c->frameDirty) {
+        r = ptb_reset(c);
+        if (r) return r;
+    }
+    if (c->nSlots == 0) return PTB_OK;
+    const bool count = c->prm.count_tests || c->prm.debug_view;
+    return count ? render_dispatch<true>(c, add_samples) : render_dispatch<false>(c, add_samples);
+}
+extern "C" int ptb_render_async(ptb_ctx *c, int add_samples) { return ptb_render(c, add_samples); }
+extern "C" int ptb_sync(ptb_ctx *c) {
+    GUARD(c);
+    CK(cudaStreamSynchronize(c->stream));
+    return PTB_OK;
+}
+extern "C" double ptb_last_render_ms(const ptb_ctx *c) { return c ? c->lastMs : 0.0; }
+
+// =============================================================================================
+// traversal-only entry points
+// =============================================================================================
+static int ensure_scratch(ptb_ctx *c, uint64_t n, bool rays) {
+    if (n > c->scratchN) {
+        devFree(c->dScratchF); devFree(c->dScratchI); devFree(c->dRays);
+        c->scratchN = 0;
+        CK(cudaMalloc(&c->dScratchF, n * sizeof(float)));
+        CK(cudaMalloc(&c->dScratchI, 2 * n * sizeof(int)));
+        c->scratchN = n;
+    }
+    if (rays && !c->dRays) CK(cudaMalloc(&c->dRays, c->scratchN * 6 * sizeof(float)));
+    return PTB_OK;
+}
+
+extern "C" int ptb_primary_hits(ptb_ctx *c, float *t, int32_t *tri, int32_t *mat) {
+    GUARD(c);
+    if (!c->haveParams) return fail(c, PTB_ERR_INVALID, "ptb_set_params first");
+    int r = check_mode_ready(c, c->prm.mode);
+    if (r) return r;
+    const uint64_t n = (uint64_t)c->prm.width * c->prm.height;
+    if ((r = ensure_scratch(c, n, false))) return r;
+    const ParamsDev P = make_params(c);
+    const int g = grid_for(c);
+    float *dT = c->dScratchF;
+    int *dTri = c->dScratchI, *dMat = c->dScratchI + n;
+    CK(cudaEventRecord(c->evStart, c->stream));
+    switch (c->prm.mode) {
+    case PTB_MODE_ALL: k_primary<0><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
+    case PTB_MODE_BVH: k_primary<1><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
+    case PTB_MODE_TWO_PLANE: k_primary<2><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
+    default: k_primary<3><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
+    }
+    CK(cudaEventRecord(c->evStop, c->stream));
+    c->counters[PTB_CNT_KERNELS]++;
+    if (t) CK(cudaMemcpyAsync(t, dT, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    if (tri) CK(cudaMemcpyAsync(tri, dTri, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (mat) CK(cudaMemcpyAsync(mat, dMat, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->evStart, c->evStop);
+    c->lastMs = ms;
+    return PTB_OK;
+}
+
+extern "C" int ptb_trace_rays_device(ptb_ctx *c, const float *od6, uint64_t n, int mode, float *t, int32_t *tri) {
+    GUARD(c);
+    if (mode < 0 || mode > 3) return fail(c, PTB_ERR_INVALID, "mode must be 0..3");
+    int r = check_mode_ready(c, mode);
+    if (r) return r;
+    if (n == 0) return PTB_OK;
+    if (!od6 || !t || !tri) return fail(c, PTB_ERR_INVALID, "null ray / result pointers");
+    const int g = (int)std::min<uint64_t>((uint64_t)grid_for(c), (n + 127) / 128);
+    const bool count = c->prm.count_tests != 0;
+    CK(cudaEventRecord(c->evStart, c->stream));
+#define PTB_TRACE(M)                                                                                                    \
+    if (count) k_trace<M, true><<<g, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters);             \
+    else k_trace<M, false><<<g, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters)
+    switch (mode) {
+    case PTB_MODE_ALL: PTB_TRACE(0); break;
+    case PTB_MODE_BVH: PTB_TRACE(1); break;
+    case PTB_MODE_TWO_PLANE: PTB_TRACE(2); break;
+    default: PTB_TRACE(3); break;
+    }
+#undef PTB_TRACE
+    CK(cudaEventRecord(c->evStop, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->evStart, c->evStop);
+    c->lastMs = ms;
+    c->counters[PTB_CNT_KERNELS]++;
+    c->counters[PTB_CNT_RAYS] += n;
+    if (count) {
+        unsigned long long dc[8];
+        CK(cudaMemcpy(dc, c->dCounters, sizeof dc, cudaMemcpyDeviceToHost));
+        c->counters[PTB_CNT_TRI_TESTS] = dc[2];
+        c->counters[PTB_CNT_AS_TESTS] = dc[3];
+    }
+    return PTB_OK;
+}
+
+extern "C" int ptb_trace_rays(ptb_ctx *c, const float *od6, uint64_t n, int mode, float *t, int32_t *tri) {
+    GUARD(c);
+    if (n == 0) return PTB_OK;
+    if (!od6 || !t || !tri) return fail(c, PTB_ERR_INVALID, "null ray / result pointers");
+    int r = ensure_scratch(c, n, true);
+    if (r) return r;
+    CK(cudaMemcpyAsync(c->dRays, od6, n * 6 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    if ((r = ptb_trace_rays_device(c, c->dRays, n, mode, c->dScratchF, c->dScratchI))) return r;
+    CK(cudaMemcpyAsync(t, c->dScratchF, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(tri, c->dScratchI, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PTB_OK;
+}
+
+// =============================================================================================
+// read-back
+// =============================================================================================
+extern "C" int ptb_read_image(ptb_ctx *c, float *rgba) {
+    GUARD(c);
+    if (!rgba || !c->F.image) return fail(c, PTB_ERR_INVALID, "no frame / null buffer");
+    CK(cudaMemcpyAsync(rgba, c->F.image, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PTB_OK;
+}
+
+extern "C" int ptb_read_state(ptb_ctx *c, int32_t *samples, uint32_t *rng) {
+    GUARD(c);
+    if (!c->F.image) return fail(c, PTB_ERR_INVALID, "no frame");
+    const size_t n = (size_t)c->W * c->H;
+    if (samples) CK(cudaMemcpyAsync(samples, c->F.samples, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (rng) CK(cudaMemcpyAsync(rng, c->F.rng, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PTB_OK;
+}
+
+extern "C" int ptb_write_state(ptb_ctx *c, const float *rgba, const int32_t *samples, const uint32_t *rng) {
+    GUARD(c);
+    if (!c->F.image) return fail(c, PTB_ERR_INVALID, "no frame (ptb_reset first)");
+    if (!rgba || !samples || !rng) return fail(c, PTB_ERR_INVALID, "null state arrays");
+    const size_t n = (size_t)c->W * c->H;
+    CK(cudaMemcpyAsync(c->F.image, rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->F.samples, samples, n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->F.rng, rng, n * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    int mx = 0;
+    for (size_t i = 0; i < n; ++i) mx = std::max(mx, samples[i]);
+    c->targetSamples = mx;
+    return PTB_OK;
+}
+
+extern "C" int ptb_read_rgba8(ptb_ctx *c, uint8_t *rgba8, int tone_mapping) {
+    GUARD(c);
+    if (!rgba8 || !c->F.image) return fail(c, PTB_ERR_INVALID, "no frame / null buffer");
+    const uint32_t n = (uint32_t)c->W * c->H;
+    uchar4 *d = nullptr;
+    CK(cudaMalloc(&d, (size_t)n * 4));
+    k_tonemap<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, d, n, tone_mapping);
+    c->counters[PTB_CNT_KERNELS]++;
+    cudaError_t e = cudaMemcpyAsync(rgba8, d, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    CK(e);
+    return PTB_OK;
+}
+
+extern "C" int ptb_read_counters(ptb_ctx *c, uint64_t out[PTB_CNT__N]) {
+    GUARD(c);
+    if (!out) return fail(c, PTB_ERR_INVALID, "null");
+    memcpy(out, c->counters, sizeof c->counters);
+    return PTB_OK;
+}
+
+extern "C" void *ptb_image_device_ptr(ptb_ctx *c) { return c ? (void *)c->F.image : nullptr; }
+
+// =============================================================================================
+// Subgrid / Subbeam structures (host builders in ptb_grid_build.cpp)
+// =============================================================================================
+static void leaf_positions(const ptb_ctx *c, std::vector<float> &out) {
+    const size_t n = c->mat.size();
+    out.resize(9 * n);
+    for (size_t k = 0; k < n; ++k) memcpy(&out[9 * k], &c->pos9[9 * (size_t)c->bvh.order[k]], 36);
+}
+
+extern "C" int ptb_build_subgrid(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
+    GUARD(c);
+    if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (the Subgrid hierarchy derives from the BVH)");
+    if (gs < 1 || gs > 64 || os < 1 || os > 64) return fail(c, PTB_ERR_INVALID, "grid sizes must be 1..64");
+    std::vector<float> leaf;
+    leaf_positions(c, leaf);
+    SubgridResult R;
+    build_subgrid(leaf.data(), c->mat.size(), c->bvh, gs, os, m, R);
+    if (R.lut.size() >= (1ull << 32) || R.idx.size() >= (1ull << 32)) return fail(c, PTB_ERR_INVALID, "Subgrid pools exceed 2^32 entries");
+    devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
+    CK(cudaMalloc(&c->dGridHdr, std::max<size_t>(1, R.hdr.size()) * sizeof(GridHdr)));
+    CK(cudaMalloc(&c->dGridLut, std::max<size_t>(1, R.lut.size()) * sizeof(GridCell)));
+    CK(cudaMalloc(&c->dGridIdx, std::max<size_t>(1, R.idx.size()) * sizeof(uint32_t)));
+    CK(cudaMemcpy(c->dGridHdr, R.hdr.data(), R.hdr.size() * sizeof(GridHdr), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->dGridLut, R.lut.data(), R.lut.size() * sizeof(GridCell), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->dGridIdx, R.idx.data(), R.idx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    c->S.grid_hdr = c->dGridHdr;
+    c->S.grid_lut = c->dGridLut;
+    c->S.grid_idx = c->dGridIdx;
+    c->gridBytes = R.hdr.size() * sizeof(GridHdr) + R.lut.size() * sizeof(GridCell) + R.idx.size() * sizeof(uint32_t);
+    c->gridBuilt = true;
+    return PTB_OK;
+}
+
+extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
+    GUARD(c);
+    if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (it lays out the triangles)");
+    if (gs < 1 || gs > 64) return fail(c, PTB_ERR_INVALID, "grid size must be 1..64");
+    std::vector<float> leaf;
+    leaf_positions(c, leaf);
+    SubbeamResult R;
+    build_subbeams(leaf.data(), c->mat.size(), c->bvh.lo, c->bvh.hi, gs, m, 12, R);
+    devFree(c->dBeam); devFree(c->dBeamIdx);
+    for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
+    CK(cudaMalloc(&c->dBeam, std::max<size_t>(1, R.beams.size()) * sizeof(BeamRec)));
+    CK(cudaMalloc(&c->dBeamIdx, std::max<size_t>(1, R.idx.size()) * sizeof(uint32_t)));
+    CK(cudaMemcpy(c->dBeam, R.beams.data(), R.beams.size() * sizeof(BeamRec), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->dBeamIdx, R.idx.data(), R.idx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    c->beamBytes = R.beams.size() * sizeof(BeamRec) + R.idx.size() * sizeof(uint32_t);
+    for (int k = 0; k < 3; ++k) {
+        CK(cudaMalloc(&c->dBeamRoot[k], std::max<size_t>(1, R.root[k].size()) * sizeof(uint32_t)));
+        CK(cudaMemcpy(c->dBeamRoot[k], R.root[k].data(), R.root[k].size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        c->S.beam_root[k] = c->dBeamRoot[k];
+        c->beamBytes += R.root[k].size() * sizeof(uint32_t);
+        for (int j = 0; j < 3; ++j) {
+            c->S.beam_gmin[k][j] = R.gmin[k][j];
+            c->S.beam_gmax[k][j] = R.gmax[k][j];
+        }
+        c->S.beam_amin[k] = R.amin[k];
+        c->S.beam_amax[k] = R.amax[k];
+    }
+    c->S.beam = reinterpret_cast<const float4 *>(c->dBeam);
+    c->S.beam_idx = c->dBeamIdx;
+    c->S.beam_grid_size = R.grid_size;
+    c->S.n_beams = (uint32_t)R.beams.size();
+    c->beamBuilt = true;
+    return PTB_OK;
+}

@@ -1,0 +1,318 @@
+// ptb_device.cuh — device-side building blocks of the sm_100a wavefront path tracer.
+//
+// Arithmetic contract: every float expression that decides a hit, a
+// direction or an RNG draw is evaluated in the reference's order with IEEE fp32 and NO fused
+// multiply-add.  The translation unit is compiled with -fmad=false -prec-div=true
+// -prec-sqrt=true -ftz=false, so `a*b+c` below is two roundings, `/` and sqrtf are correctly
+// rounded, and denormals are kept — the same results as the reference's x86 SSE/AVX code
+// (CMakeLists.txt:12 has no -mfma).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ptb {
+
+#define PTB_INF __int_as_float(0x7f800000)
+#define PTB_EPS 0.00001f /* src/common.h:6 */
+
+struct f3 {
+    float x, y, z;
+};
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { return f3{x, y, z}; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return f3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return f3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return f3{a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ f3 operator*(float s, f3 a) { return f3{a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return f3{a.x * b.x, a.y * b.y, a.z * b.z}; }
+__device__ __forceinline__ f3 operator/(f3 a, float s) { return f3{a.x / s, a.y / s, a.z / s}; }
+// Eigen Vector3f::dot order: a0*b0 + (a1*b1 + a2*b2)   
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) {
+    return f3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+// Eigen normalize(): squaredNorm > 0 ? v / sqrt(squaredNorm) : v   (Eigen/src/Core/Dot.h:134-138)
+__device__ __forceinline__ f3 normalize3(f3 v) {
+    float z = v.x * v.x + (v.y * v.y + v.z * v.z);
+    if (z > 0.0f) {
+        float l = sqrtf(z);
+        return f3{v.x / l, v.y / l, v.z / l};
+    }
+    return v;
+}
+__device__ __forceinline__ float max3(f3 v) { return fmaxf(v.x, fmaxf(v.y, v.z)); } // src/types/vector.cpp:6-9
+// std::max / std::min select forms (NaN-order sensitive; src/types/aabb.cpp:17-23)
+__device__ __forceinline__ float smax(float a, float b) { return (a < b) ? b : a; }
+__device__ __forceinline__ float smin(float a, float b) { return (b < a) ? b : a; }
+__device__ __forceinline__ float comp(f3 v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : v.z); }
+__device__ __forceinline__ f3 rcp3(f3 d) { return f3{1.0f / d.x, 1.0f / d.y, 1.0f / d.z}; }
+
+// ---- RNG: src/common.cpp:8-21.  (float)UINT32_MAX rounds to 2^32, so the divide is an exact
+// scale by 2^-32; the result lies in [0,1] inclusive.
+__device__ __forceinline__ uint32_t hash_coords(int x, int y) { return ((uint32_t)x << 16) | (uint32_t)y; }
+__device__ __forceinline__ float fast_random(uint32_t &seed) {
+    uint32_t state = seed * 747796405u + 2891336453u;
+    uint32_t word = ((state >> ((state >> 28u) + 4u)) ^ state) * 277803737u;
+    seed = (word >> 22u) ^ word;
+    return __uint2float_rn(seed) * 2.3283064365386963e-10f;
+}
+
+// ---- hit record kept during traversal (deferred attributes: SURVEY.md §8 a10) -------------
+struct Hit {
+    float t;  // ray.tmax
+    int tri;  // index into the leaf-ordered triangle array, -1 = miss
+    float u, v;
+    int id;   // reference triangle id of `tri` (tie rule)
+};
+
+// Flattened structures in HBM (layouts: DESIGN.md "Data layout").
+struct SceneDev {
+    const float4 *__restrict__ tri;     // 3 float4 per triangle: (v0, id), (e1, -), (e2, -); leaf order
+    const float4 *__restrict__ nodes;   // BVH2, 4 float4 (64 B) per inner node
+    int bvh_root;                       // node ref (>=0 inner, <0 leaf)
+    uint32_t n_tris;
+    // Subgrid ("2Plane")
+    const float4 *__restrict__ grid_hdr; // 4 float4 (64 B) per grid
+    const uint2 *__restrict__ grid_lut;  // {start,end} per cell, absolute into grid_idx
+    const uint32_t *__restrict__ grid_idx;
+    // Subbeams
+    const float4 *__restrict__ beam;     // 3 float4 (48 B) per beam: minUVST, maxUVST, (start,end,hasTris,-)
+    const uint32_t *__restrict__ beam_root[3];
+    const uint32_t *__restrict__ beam_idx;
+    float beam_gmin[3][3], beam_gmax[3][3], beam_amin[3], beam_amax[3];
+    uint32_t beam_grid_size;
+    uint32_t n_beams;
+};
+
+// ---- Moeller-Trumbore: src/primitives/triangle.cpp:7-52, positions only --------------------
+// Accept rule: !(t < 1e-5) && !(tmax < t); among bit-equal t the larger reference id wins
+// (the reference lets the later-tested one win; brute-force order == ascending id).
+template <bool COUNT>
+__device__ __forceinline__ void intersect_tri(const float4 *__restrict__ tri, int idx, f3 o, f3 d, Hit &h, uint32_t &nTri) {
+    const float4 a = __ldg(&tri[3 * idx]);
+    const float4 b = __ldg(&tri[3 * idx + 1]);
+    const float4 c = __ldg(&tri[3 * idx + 2]);
+    if (COUNT) nTri++;
+    const f3 v0 = mk3(a.x, a.y, a.z), e1 = mk3(b.x, b.y, b.z), e2 = mk3(c.x, c.y, c.z);
+    const f3 p = cross3(d, e2);
+    const float det = dot3(e1, p);
+    if (fabsf(det) <= 0.01f) return; // fabs(det) < 0.01 evaluated in double (triangle.cpp:20)
+    const float inv = 1.0f / det;
+    const f3 tv = o - v0;
+    const float u = dot3(tv, p) * inv;
+    if (0.0f > u || u > 1.0f) return;
+    const f3 q = cross3(tv, e1);
+    const float v = dot3(d, q) * inv;
+    if (0.0f > v || u + v > 1.0f) return;
+    const float t = dot3(e2, q) * inv;
+    if (t < 0.00001f || h.t < t) return;
+    const int id = __float_as_int(a.w);
+    if (t == h.t && id < h.id) return;
+    h.t = t;
+    h.tri = idx;
+    h.u = u;
+    h.v = v;
+    h.id = id;
+}
+
+// ---- slab test: src/types/aabb.cpp:9-45 (same nesting of select-min/max) --------------------
+__device__ __forceinline__ bool slab(f3 lo, f3 hi, f3 o, f3 inv, float tmax, float &tn) {
+    const float tx1 = (lo.x - o.x) * inv.x, tx2 = (hi.x - o.x) * inv.x;
+    const float ty1 = (lo.y - o.y) * inv.y, ty2 = (hi.y - o.y) * inv.y;
+    const float tz1 = (lo.z - o.z) * inv.z, tz2 = (hi.z - o.z) * inv.z;
+    const float t0 = smax(smax(smax(smin(tx1, tx2), smin(ty1, ty2)), smin(tz1, tz2)), 0.0f);
+    const float t1 = smin(smin(smin(smax(tx1, tx2), smax(ty1, ty2)), smax(tz1, tz2)), tmax);
+    tn = t0;
+    return t0 <= t1;
+}
+
+#define PTB_STACK 64
+#define PTB_GSTACK 160 /* Subgrid: <= 16 children pushed per level */
+
+// leaf reference: ~((first << 4) | (count - 1)), count <= 16
+__device__ __forceinline__ void leaf_decode(int ref, int &first, int &count) {
+    const uint32_t r = (uint32_t)~ref;
+    first = (int)(r >> 4);
+    count = (int)(r & 15u) + 1;
+}
+
+// ---- BVH closest hit: stands in for findBVHIntesection (bvh.cpp:48-99) ---------------------
+// One 64-byte node holds both children's boxes, so each inner node costs 4 LDG.128 and two slab
+// tests (the reference re-tests a node's own box after its parent already did).  Near child
+// first; the far child is pushed with its entry distance and culled against the shrunken tmax
+// when popped (same effect as the reference's pop-time re-test).
+template <bool COUNT>
+__device__ __forceinline__ void bvh_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nBox) {
+    const f3 inv = rcp3(d);
+    int sref[PTB_STACK];
+    float sdist[PTB_STACK];
+    int sp = 0;
+    int ref = S.bvh_root;
+    for (;;) {
+        if (ref >= 0) {
+            const float4 *n = S.nodes + 4 * (size_t)ref;
+            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
+            const int4 q3 = __ldg(reinterpret_cast<const int4 *>(n + 3));
+            if (COUNT) nBox += 2;
+            float d0, d1;
+            const bool h0 = slab(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
+            const bool h1 = slab(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
+            if (h0 && h1) {
+                // bvh.cpp:75-84: left first unless the right child is strictly nearer
+                const bool leftFirst = d1 >= d0;
+                const int nearRef = leftFirst ? q3.x : q3.y, farRef = leftFirst ? q3.y : q3.x;
+                sref[sp] = farRef;
+                sdist[sp] = leftFirst ? d1 : d0;
+                sp++;
+                ref = nearRef;
+                continue;
+            } else if (h0) {
+                ref = q3.x;
+                continue;
+            } else if (h1) {
+                ref = q3.y;
+                continue;
+            }
+        } else {
+            int first, count;
+            leaf_decode(ref, first, count);
+            for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
+        }
+        // pop
+        for (;;) {
+            if (sp == 0) return;
+            sp--;
+            if (!(sdist[sp] > h.t)) break;
+        }
+        ref = sref[sp];
+    }
+}
+
+// ---- brute force: mode ALL (scene.cpp:77-86, object.cpp:19-34) ------------------------------
+template <bool COUNT>
+__device__ __forceinline__ void brute_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri) {
+    for (uint32_t i = 0; i < S.n_tris; ++i) intersect_tri<COUNT>(S.tri, (int)i, o, d, h, nTri);
+}
+
+// dominant axis: lightFieldGrid.cpp:79-95 (strict >, first wins)
+__device__ __forceinline__ int dominant_axis(f3 d) {
+    int axis = 0;
+    float m = 0.0f;
+    const float f0 = fabsf(d.x), f1 = fabsf(d.y), f2 = fabsf(d.z);
+    if (f0 > m) { m = f0; axis = 0; }
+    if (f1 > m) { m = f1; axis = 1; }
+    if (f2 > m) { m = f2; axis = 2; }
+    return axis;
+}
+
+// ---- Subgrid ("2Plane"/Hybrid) closest hit: stands in for intersectGrid (lightFieldGrid.cpp:71-147)
+// Grid header (4 float4): (aabb.min, size | hasTris<<31) (aabb.max, lutBase) (min, -) (inv_delta, -)
+// grid.max[axis] is aabb.max[axis] + 0.1f (adjustGridSize, lightFieldGrid.cpp:176-178).
+template <bool COUNT>
+__device__ __forceinline__ void subgrid_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
+    const f3 inv = rcp3(d);
+    const int axis = dominant_axis(d);
+    const int right = axis == 0 ? 1 : 0, up = axis == 2 ? 1 : 2; // lightFieldGrid.cpp:26-35
+    const float oa = comp(o, axis), ia = comp(inv, axis), da = comp(d, axis);
+    const float orr = comp(o, right), dr = comp(d, right), ou = comp(o, up), du = comp(d, up);
+    uint32_t stack[PTB_GSTACK];
+    int sp = 0;
+    stack[sp++] = (uint32_t)axis;
+    while (sp > 0) {
+        const uint32_t g = stack[--sp];
+        const float4 *hd = S.grid_hdr + 4 * (size_t)g;
+        const float4 h0 = __ldg(hd), h1 = __ldg(hd + 1);
+        if (COUNT) nAS++;
+        float tn;
+        if (!slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)) continue;
+        if (COUNT) nAS++;
+        const float4 h2 = __ldg(hd + 2), h3 = __ldg(hd + 3);
+        const f3 gmin = mk3(h2.x, h2.y, h2.z), idl = mk3(h3.x, h3.y, h3.z);
+        const float gmaxA = comp(mk3(h1.x, h1.y, h1.z), axis) + 0.1f;
+        const float d1 = (comp(gmin, axis) - oa) * ia;
+        const float d2 = (gmaxA - oa) * ia;
+        // in = (origin + d1*dir - min) * inv_delta, out likewise (lightFieldGrid.cpp:116-117)
+        const float inR = ((orr + d1 * dr) - comp(gmin, right)) * comp(idl, right);
+        const float inU = ((ou + d1 * du) - comp(gmin, up)) * comp(idl, up);
+        const float outR = ((orr + d2 * dr) - comp(gmin, right)) * comp(idl, right);
+        const float outU = ((ou + d2 * du) - comp(gmin, up)) * comp(idl, up);
+        const uint32_t sz = __float_as_uint(h0.w) & 0x7fffffffu;
+        const bool hasTris = (__float_as_uint(h0.w) >> 31) != 0u;
+        const float fs = (float)sz;
+        const int iu = (int)(inR * fs), iv = (int)(inU * fs), is = (int)(outR * fs), it = (int)(outU * fs);
+        // the reference indexes without a bounds check (A.12); outside the planes means no cell
+        if ((unsigned)iu >= sz || (unsigned)iv >= sz || (unsigned)is >= sz || (unsigned)it >= sz) continue;
+        const uint32_t cell = ((((uint32_t)iu * sz + (uint32_t)iv) * sz + (uint32_t)is) * sz + (uint32_t)it);
+        const uint2 se = __ldg(&S.grid_lut[(size_t)__float_as_uint(h1.w) + cell]);
+        if (hasTris) {
+            for (uint32_t i = se.x; i < se.y; ++i) intersect_tri<COUNT>(S.tri, (int)__ldg(&S.grid_idx[i]), o, d, h, nTri);
+        } else if (da < 0.0f) {
+            for (uint32_t i = se.x; i < se.y && sp < PTB_GSTACK; ++i) stack[sp++] = __ldg(&S.grid_idx[i]);
+        } else {
+            for (uint32_t i = se.y; i > se.x && sp < PTB_GSTACK; --i) stack[sp++] = __ldg(&S.grid_idx[i - 1]);
+        }
+    }
+}
+
+// ---- Subbeam closest hit: stands in for intersectSubBeamGrid (SubBeams.cpp:73-170) ---------
+template <bool COUNT>
+__device__ __forceinline__ void subbeam_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
+    const f3 inv = rcp3(d);
+    const int axis = dominant_axis(d);
+    const int right = axis == 0 ? 1 : 0, up = axis == 2 ? 1 : 2;
+    const f3 gmin = mk3(S.beam_gmin[axis][0], S.beam_gmin[axis][1], S.beam_gmin[axis][2]);
+    const f3 gmax = mk3(S.beam_gmax[axis][0], S.beam_gmax[axis][1], S.beam_gmax[axis][2]);
+    if (COUNT) nAS++;
+    const float oa = comp(o, axis), ia = comp(inv, axis);
+    const float d1 = (comp(gmin, axis) - oa) * ia;
+    const float d2 = (comp(gmax, axis) - oa) * ia;
+    if (smax(d1, d2) < 0.0f) return;
+    if (COUNT) nAS++;
+    float tn;
+    if (!slab(mk3(S.beam_amin[0], S.beam_amin[1], S.beam_amin[2]), mk3(S.beam_amax[0], S.beam_amax[1], S.beam_amax[2]), o, inv, h.t, tn)) return;
+    const float orr = comp(o, right), dr = comp(d, right), ou = comp(o, up), du = comp(d, up);
+    const float ext_r = comp(gmax, right) - comp(gmin, right), ext_u = comp(gmax, up) - comp(gmin, up);
+    float uvst[4];
+    uvst[0] = ((orr + d1 * dr) - comp(gmin, right)) / ext_r;
+    uvst[1] = ((ou + d1 * du) - comp(gmin, up)) / ext_u;
+    uvst[2] = ((orr + d2 * dr) - comp(gmin, right)) / ext_r;
+    uvst[3] = ((ou + d2 * du) - comp(gmin, up)) / ext_u;
+    const uint32_t gs = S.beam_grid_size;
+    const float fs = (float)gs;
+    const int iu = (int)(uvst[0] * fs), iv = (int)(uvst[1] * fs), is = (int)(uvst[2] * fs), it = (int)(uvst[3] * fs);
+    if ((unsigned)iu >= gs || (unsigned)iv >= gs || (unsigned)is >= gs || (unsigned)it >= gs) return;
+    uint32_t b = __ldg(&S.beam_root[axis][(((uint32_t)iu * gs + (uint32_t)iv) * gs + (uint32_t)is) * gs + (uint32_t)it]);
+    const float invg = 1.0f / fs;
+    for (;;) {
+        if (b >= S.n_beams) return;
+        const float4 mn = __ldg(&S.beam[3 * (size_t)b]);
+        const float4 mx = __ldg(&S.beam[3 * (size_t)b + 1]);
+        const uint4 se = __ldg(reinterpret_cast<const uint4 *>(&S.beam[3 * (size_t)b + 2]));
+        if (se.x >= se.y) return;
+        if (se.z) {
+            for (uint32_t i = se.x; i < se.y; ++i) intersect_tri<COUNT>(S.tri, (int)__ldg(&S.beam_idx[i]), o, d, h, nTri);
+            return;
+        }
+        if (COUNT) nAS++;
+        // scaled = (ray - min/gridSize) / ((max-min)/gridSize); Vector4/float is v*(1.0f/s) (vector.cpp)
+        const float s0 = (uvst[0] - mn.x * invg) / ((mx.x - mn.x) * invg);
+        const float s1 = (uvst[1] - mn.y * invg) / ((mx.y - mn.y) * invg);
+        const float s2 = (uvst[2] - mn.z * invg) / ((mx.z - mn.z) * invg);
+        const float s3 = (uvst[3] - mn.w * invg) / ((mx.w - mn.w) * invg);
+        if (s0 < 0 || s0 > 1 || s1 < 0 || s1 > 1 || s2 < 0 || s2 > 1 || s3 < 0 || s3 > 1) return;
+        // getBeamIdx (SubBeams.cpp:28-34); a coordinate of exactly 1.0 would index past the 16
+        // children there — clamped to the last child here (documented deviation, measure zero)
+        const int c0 = min((int)floorf(s0 * 2.0f), 1), c1 = min((int)floorf(s1 * 2.0f), 1);
+        const int c2 = min((int)floorf(s2 * 2.0f), 1), c3 = min((int)floorf(s3 * 2.0f), 1);
+        b = se.x + (uint32_t)(c0 * 8 + c1 * 4 + c2 * 2 + c3);
+    }
+}
+
+template <int MODE, bool COUNT>
+__device__ __forceinline__ void closest_hit(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
+    if (MODE == 1) bvh_closest<COUNT>(S, o, d, h, nTri, nAS);
+    else if (MODE == 2) subgrid_closest<COUNT>(S, o, d, h, nTri, nAS);
+    else if (MODE == 3) subbeam_closest<COUNT>(S, o, d, h, nTri, nAS);
+    else brute_closest<COUNT>(S, o, d, h, nTri);
+}
+
+} // namespace ptb

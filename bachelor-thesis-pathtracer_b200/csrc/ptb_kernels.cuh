@@ -1,0 +1,561 @@
+// ptb_kernels.cuh — the wavefront stages.
+//
+//   k_extend  : closest hit for every queued ray (path rays + NEE shadow rays) — pure traversal
+//   k_logic   : everything between two traversals of a path: [resolve shadow] -> shade the hit
+//               (or replay the reference's miss loop arithmetically) -> depth/terminate ->
+//               accumulate -> regenerate the pixel's next sample -> next roulette draw ->
+//               append the slot to the next queue (warp-ballot aggregated)
+//   k_trace / k_primary : traversal-only entry points (ptb_trace_rays, ptb_primary_hits)
+//   k_tonemap : display transform
+//
+// One slot per owned pixel: a pixel's samples are serialised because sample k+1 continues the
+// RNG stream of sample k and the running mean is order dependent (tracer.cpp:147-154), so the
+// in-flight set is "one path per pixel", regenerated in place when a path ends.
+#pragma once
+#include "ptb_device.cuh"
+
+namespace ptb {
+
+struct CamDev { // createCameraRay inputs, camera.cpp:47-66
+    float origin[3], forward[3], right[3], up[3];
+    float focus, dof, fovScale;
+};
+
+struct MatDev { // 16 floats
+    float albedo[3];
+    float gamma[3]; // powf(albedo, 2.2f) evaluated on the host with the same libm the reference uses (shader.cpp:39-44)
+    float ior1, ior2, emission, roughness, wl, wr, wt;
+    float pad[3];
+};
+
+struct LightDev { // Object fields NEE reads (shader.cpp:69-113, object.cpp:176-180)
+    int start, end; // reference triangle id range
+    float surfaceArea;
+    int pad;
+};
+
+struct ParamsDev {
+    int W, H;
+    int nee, primary_only, max_depth, quirks, debug_view, debug_scale;
+    int target_samples;
+    uint32_t n_lights;
+    CamDev cam;
+};
+
+#define PTB_FLAG_KILLED 1u  /* roulette-killed ray that TWO_PLANE still traverses and shades (A.4) */
+#define PTB_FLAG_SHADOW 2u  /* a shadow ray of this slot is in flight */
+#define PTB_FLAG_DONE 4u    /* path already ended; only its shadow result is awaited before accumulation */
+#define PTB_Q_NOEXTEND 0x80000000u /* queue entry bit: visit k_logic next iteration but do not traverse */
+
+struct FrameDev {
+    float4 *image;      // [W*H] running mean, alpha 1
+    int *samples;       // [W*H]
+    uint32_t *rng;      // [W*H]
+    const uint32_t *slot_pixel; // [n_slots] pixel index y*W+x of each owned slot
+    uint32_t n_slots;
+    float4 *ray_o, *ray_d;  // [n_slots] origin / direction of the ray being extended
+    float4 *hit;            // [n_slots] (t, tri bits, u, v)
+    float4 *tp;             // [n_slots] throughput.xyz, depth bits
+    float4 *light;          // [n_slots] light.xyz, flag bits
+    // NEE shadow records
+    float4 *sh_o, *sh_d;    // origin.xyz + initial tmax ; direction.xyz + light triangle (leaf order) bits
+    float4 *sh_a;           // throughput.xyz at the bounce, distance
+    float4 *sh_b;           // emission*throughput (pending add), cosSurface
+    float4 *sh_c;           // cosLight, surfaceArea
+    float4 *sh_hit;         // (t, tri bits, -, -)
+    // per-ray test counters for the heat-map view / counter parity (optional)
+    uint32_t *cnt_tri, *cnt_as; // [n_slots]
+};
+
+struct AttrDev {
+    const float4 *nrm;   // 3 float4 per triangle (n0,n1,n2), leaf order; n0.w = material index bits
+    const MatDev *mats;
+    const LightDev *lights;
+    const uint32_t *tri_of_id; // reference triangle id -> leaf-order index
+    const uint32_t *id_of_tri; // leaf-order index -> reference id
+    const float *vtx;          // 9 floats per triangle by reference id (NEE light points); null unless nee
+};
+
+__device__ __forceinline__ f3 ld3(const float *p) { return mk3(p[0], p[1], p[2]); }
+
+// ---- raygen: setupRay (tracer.cpp:72-88) + createCameraRay (camera.cpp:47-66) ---------------
+__device__ __forceinline__ void setup_ray(const ParamsDev &P, int x, int y, uint32_t &rng, f3 &o, f3 &d) {
+    const float xi1 = 2 * fast_random(rng) - 1.0f;
+    const float xi2 = 2 * fast_random(rng) - 1.0f;
+    float xIn = 2.0f * (((float)x + xi1) / (float)P.W) - 1.0f;
+    float yIn = 2.0f * (((float)y + xi2) / (float)P.H) - 1.0f;
+    yIn = -yIn;
+    if (P.W >= P.H) yIn = (float)P.H / (float)P.W * yIn;
+    else xIn = (float)P.W / (float)P.H * xIn;
+    const f3 right = ld3(P.cam.right), up = ld3(P.cam.up), fwd = ld3(P.cam.forward);
+    o = ld3(P.cam.origin);
+    d = normalize3(right * (xIn * P.cam.fovScale) + up * (yIn * P.cam.fovScale) + fwd);
+    const float l1 = fast_random(rng) * P.cam.dof;
+    const float l2 = fast_random(rng) * P.cam.dof;
+    const f3 lens = right * l1 + up * l2;
+    o = o + lens;
+    d = normalize3(d * P.cam.focus - lens);
+}
+
+// ---- sampling: src/types/ray.cpp:8-29 (double cos/sin/sqrt on float arguments, pi = 3.14f) --
+__device__ __forceinline__ void sample_disk(uint32_t &rng, float &sx, float &sy) {
+    const float theta = fast_random(rng);
+    const float st = sqrtf(theta);
+    const float phi = 2 * 3.14f * fast_random(rng);
+    double s, c;
+    sincos((double)phi, &s, &c);
+    sx = (float)((double)st * c);
+    sy = (float)((double)st * s);
+}
+__device__ __forceinline__ f3 cosine_dir(uint32_t &rng) {
+    f3 r;
+    sample_disk(rng, r.x, r.y);
+    r.z = sqrtf(smax(0.0f, 1.0f - r.x * r.x - r.y * r.y)); // sqrt in double then narrowed == sqrtf (innocuous double rounding)
+    return r;
+}
+
+// tangent frame + interpolated normal: triangle.cpp:43-45
+__device__ __forceinline__ void hit_frame(const AttrDev &A, int tri, float u, float v, f3 &n, f3 &tg, f3 &bt, int &mat) {
+    const float4 a = __ldg(&A.nrm[3 * tri]), b = __ldg(&A.nrm[3 * tri + 1]), c = __ldg(&A.nrm[3 * tri + 2]);
+    mat = __float_as_int(a.w);
+    const float w = 1 - u - v;
+    n = normalize3(u * mk3(b.x, b.y, b.z) + v * mk3(c.x, c.y, c.z) + w * mk3(a.x, a.y, a.z));
+    const f3 helper = (fabsf(n.z) < 0.999f) ? mk3(0, 0, 1) : mk3(1.0f, 0.0f, 0.0f); // (double)|z| < 0.999  <=>  |z| < 0.999f
+    tg = normalize3(cross3(n, helper));
+    bt = cross3(n, tg);
+}
+
+struct PathState {
+    f3 o, d, tp, light;
+    int depth;
+    uint32_t flags;
+    uint32_t rng;
+};
+
+struct ShadowOut {
+    bool emit;
+    f3 o, d;
+    float tmax0, distance, cosSurface, cosLight, area;
+    int lightTri;
+};
+
+// ---- shade: shader.cpp:239-277 with lambert :204-236, reflection :116-139, refraction :141-201
+// Returns with the path's next ray in (o,d).  When NEE fires a shadow ray, `light` is left
+// BEFORE the two adds of shader.cpp:233 and :275; they are applied in order by the shadow
+// resolve (pendingEm = emission*throughput).
+__device__ __forceinline__ void shade_hit(const ParamsDev &P, const SceneDev &S, const AttrDev &A, PathState &ps, float t, int tri,
+                                          float u, float v, bool &terminated, ShadowOut &sh, f3 &pendingEm) {
+    f3 n, tg, bt;
+    int mi;
+    hit_frame(A, tri, u, v, n, tg, bt, mi);
+    const MatDev m = A.mats[mi];
+    if (P.primary_only) {
+        terminated = true;
+        ps.light = ld3(m.albedo);
+    }
+    const float xi = fast_random(ps.rng);
+    const f3 color = ld3(m.gamma);
+    sh.emit = false;
+    if (xi < m.wl) { // lambert
+        ps.o = ps.o + ps.d * t;
+        const f3 rd = cosine_dir(ps.rng);
+        ps.d = normalize3(rd.x * tg + rd.y * bt + rd.z * n);
+        ps.o = ps.o + ps.d * PTB_EPS;
+        ps.tp = ps.tp * color;
+        if (P.nee && P.n_lights > 0) { // nextEventEstimation, shader.cpp:69-113
+            const float f = fast_random(ps.rng);
+            uint32_t li = (uint32_t)floorf(f * (float)P.n_lights);
+            if (li >= P.n_lights) li = P.n_lights - 1; // f == 1.0: the reference reads past the end (A.12)
+            const LightDev L = A.lights[li];
+            float xi1, xi2;
+            sample_disk(ps.rng, xi1, xi2);
+            const float xi3 = 1 - xi1 - xi2;
+            const uint32_t range = (uint32_t)(L.end - L.start);
+            const uint32_t id = (uint32_t)((float)L.start + floorf(fast_random(ps.rng) * (float)range));
+            if (id < S.n_tris) {
+                const float *pv = A.vtx + 9 * (size_t)id; // exact reference vertices (Triangle::vertices)
+                const f3 v0 = ld3(pv), v1 = ld3(pv + 3), v2 = ld3(pv + 6);
+                const f3 point = v1 * xi1 + v2 * xi2 + v0 * xi3;
+                const f3 sd = normalize3(point - ps.o);
+                const float cosSurface = dot3(n, sd);
+                if (!(cosSurface < PTB_EPS)) {
+                    const int lt = (int)__ldg(&A.tri_of_id[id]);
+                    Hit lh{PTB_INF, -1, 0.0f, 0.0f, -1};
+                    uint32_t dummy = 0;
+                    intersect_tri<false>(S.tri, lt, ps.o, sd, lh, dummy); // shader.cpp:97
+                    if (lh.tri >= 0) { // a failed test leaves distance = inf there -> no contribution
+                        f3 nl, t2, b2;
+                        int lm;
+                        hit_frame(A, lt, lh.u, lh.v, nl, t2, b2, lm);
+                        sh.emit = true;
+                        sh.o = ps.o;
+                        sh.d = sd;
+                        sh.cosSurface = cosSurface;
+                        sh.cosLight = -dot3(nl, sd);
+                        sh.tmax0 = lh.t - PTB_EPS;
+                        sh.distance = sh.tmax0;
+                        sh.area = L.surfaceArea;
+                        sh.lightTri = lt;
+                    }
+                }
+            }
+        }
+    } else if (xi < (m.wl + m.wr)) { // reflection
+        ps.o = ps.o + ps.d * t;
+        ps.d = ps.d - 2.0f * dot3(ps.d, n) * n;
+        const f3 rd = cosine_dir(ps.rng);
+        f3 dir = rd.x * tg;
+        dir = dir + rd.y * bt;
+        dir = dir + rd.z * n;
+        dir = normalize3(dir);
+        ps.d = normalize3(ps.d * (1 - m.roughness) + dir * m.roughness);
+        ps.tp = ps.tp * color;
+        ps.o = ps.o + ps.d * 0.01f;
+    } else { // refraction
+        f3 nn = n;
+        const float n1 = m.ior1, n2 = m.ior2;
+        float eta = n1 / n2;
+        float cs = dot3(ps.d, n);
+        if (cs >= PTB_EPS) {
+            cs *= -1;
+            eta = 1.0f / eta;
+            nn = n * -1.0f;
+        }
+        const float disc = 1.0f - (eta * eta) * (1.0f - (cs * cs));
+        const float x2 = fast_random(ps.rng);
+        float r0 = ((n1 - n2) / (n1 + n2)); // calculateFresnelTerm, shader.cpp:46-50 (pow in double)
+        r0 *= r0;
+        float refl = (float)((double)r0 + (double)(1 - r0) * pow((double)(1 - (-cs)), 5.0));
+        if (refl > 1) refl = 1;
+        if (refl < 0) refl = 0;
+        f3 rdir;
+        if (disc < PTB_EPS || x2 < refl) rdir = normalize3(ps.d - 2.0f * dot3(ps.d, n) * n);
+        else rdir = normalize3(eta * (ps.d - cs * nn) - nn * sqrtf(disc + PTB_EPS));
+        ps.o = ps.o + ps.d * t + rdir * PTB_EPS;
+        ps.tp = ps.tp * color;
+        ps.d = rdir;
+        const f3 rd = cosine_dir(ps.rng);
+        f3 dir = rd.x * tg;
+        dir = dir + rd.y * bt;
+        dir = dir + rd.z * n;
+        dir = normalize3(dir);
+        ps.d = normalize3(ps.d * (1 - m.roughness) + dir * m.roughness);
+    }
+    pendingEm = m.emission * ps.tp; // shader.cpp:275 (always added; with NEE after the NEE term)
+}
+
+
+// warp-aggregated queue append: one atomicAdd per warp (ballot + popc + shuffle broadcast)
+__device__ __forceinline__ void queue_push(bool pred, uint32_t value, uint32_t *__restrict__ q, uint32_t *__restrict__ count) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0u) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(count, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) q[base + __popc(m & ((1u << lane) - 1u))] = value;
+}
+
+// ---- extend: closest hit for the queued rays -------------------------------------------------
+// Entries [0, nMain) are path rays of slot q[e]; entries [nMain, nMain+nShadow) are the NEE
+// shadow rays of slot qs[e-nMain], which start from the light triangle's own hit
+// (shader.cpp:97-101).  Persistent grid, warp-granular work distribution.
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(128) k_extend(SceneDev S, FrameDev F, const uint32_t *__restrict__ q, const uint32_t *__restrict__ qs,
+                                                const uint32_t *__restrict__ nMainPtr, const uint32_t *__restrict__ nShadowPtr) {
+    const uint32_t nMain = *nMainPtr, nShadow = nShadowPtr ? *nShadowPtr : 0u;
+    const uint32_t total = nMain + nShadow;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+        uint32_t nTri = 0, nAS = 0;
+        if (e < nMain) {
+            const uint32_t slot = q[e];
+            if (slot & PTB_Q_NOEXTEND) continue;
+            const float4 o4 = F.ray_o[slot], d4 = F.ray_d[slot];
+            Hit h{PTB_INF, -1, 0.0f, 0.0f, -1};
+            closest_hit<MODE, COUNT>(S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), h, nTri, nAS);
+            F.hit[slot] = make_float4(h.t, __int_as_float(h.tri), h.u, h.v);
+            if (COUNT) {
+                F.cnt_tri[slot] = nTri;
+                F.cnt_as[slot] = nAS;
+            }
+        } else {
+            const uint32_t slot = qs[e - nMain];
+            const float4 o4 = F.sh_o[slot], d4 = F.sh_d[slot];
+            const int lt = __float_as_int(d4.w);
+            Hit h{o4.w, lt, 0.0f, 0.0f, __float_as_int(__ldg(&S.tri[3 * lt]).w)};
+            closest_hit<MODE, false>(S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), h, nTri, nAS);
+            F.sh_hit[slot] = make_float4(h.t, __int_as_float(h.tri), 0.0f, 0.0f);
+        }
+    }
+}
+
+// Russian roulette of the NEXT findIntersection call (scene.cpp:67-72): one draw always;
+// for depth > 2 kill if xi*max(tp) < 0.15 (double compare <=> p < 0.15f), else rescale by
+// (float)(1.0f / ((1 - 0.15) * (double)max)).  Returns true when the ray was killed.
+__device__ __forceinline__ bool roulette(uint32_t &rng, int depth, f3 &tp) {
+    const float xi = fast_random(rng);
+    if (depth > 2) {
+        const float m = max3(tp);
+        if (xi * m < 0.15f) return true;
+        const float f = (float)(1.0f / ((1 - 0.15) * (double)m));
+        tp = tp * f;
+    }
+    return false;
+}
+
+// ---- logic: one step of every queued path between two traversals ---------------------------
+// START = true: first launch of a render call; every owned pixel that still needs samples gets
+// its next primary ray (no hit to process).
+template <int MODE, bool START, bool COUNT>
+__global__ void __launch_bounds__(128) k_logic(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, const uint32_t *__restrict__ qin,
+                                               const uint32_t *__restrict__ nInPtr, uint32_t *__restrict__ qout,
+                                               uint32_t *__restrict__ nOutPtr, uint32_t *__restrict__ qsOut,
+                                               uint32_t *__restrict__ nsOutPtr, unsigned long long *__restrict__ counters) {
+    const uint32_t nIn = START ? F.n_slots : *nInPtr;
+    const uint32_t rounded = (nIn + 31u) & ~31u;
+    unsigned long long cTri = 0, cAS = 0, cPaths = 0, cRef = 0, cNoExt = 0;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < rounded; e += gridDim.x * blockDim.x) {
+        const bool valid = e < nIn;
+        bool cont = false, shadow = false, noExtend = false;
+        uint32_t slot = 0;
+        if (valid) {
+            slot = START ? e : (qin[e] & ~PTB_Q_NOEXTEND);
+            const uint32_t pixel = F.slot_pixel[slot];
+            PathState ps;
+            ps.rng = F.rng[pixel];
+            bool terminated = START;
+            bool fresh = START;
+            if (!START) {
+                const float4 o4 = F.ray_o[slot], d4 = F.ray_d[slot], tp4 = F.tp[slot], l4 = F.light[slot];
+                ps.o = mk3(o4.x, o4.y, o4.z);
+                ps.d = mk3(d4.x, d4.y, d4.z);
+                ps.tp = mk3(tp4.x, tp4.y, tp4.z);
+                ps.depth = __float_as_int(tp4.w);
+                ps.light = mk3(l4.x, l4.y, l4.z);
+                ps.flags = __float_as_uint(l4.w);
+                if (ps.flags & PTB_FLAG_SHADOW) { // finish nextEventEstimation, shader.cpp:102-112 + :233 + :275
+                    const float4 sa = F.sh_a[slot], sb = F.sh_b[slot], sc = F.sh_c[slot], shh = F.sh_hit[slot];
+                    const float distance = sa.w, tAfter = shh.x;
+                    if (!(distance <= tAfter - 0.01f || distance >= tAfter + 0.01f)) {
+                        const float inv_sq = smin(1.0f, (1.0f / (distance * distance)));
+                        const int lm = __float_as_int(__ldg(&A.nrm[3 * __float_as_int(shh.y)]).w);
+                        const MatDev m = A.mats[lm];
+                        f3 lc = ld3(m.gamma);
+                        lc = lc / 3.14f * m.emission * sb.w * inv_sq * sc.x * sc.y * (float)P.n_lights;
+                        ps.light = ps.light + lc * mk3(sa.x, sa.y, sa.z);
+                    }
+                    ps.light = ps.light + mk3(sb.x, sb.y, sb.z);
+                    ps.flags &= ~PTB_FLAG_SHADOW;
+                }
+                const float4 h4 = F.hit[slot];
+                const int tri = __float_as_int(h4.y);
+                const bool done = (ps.flags & PTB_FLAG_DONE) != 0u;
+                if (COUNT && !done) {
+                    cTri += F.cnt_tri[slot];
+                    cAS += F.cnt_as[slot];
+                }
+                if (!done) cRef++;
+                const bool killed = (ps.flags & PTB_FLAG_KILLED) != 0u;
+                if (done) {
+                    terminated = true;
+                } else if (tri < 0) {
+                    // miss: shade is a no-op and the reference re-traces the unchanged ray until
+                    // roulette ends the path; replayed here without traversals.
+                    if (killed) {
+                        ps.depth++;
+                        terminated = true;
+                    } else {
+                        for (;;) {
+                            ps.depth++;
+                            if (P.max_depth > 0 && ps.depth >= P.max_depth) break;
+                            if (roulette(ps.rng, ps.depth, ps.tp)) {
+                                if (MODE == 2 && P.quirks) cRef++; // TWO_PLANE traverses the killed ray once more
+                                ps.depth++;
+                                break;
+                            }
+                            cRef++; // the reference traverses the same ray again
+                        }
+                        terminated = true;
+                    }
+                } else {
+                    ShadowOut sh;
+                    f3 pendingEm;
+                    shade_hit(P, S, A, ps, h4.x, tri, h4.z, h4.w, terminated, sh, pendingEm);
+                    if (sh.emit) {
+                        F.sh_o[slot] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax0);
+                        F.sh_d[slot] = make_float4(sh.d.x, sh.d.y, sh.d.z, __int_as_float(sh.lightTri));
+                        F.sh_a[slot] = make_float4(ps.tp.x, ps.tp.y, ps.tp.z, sh.distance);
+                        F.sh_b[slot] = make_float4(pendingEm.x, pendingEm.y, pendingEm.z, sh.cosSurface);
+                        F.sh_c[slot] = make_float4(sh.cosLight, sh.area, 0.0f, 0.0f);
+                        ps.flags |= PTB_FLAG_SHADOW;
+                        shadow = true;
+                    } else {
+                        ps.light = ps.light + pendingEm;
+                    }
+                    ps.depth++;
+                    if (P.max_depth > 0 && ps.depth >= P.max_depth) terminated = true;
+                    if (killed) terminated = true;
+                }
+                ps.flags &= ~PTB_FLAG_KILLED;
+                if (!terminated) {
+                    if (roulette(ps.rng, ps.depth, ps.tp)) {
+                        if (MODE == 2 && P.quirks) ps.flags |= PTB_FLAG_KILLED; // intersectGrid has no `terminated` check (A.4)
+                        else {
+                            ps.depth++;
+                            terminated = true;
+                        }
+                    }
+                }
+            }
+            if (terminated && !shadow) {
+                if (!fresh) { // tracer.cpp:145-155
+                    const int n = F.samples[pixel] + 1;
+                    F.samples[pixel] = n;
+                    const float cs = (float)n;
+                    const float4 prev = F.image[pixel];
+                    f3 color = ps.light;
+                    color = color + mk3(prev.x, prev.y, prev.z) * cs;
+                    color = color / (cs + 1.0f);
+                    F.image[pixel] = make_float4(color.x, color.y, color.z, 1.0f);
+                    cPaths++;
+                }
+                if (F.samples[pixel] < P.target_samples) { // next sample of this pixel, in place
+                    const int x = (int)(pixel % (uint32_t)P.W), y = (int)(pixel / (uint32_t)P.W);
+                    setup_ray(P, x, y, ps.rng, ps.o, ps.d);
+                    ps.tp = mk3(1.0f, 1.0f, 1.0f);
+                    ps.light = mk3(0.0f, 0.0f, 0.0f);
+                    ps.depth = 0;
+                    ps.flags = 0;
+                    roulette(ps.rng, 0, ps.tp); // findIntersection's draw at depth 0 (never kills)
+                    cont = true;
+                }
+                F.rng[pixel] = ps.rng;
+            } else {
+                // a terminated path with a shadow ray in flight makes one more logic pass (no extend)
+                // so the NEE term lands before accumulation; a live path continues normally
+                cont = true;
+                F.rng[pixel] = ps.rng;
+                if (terminated) {
+                    ps.flags |= PTB_FLAG_DONE;
+                    noExtend = true;
+                    cNoExt++;
+                }
+            }
+            if (cont) {
+                F.ray_o[slot] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
+                F.ray_d[slot] = make_float4(ps.d.x, ps.d.y, ps.d.z, 0.0f);
+                F.tp[slot] = make_float4(ps.tp.x, ps.tp.y, ps.tp.z, __int_as_float(ps.depth));
+                F.light[slot] = make_float4(ps.light.x, ps.light.y, ps.light.z, __uint_as_float(ps.flags));
+            }
+        }
+        queue_push(cont, noExtend ? (slot | PTB_Q_NOEXTEND) : slot, qout, nOutPtr);
+        if (qsOut) queue_push(shadow, slot, qsOut, nsOutPtr);
+    }
+    // block-level counter reduction -> one atomic per counter per warp
+    if (!START) {
+        for (int off = 16; off > 0; off >>= 1) {
+            cTri += __shfl_down_sync(0xffffffffu, cTri, off);
+            cAS += __shfl_down_sync(0xffffffffu, cAS, off);
+            cPaths += __shfl_down_sync(0xffffffffu, cPaths, off);
+            cRef += __shfl_down_sync(0xffffffffu, cRef, off);
+            cNoExt += __shfl_down_sync(0xffffffffu, cNoExt, off);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (cPaths) atomicAdd(&counters[0], cPaths);
+            if (cRef) atomicAdd(&counters[1], cRef);
+            if (cNoExt) atomicAdd(&counters[4], cNoExt);
+            if (COUNT && cTri) atomicAdd(&counters[2], cTri);
+            if (COUNT && cAS) atomicAdd(&counters[3], cAS);
+        }
+    }
+}
+
+
+// ---- traversal-only entry points -------------------------------------------------------------
+// ptb_trace_rays: findIntersection on fresh rays (tmin 0, tmax inf); od6 = n x {o.xyz, d.xyz}.
+// Rays are staged through shared memory so the 24-byte records are read with coalesced loads.
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(128) k_trace(SceneDev S, const float *__restrict__ od6, uint64_t n, float *__restrict__ tOut,
+                                               int *__restrict__ triOut, const uint32_t *__restrict__ idOfTri,
+                                               unsigned long long *__restrict__ counters) {
+    __shared__ float stage[128 * 6];
+    unsigned long long cTri = 0, cAS = 0;
+    const uint64_t rounded = (n + 127ull) & ~127ull;
+    for (uint64_t base = (uint64_t)blockIdx.x * 128ull; base < rounded; base += (uint64_t)gridDim.x * 128ull) {
+        const uint64_t cnt = (n - base < 128ull) ? (n - base) : 128ull;
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < cnt * 6; i += 128) stage[i] = od6[base * 6 + i];
+        __syncthreads();
+        if (threadIdx.x < cnt) {
+            const float *r = &stage[threadIdx.x * 6];
+            Hit h{PTB_INF, -1, 0.0f, 0.0f, -1};
+            uint32_t nTri = 0, nAS = 0;
+            closest_hit<MODE, COUNT>(S, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), h, nTri, nAS);
+            tOut[base + threadIdx.x] = h.t;
+            triOut[base + threadIdx.x] = h.tri >= 0 ? (int)idOfTri[h.tri] : -1;
+            cTri += nTri;
+            cAS += nAS;
+        }
+    }
+    if (COUNT) {
+        for (int off = 16; off > 0; off >>= 1) {
+            cTri += __shfl_down_sync(0xffffffffu, cTri, off);
+            cAS += __shfl_down_sync(0xffffffffu, cAS, off);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (cTri) atomicAdd(&counters[2], cTri);
+            if (cAS) atomicAdd(&counters[3], cAS);
+        }
+    }
+}
+
+// ptb_primary_hits: first-sample primary ray of every pixel (seed x<<16|y) + closest hit.
+template <int MODE>
+__global__ void __launch_bounds__(128) k_primary(ParamsDev P, SceneDev S, AttrDev A, float *__restrict__ tOut, int *__restrict__ triOut,
+                                                 int *__restrict__ matOut) {
+    const uint32_t n = (uint32_t)P.W * (uint32_t)P.H;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const int x = (int)(p % (uint32_t)P.W), y = (int)(p / (uint32_t)P.W);
+        uint32_t rng = hash_coords(x, y);
+        f3 o, d;
+        setup_ray(P, x, y, rng, o, d);
+        Hit h{PTB_INF, -1, 0.0f, 0.0f, -1};
+        uint32_t a = 0, b = 0;
+        closest_hit<MODE, false>(S, o, d, h, a, b);
+        if (tOut) tOut[p] = h.t;
+        if (triOut) triOut[p] = h.tri >= 0 ? (int)A.id_of_tri[h.tri] : -1;
+        if (matOut) matOut[p] = h.tri >= 0 ? __float_as_int(__ldg(&A.nrm[3 * h.tri]).w) : -1;
+    }
+}
+
+// initTracer (tracer.cpp:227-244) for a W x H frame
+__global__ void k_reset(float4 *image, int *samples, uint32_t *rng, int W, int H) {
+    const uint32_t n = (uint32_t)W * (uint32_t)H;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        image[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        samples[p] = 0;
+        rng[p] = hash_coords((int)(p % (uint32_t)W), (int)(p / (uint32_t)W));
+    }
+}
+
+// display transform, window.cpp:507-531: Reinhard, pow(c, 0.4545f), clamp, (u8)(c*255)
+__global__ void k_tonemap(const float4 *__restrict__ image, uchar4 *__restrict__ out, uint32_t n, int tone) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const float4 c4 = image[p];
+        float c[3] = {c4.x, c4.y, c4.z};
+        unsigned char b[3];
+        for (int k = 0; k < 3; ++k) {
+            float v = c[k];
+            if (tone) {
+                v = v / (1.0f + v);
+                v = powf(v, 0.4545f);
+            }
+            v = fminf(v, 1.0f);
+            b[k] = (unsigned char)(v * 255);
+        }
+        out[p] = make_uchar4(b[0], b[1], b[2], 255);
+    }
+}
+
+} // namespace ptb

@@ -1,0 +1,127 @@
+/* ptb.h — C ABI of libptb.so, the B200 (sm_100a) implementation of the thesis path tracer's
+ * hot path: wavefront ray generation -> acceleration-structure traversal (BVH, Subgrid /
+ * "2Plane", Subbeams, brute force) -> Moeller-Trumbore -> bounce/shade -> accumulation.
+ *
+ * The reference has no FFI; this path sits behind plain C++ free functions over globals.  Each
+ * entry point below names the reference function(s) it stands in for (paths relative to the
+ * reference repository).  A C++ facade with the reference's own signatures (tracer.h, scene.h,
+ * bvh.h, lightFieldGrid.h, lightFieldGridSubBeams.h, common.h, shader.h) that forwards to this
+ * ABI is in bachelor-thesis-pathtracer_b200/host/; INTEGRATION.md shows how a maintainer links it.
+ *
+ * Conventions: every function returns 0 on success or a negative ptb_status; the message of the
+ * last failure of a context is available from ptb_last_error().  All pointers are plain host
+ * pointers to POD arrays unless the name says `_device`; upload_* copy, so the caller may free
+ * its arrays on return.  A context is single-owner: calls on one context must not overlap.
+ * There is no CPU fallback: without a CUDA device ptb_create fails.
+ */
+#ifndef PTB_H
+#define PTB_H
+#include <stdint.h>
+#include "ptbs_format.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ptb_ctx ptb_ctx;
+
+typedef enum ptb_status {
+    PTB_OK = 0,
+    PTB_ERR_INVALID = -1, /* bad argument / call order */
+    PTB_ERR_CUDA = -2,    /* CUDA runtime error (sticky: the context is poisoned) */
+    PTB_ERR_IO = -3,
+    PTB_ERR_NOT_BUILT = -4 /* the structure the mode needs has not been built / uploaded */
+} ptb_status;
+
+/* src/common.h:13  enum IntersectMode{ALL, BVH, TWO_PLANE, SUB_BEAMS} */
+typedef enum ptb_mode { PTB_MODE_ALL = 0, PTB_MODE_BVH = 1, PTB_MODE_TWO_PLANE = 2, PTB_MODE_SUB_BEAMS = 3 } ptb_mode;
+
+/* src/types/camera.h:5-18 — what createCameraRay (camera.cpp:47-66) reads */
+typedef struct ptb_camera {
+    float origin[3];
+    float forward[3]; /* any length; orthonormalised like cameraSetForward (camera.cpp:25-32) */
+    float focus;
+    float dof;
+    float fov_degrees; /* 70 in every scene file; fovScale = tanf((fov*3.14f/180)/2) (camera.cpp:16,43-45) */
+} ptb_camera;
+
+/* The mutable globals the reference reads per ray, passed once per launch instead:
+ * WIDTH/HEIGHT (tracer.cpp:22-23), getIntersectMode (common.cpp:12), getNEE / getPrimaryOnly
+ * (shader.cpp:17-18), getDebugView/ShowTris/Scale (tracer.cpp:35-37). */
+typedef struct ptb_params {
+    int32_t width, height;
+    int32_t mode;             /* ptb_mode */
+    int32_t nee;              /* shader.cpp:17 (the --testing protocol turns it off, main.cpp:101) */
+    int32_t primary_only;     /* shader.cpp:245-248 */
+    int32_t max_depth;        /* 0 = unbounded like the reference; N = terminate when depth >= N after depth++ */
+    int32_t reference_quirks; /* 1: per-mode behaviour of roulette-killed rays */
+    int32_t debug_view;       /* tracer.cpp:136-142: 0 off, 1 AS-test heat map, 2 triangle-test heat map */
+    int32_t debug_scale;
+    /* multi-GPU pixel partition: tile (tx,ty) of tile_w x tile_h pixels belongs to rank
+     * (ty*tiles_x + tx) % world.  world = 1 -> the whole frame. */
+    int32_t rank, world, tile_w, tile_h;
+    int32_t count_tests;      /* 1: accumulate the reference's two counters (tracer.cpp:131-132) */
+} ptb_params;
+
+/* counters, ptb_read_counters */
+enum {
+    PTB_CNT_RAYS = 0,        /* traversals executed on the GPU (primary + bounce + shadow) */
+    PTB_CNT_PATHS = 1,       /* completed paths (samples accumulated) */
+    PTB_CNT_TRI_TESTS = 2,   /* getIntersectionCount (tracer.cpp:60-64); needs count_tests */
+    PTB_CNT_AS_TESTS = 3,    /* getStructureIntersectionCount (tracer.cpp:66-70); needs count_tests */
+    PTB_CNT_SHADOW_RAYS = 4,
+    PTB_CNT_ITERATIONS = 5,  /* wavefront iterations launched */
+    PTB_CNT_KERNELS = 6,     /* kernels launched by this context since ptb_reset */
+    PTB_CNT_REF_RAYS = 7,    /* what the reference would have traversed (incl. re-traced misses, A.3) */
+    PTB_CNT__N = 8
+};
+
+/* ---- lifetime ---------------------------------------------------------------------------- */
+int ptb_create(int device, ptb_ctx **out);
+void ptb_destroy(ptb_ctx *ctx);                 /* destroyTracer, tracer.cpp:245-251 */
+const char *ptb_last_error(const ptb_ctx *ctx); /* never NULL; ctx may be NULL (creation errors) */
+
+/* ---- scene: what initScene leaves in getTris()/getObjects()/getMaterials() (scene.cpp:97-131) */
+int ptb_upload_triangles(ptb_ctx *ctx, const float *pos9, const float *nrm9, const float *uv6, const int32_t *mat, uint64_t n);
+int ptb_upload_objects(ptb_ctx *ctx, const ptbs_object *objects, uint32_t n);       /* also derives the light list, scene.cpp:138-148 */
+int ptb_upload_materials(ptb_ctx *ctx, const ptbs_material *materials, uint32_t n); /* may be called again (UI edits + reset) */
+int ptb_load_ptbs(ptb_ctx *ctx, const char *path); /* the three uploads + camera from one .ptbs container */
+int ptb_set_camera(ptb_ctx *ctx, const ptb_camera *cam); /* cameraSetForward + origin/dof/focus, scene.cpp:127-130 */
+
+/* ---- acceleration structures ---------------------------------------------------------------
+ * Builders run on the host inside the library (construction is outside the timed path in the
+ * reference too, main.cpp:97 vs :116) and upload flattened device layouts. */
+int ptb_build_bvh(ptb_ctx *ctx);                                        /* constructBVH, bvh.h:33 (scene.cpp:113-120) */
+int ptb_build_subgrid(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m); /* setGridSettings + constructGrid, lightFieldGrid.h:24,26 */
+int ptb_build_subbeams(ptb_ctx *ctx, uint32_t gs, uint32_t m);          /* setGridBeamsSettings + buildGridsWithSubBeams, lightFieldGridSubBeams.h:28-29 */
+uint64_t ptb_structure_bytes(const ptb_ctx *ctx, int mode);             /* getMemoryBVH / getMemory2Plane / getMemoryGridBeams */
+
+/* ---- rendering ------------------------------------------------------------------------------ */
+int ptb_set_params(ptb_ctx *ctx, const ptb_params *p); /* setWindowSize + setIntersectMode + getNEE() ... */
+int ptb_reset(ptb_ctx *ctx);                           /* initTracer, tracer.cpp:227-244: zero image/samples, reseed rng x<<16|y */
+int ptb_render(ptb_ctx *ctx, int add_samples);         /* trace(true) with MAX_SAMPLE_COUNT += add_samples, tracer.cpp:164-185; synchronous */
+int ptb_render_async(ptb_ctx *ctx, int add_samples);   /* same, returns after enqueueing what can be enqueued; pair with ptb_sync */
+int ptb_sync(ptb_ctx *ctx);
+
+/* closest hit of the first-sample primary rays of every pixel (setupRay + findIntersection,
+ * tracer.cpp:72-88,129); does not touch the frame state.  Any out pointer may be NULL. */
+int ptb_primary_hits(ptb_ctx *ctx, float *t, int32_t *tri, int32_t *mat);
+
+/* closest hit for caller-supplied rays (findIntersection on a fresh ray: tmin 0, tmax inf).
+ * od6 = n x {origin.xyz, direction.xyz}.  Host-buffer variant copies in and out. */
+int ptb_trace_rays(ptb_ctx *ctx, const float *od6, uint64_t n, int mode, float *t, int32_t *tri);
+int ptb_trace_rays_device(ptb_ctx *ctx, const float *od6_device, uint64_t n, int mode, float *t_device, int32_t *tri_device);
+
+/* ---- read-back ------------------------------------------------------------------------------ */
+int ptb_read_image(ptb_ctx *ctx, float *rgba);                       /* tracerGetPixel for every pixel, row-major y*W+x, alpha 1 */
+int ptb_read_state(ptb_ctx *ctx, int32_t *samples, uint32_t *rng);   /* samples[][] / randomStates[][] (tracer.cpp:25-26), y*W+x */
+int ptb_write_state(ptb_ctx *ctx, const float *rgba, const int32_t *samples, const uint32_t *rng); /* resume a dumped render */
+int ptb_read_rgba8(ptb_ctx *ctx, uint8_t *rgba8, int tone_mapping);  /* display transform, window.cpp:507-531 (bytes R,G,B,255) */
+int ptb_read_counters(ptb_ctx *ctx, uint64_t out[PTB_CNT__N]);
+void *ptb_image_device_ptr(ptb_ctx *ctx);                            /* float4[W*H] in HBM, for an NCCL reduce by the caller */
+double ptb_last_render_ms(const ptb_ctx *ctx);                       /* device time of the last ptb_render (CUDA events) */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB_H */
