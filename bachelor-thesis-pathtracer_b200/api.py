@@ -104,6 +104,7 @@ class PathTracer:
         if rc != 0:
             raise PtbError(f"ptb_create: {self.L.ptb_last_error(None).decode()} (rc {rc})")
         self.h = h
+        self.device = device
         self.params = Params(reference_quirks=1, world=1, tile_w=32, tile_h=8, mode=MODE_BVH)
 
     def _ck(self, rc, what):
