@@ -21,7 +21,7 @@ SYMBOLS = (
     "ptb_load_ptbs", "ptb_set_camera", "ptb_build_bvh", "ptb_build_subgrid", "ptb_build_subbeams", "ptb_structure_bytes",
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
-    "ptb_image_device_ptr", "ptb_last_render_ms",
+    "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream",
 )
 
 
@@ -85,6 +85,10 @@ def load_library():
     L.ptb_image_device_ptr.restype = vp
     L.ptb_last_render_ms.argtypes = [vp]
     L.ptb_last_render_ms.restype = ctypes.c_double
+    L.ptb_stream.argtypes = [vp]
+    L.ptb_stream.restype = vp
+    L.ptb_set_profiling.argtypes = [vp, ci]
+    L.ptb_read_stage_ms.argtypes = [vp, vp, vp]
     _lib = L
     return L
 
@@ -225,6 +229,19 @@ class PathTracer:
         c = np.zeros(8, np.uint64)
         self._ck(self.L.ptb_read_counters(self.h, _ptr(c)), "ptb_read_counters")
         return dict(zip(COUNTER_NAMES, (int(v) for v in c)))
+
+    def stream_handle(self):
+        return int(self.L.ptb_stream(self.h) or 0)
+
+    def set_profiling(self, on=True):
+        self._ck(self.L.ptb_set_profiling(self.h, int(on)), "ptb_set_profiling")
+
+    def stage_ms(self):
+        """{'extend_ms', 'logic_ms', 'extend_launches', 'logic_launches'} since reset (needs set_profiling)."""
+        ms = np.zeros(2, np.float64)
+        n = np.zeros(2, np.uint64)
+        self._ck(self.L.ptb_read_stage_ms(self.h, _ptr(ms), _ptr(n)), "ptb_read_stage_ms")
+        return {"extend_ms": float(ms[0]), "logic_ms": float(ms[1]), "extend_launches": int(n[0]), "logic_launches": int(n[1])}
 
     def image_device_ptr(self):
         return int(self.L.ptb_image_device_ptr(self.h) or 0)

@@ -78,6 +78,12 @@ struct ptb_ctx {
     uint64_t counters[PTB_CNT__N] = {0};
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     double lastMs = 0.0;
+    // per-stage device time (ptb_set_profiling): CUDA events around every k_extend / k_logic launch,
+    // harvested at the scheduler's own batch syncs
+    bool profile = false;
+    std::vector<cudaEvent_t> evPool; // 3 per iteration of a batch
+    double stageMs[2] = {0.0, 0.0};  // extend, logic (since reset)
+    uint64_t stageLaunches[2] = {0, 0};
     bool frameDirty = true; // params changed: (re)allocate the frame on next reset
 
     // scratch for ptb_trace_rays / primary hits
@@ -243,6 +249,7 @@ extern "C" void ptb_destroy(ptb_ctx *c) {
     if (c->hShCnt) cudaFreeHost(c->hShCnt);
     if (c->evStart) cudaEventDestroy(c->evStart);
     if (c->evStop) cudaEventDestroy(c->evStop);
+    for (auto &e : c->evPool) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -507,6 +514,8 @@ extern "C" int ptb_reset(ptb_ctx *c) {
     CK(cudaMemsetAsync(c->dCounters, 0, 8 * sizeof(unsigned long long), c->stream));
     CK(cudaStreamSynchronize(c->stream));
     c->targetSamples = 0;
+    c->stageMs[0] = c->stageMs[1] = 0.0;
+    c->stageLaunches[0] = c->stageLaunches[1] = 0;
     c->queueEntries = 0;
     memset(c->counters, 0, sizeof c->counters);
     c->counters[PTB_CNT_KERNELS] = 1;
@@ -526,15 +535,18 @@ static int check_mode_ready(ptb_ctx *c, int mode) {
 namespace {
 
 template <int MODE, bool COUNT>
-void launch_iteration(ptb_ctx *c, const ParamsDev &P, uint32_t it, bool nee) {
+void launch_iteration(ptb_ctx *c, const ParamsDev &P, uint32_t it, bool nee, int evSlot) {
     // iteration `it`: extend rays of queue[it&1] (sizes dCnt[it], dShCnt[it]), then logic -> queue[(it+1)&1]
     const int g = grid_for(c);
+    if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot], c->stream);
     k_extend<MODE, COUNT><<<g, kThreads, 0, c->stream>>>(c->S, c->F, c->dQueue[it & 1], c->dShadowQ, c->dCnt + it,
                                                          nee ? c->dShCnt + it : nullptr);
+    if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot + 1], c->stream);
     k_logic<MODE, false, COUNT><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, c->dQueue[it & 1], c->dCnt + it,
                                                                c->dQueue[(it + 1) & 1], c->dCnt + it + 1,
                                                                nee ? c->dShadowQ : nullptr, nee ? c->dShCnt + it + 1 : nullptr,
                                                                c->dCounters);
+    if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot + 2], c->stream);
 }
 
 template <int MODE, bool COUNT>
@@ -569,11 +581,21 @@ int render_mode(ptb_ctx *c, int add) {
         bool done = false;
         uint32_t checked = it;
         while (!done && it + (uint32_t)batch + 2 < kRing) {
-            for (int b = 0; b < batch; ++b, ++it) launch_iteration<MODE, COUNT>(c, P, it, nee);
+            for (int b = 0; b < batch; ++b, ++it) launch_iteration<MODE, COUNT>(c, P, it, nee, c->profile ? b : -1);
             kernels += 2ull * batch;
             CK(cudaMemcpyAsync(c->hCnt + checked, c->dCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
             if (nee) CK(cudaMemcpyAsync(c->hShCnt + checked, c->dShCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
             CK(cudaStreamSynchronize(c->stream));
+            if (c->profile)
+                for (int b = 0; b < batch; ++b) {
+                    float e = 0.0f, l = 0.0f;
+                    cudaEventElapsedTime(&e, c->evPool[3 * b], c->evPool[3 * b + 1]);
+                    cudaEventElapsedTime(&l, c->evPool[3 * b + 1], c->evPool[3 * b + 2]);
+                    c->stageMs[0] += e;
+                    c->stageMs[1] += l;
+                    c->stageLaunches[0]++;
+                    c->stageLaunches[1]++;
+                }
             for (uint32_t k = checked; k < it; ++k) {
                 rays += c->hCnt[k];
                 if (nee) shadowRays += c->hShCnt[k];
@@ -644,6 +666,28 @@ extern "C" int ptb_sync(ptb_ctx *c) {
     return PTB_OK;
 }
 extern "C" double ptb_last_render_ms(const ptb_ctx *c) { return c ? c->lastMs : 0.0; }
+
+extern "C" void *ptb_stream(ptb_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+extern "C" int ptb_set_profiling(ptb_ctx *c, int on) {
+    GUARD(c);
+    if (on && c->evPool.empty()) {
+        c->evPool.resize(3 * 64);
+        for (auto &e : c->evPool) CK(cudaEventCreate(&e));
+    }
+    c->profile = on != 0;
+    return PTB_OK;
+}
+
+extern "C" int ptb_read_stage_ms(ptb_ctx *c, double ms[2], uint64_t launches[2]) {
+    GUARD(c);
+    if (!ms || !launches) return fail(c, PTB_ERR_INVALID, "null");
+    for (int k = 0; k < 2; ++k) {
+        ms[k] = c->stageMs[k];
+        launches[k] = c->stageLaunches[k];
+    }
+    return PTB_OK;
+}
 
 // =============================================================================================
 // traversal-only entry points

@@ -1,0 +1,220 @@
+"""Scene containers and the synthetic workloads of BASELINE.json (host side, numpy).
+
+* read_ptbs / write_ptbs: the flat `.ptbs` container of include/ptbs_format.h — what the
+  reference holds in memory after initScene (src/scene/scene.cpp:97-131).
+* lucy_standin: BASELINE configs 3/4.  showcase/objects/lucy.obj is not shipped with the reference
+  (.MISSING_LARGE_BLOBS), so the statue is synthesised: an octahedron sphere subdivided 8 times
+  (8 * 4^8 = 524,288 faces), stretched to statue proportions and displaced by seeded fractal
+  noise (seed 0x1ACE), standing in the Cornell room with lucy.scene's material overrides and
+  camera (showcase/scenes/lucy.scene:1-30).  SURVEY.md §8d, config 3.
+* triangle_soup / soup_rays: BASELINE config 5: N triangles with constant expected
+  occupancy and 2^k incoherent rays.
+Everything is deterministic (fixed seeds), so the CPU reference and the GPU see identical bytes.
+"""
+import struct
+
+import numpy as np
+
+PTBS_MAGIC = 0x53425450
+MAX_OBJ_MATS = 28
+_OBJ = struct.Struct("<iifI28I64s")
+_MAT = struct.Struct("<10f64s")
+_HDR = struct.Struct("<8I8f")
+
+
+def _name(b):
+    return b.split(b"\0")[0].decode()
+
+
+def read_ptbs(path):
+    b = open(path, "rb").read()
+    h = _HDR.unpack_from(b, 0)
+    if h[0] != PTBS_MAGIC or h[1] != 1:
+        raise ValueError("not a .ptbs v1 container")
+    n, no, nm = h[2], h[3], h[4]
+    off = _HDR.size
+    pos = np.frombuffer(b, np.float32, n * 9, off).reshape(n, 9).copy(); off += n * 36
+    nrm = np.frombuffer(b, np.float32, n * 9, off).reshape(n, 9).copy(); off += n * 36
+    uv = np.frombuffer(b, np.float32, n * 6, off).reshape(n, 6).copy(); off += n * 24
+    mat = np.frombuffer(b, np.int32, n, off).copy(); off += n * 4
+    objects = []
+    for _ in range(no):
+        f = _OBJ.unpack_from(b, off); off += _OBJ.size
+        objects.append({"start": f[0], "end": f[1], "area": f[2], "materials": list(f[4:4 + f[3]]), "name": _name(f[32])})
+    materials = []
+    for _ in range(nm):
+        f = _MAT.unpack_from(b, off); off += _MAT.size
+        materials.append({"albedo": list(f[0:3]), "ior1": f[3], "ior2": f[4], "emission": f[5], "roughness": f[6],
+                          "weights": list(f[7:10]), "name": _name(f[10])})
+    cam = {"pos": list(h[8:11]), "forward": list(h[11:14]), "focus": h[14], "dof": h[15]}
+    return {"pos": pos, "nrm": nrm, "uv": uv, "mat": mat, "objects": objects, "materials": materials, "camera": cam}
+
+
+def pack_objects(objects):
+    out = bytearray()
+    for o in objects:
+        m = list(o["materials"])[:MAX_OBJ_MATS]
+        out += _OBJ.pack(int(o["start"]), int(o["end"]), float(o["area"]), len(m), *(m + [0] * (MAX_OBJ_MATS - len(m))),
+                         o["name"].encode()[:63])
+    return bytes(out)
+
+
+def pack_materials(materials):
+    out = bytearray()
+    for m in materials:
+        out += _MAT.pack(*[float(x) for x in m["albedo"]], float(m["ior1"]), float(m["ior2"]), float(m["emission"]),
+                         float(m["roughness"]), *[float(x) for x in m["weights"]], m["name"].encode()[:63])
+    return bytes(out)
+
+
+def write_ptbs(path, scene):
+    n = scene["pos"].shape[0]
+    c = scene["camera"]
+    with open(path, "wb") as f:
+        f.write(_HDR.pack(PTBS_MAGIC, 1, n, len(scene["objects"]), len(scene["materials"]), 0, 0, 0,
+                          *[float(x) for x in c["pos"]], *[float(x) for x in c["forward"]], float(c["focus"]), float(c["dof"])))
+        f.write(np.ascontiguousarray(scene["pos"], np.float32).tobytes())
+        f.write(np.ascontiguousarray(scene["nrm"], np.float32).tobytes())
+        f.write(np.ascontiguousarray(scene["uv"], np.float32).tobytes())
+        f.write(np.ascontiguousarray(scene["mat"], np.int32).tobytes())
+        f.write(pack_objects(scene["objects"]))
+        f.write(pack_materials(scene["materials"]))
+
+
+def upload_scene(pt, scene):
+    """The three uploads + camera of a scene dict through the C ABI."""
+    pt.upload_triangles(scene["pos"], scene["nrm"], scene["uv"], scene["mat"])
+    pt.upload_materials(pack_materials(scene["materials"]), len(scene["materials"]))
+    pt.upload_objects(pack_objects(scene["objects"]), len(scene["objects"]))
+    c = scene["camera"]
+    pt.set_camera(c["pos"], c["forward"], c["focus"], c["dof"])
+
+
+def _tri_area(pos):
+    p = pos.reshape(-1, 3, 3).astype(np.float64)
+    return 0.5 * np.linalg.norm(np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]), axis=1)
+
+
+def _flat_normals(pos):
+    p = pos.reshape(-1, 3, 3).astype(np.float64)
+    n = np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0])
+    l = np.linalg.norm(n, axis=1, keepdims=True)
+    n = np.where(l > 0, n / np.maximum(l, 1e-300), np.array([0.0, 1.0, 0.0]))
+    return np.repeat(n[:, None, :], 3, axis=1).reshape(-1, 9).astype(np.float32)
+
+
+def _octa_sphere(level):
+    """Unit octahedron sphere, every face subdivided into (2^level)^2 triangles -> [8*4^level, 3, 3] float64.
+    Lattice points are exact multiples of 1/N, so vertices shared by faces are bit-identical."""
+    N = 1 << level
+    i, j = np.meshgrid(np.arange(N + 1), np.arange(N + 1), indexing="ij")
+    # upward triangles (i,j),(i+1,j),(i,j+1) for i+j<N ; downward (i+1,j),(i+1,j+1),(i,j+1) for i+j<N-1
+    iu, ju = np.nonzero((i + j < N) & (i < N) & (j < N))
+    idn, jdn = np.nonzero((i + j < N - 1) & (i < N) & (j < N))
+    a = np.concatenate([np.stack([iu, ju], 1), np.stack([idn + 1, jdn], 1)])
+    b = np.concatenate([np.stack([iu + 1, ju], 1), np.stack([idn + 1, jdn + 1], 1)])
+    c = np.concatenate([np.stack([iu, ju + 1], 1), np.stack([idn, jdn + 1], 1)])
+    tri_ij = np.stack([a, b, c], 1).astype(np.float64)  # [N^2, 3, 2]
+    faces = []
+    for sx in (1.0, -1.0):
+        for sy in (1.0, -1.0):
+            for sz in (1.0, -1.0):
+                A, B, C = np.array([sx, 0, 0]), np.array([0, sy, 0]), np.array([0, 0, sz])
+                u, v = tri_ij[..., 0] / N, tri_ij[..., 1] / N
+                w = 1.0 - u - v
+                p = u[..., None] * A + v[..., None] * B + w[..., None] * C
+                if sx * sy * sz < 0:  # keep outward winding
+                    p = p[:, ::-1, :]
+                faces.append(p)
+    p = np.concatenate(faces)
+    return p / np.linalg.norm(p, axis=-1, keepdims=True)
+
+
+def _fractal(p, seed, octaves=6):
+    """Seeded sum-of-sines fractal on unit directions p[..., 3] (float64), range about [-1, 1]."""
+    rng = np.random.default_rng(seed)
+    out = np.zeros(p.shape[:-1])
+    amp, freq, tot = 1.0, 2.0, 0.0
+    for _ in range(octaves):
+        for _ in range(3):
+            d = rng.normal(size=3)
+            d /= np.linalg.norm(d)
+            out += amp * np.sin(freq * (p @ d) + rng.uniform(0, 2 * np.pi))
+        tot += 3 * amp
+        amp *= 0.5
+        freq *= 2.0
+    return out / tot
+
+
+def statue_mesh(level=8, seed=0x1ACE, radius=(105.0, 225.0, 105.0), base=(0.0, -250.0, 0.0)):
+    """[n,9] float32 positions of the stand-in statue standing on the Cornell floor."""
+    s = _octa_sphere(level)
+    r = 1.0 + 0.22 * _fractal(s, seed)
+    # a waist/shoulder profile along y so the silhouette is not a plain ellipsoid
+    prof = 0.75 + 0.25 * np.cos(3.0 * s[..., 1] + 0.6)
+    p = s * r[..., None]
+    p[..., 0] *= radius[0] * prof
+    p[..., 2] *= radius[2] * prof
+    p[..., 1] = p[..., 1] * radius[1] + radius[1] * 1.0
+    p += np.array(base)
+    return p.reshape(-1, 9).astype(np.float32)
+
+
+def lucy_standin(room, level=8, seed=0x1ACE):
+    """Scene dict: the Cornell room of `room` (a read_ptbs dict of cornel.ptbs) with its sphere replaced by
+    the synthetic statue, lucy.scene's material overrides and camera."""
+    keep = [o for o in room["objects"] if o["name"] != "Sphere"]
+    pos, nrm, uv, mat, objects = [], [], [], [], []
+    cur = 0
+    for o in keep:
+        n = o["end"] - o["start"]
+        pos.append(room["pos"][o["start"]:o["end"]]); nrm.append(room["nrm"][o["start"]:o["end"]])
+        uv.append(room["uv"][o["start"]:o["end"]]); mat.append(room["mat"][o["start"]:o["end"]])
+        objects.append(dict(o, start=cur, end=cur + n))
+        cur += n
+    materials = [dict(m) for m in room["materials"]]
+    # lucy.scene [Materials]: a named entry replaces the whole pbr + weights (scene.cpp:103-110;
+    # unspecified refractive indices default to 1.0/1.5, shader.h:20-28)
+    for name, w in (("Material.001", [0, 1, 0]), ("Material.002", [0, 1, 0])):
+        for m in materials:
+            if m["name"] == name:
+                m.update(albedo=[1.0, 1.0, 1.0], emission=0.0, roughness=0.0, weights=w, ior1=1.0, ior2=1.5)
+    materials.append({"albedo": [1.0, 0.4, 0.9], "ior1": 1.0, "ior2": 1.5, "emission": 0.0, "roughness": 0.1,
+                      "weights": [1, 0, 0], "name": "Material.008"})
+    sp = statue_mesh(level, seed)
+    n = sp.shape[0]
+    pos.append(sp); nrm.append(_flat_normals(sp)); uv.append(np.zeros((n, 6), np.float32))
+    mat.append(np.full(n, len(materials) - 1, np.int32))
+    objects.append({"start": cur, "end": cur + n, "area": float(_tri_area(sp).sum()), "materials": [len(materials) - 1],
+                    "name": "LucyStandIn"})
+    return {"pos": np.concatenate(pos), "nrm": np.concatenate(nrm), "uv": np.concatenate(uv), "mat": np.concatenate(mat),
+            "objects": objects, "materials": materials,
+            "camera": {"pos": [-250.0, 0.0, -180.0], "forward": [0.9, 0.0, 0.34], "focus": 1.0, "dof": 0.0}}
+
+
+def triangle_soup(n, seed=None):
+    """Config 5: triangle i has its centre uniform in [-100,100]^3 and vertices = centre + uniform[-s,s]^3 with
+    s = 100 * n^(-1/3) (constant expected occupancy).  One object, one lambert material, no light."""
+    seed = 7 + int(round(np.log10(n))) if seed is None else seed
+    rng = np.random.Generator(np.random.MT19937(seed))
+    s = 100.0 * float(n) ** (-1.0 / 3.0)
+    c = rng.uniform(-100.0, 100.0, size=(n, 1, 3)).astype(np.float32)
+    v = (c + rng.uniform(-s, s, size=(n, 3, 3)).astype(np.float32)).astype(np.float32)
+    pos = v.reshape(n, 9)
+    mats = [{"albedo": [0.8, 0.8, 0.8], "ior1": 1.0, "ior2": 1.5, "emission": 0.0, "roughness": 0.5, "weights": [1, 0, 0],
+             "name": "Soup"}]
+    return {"pos": pos, "nrm": _flat_normals(pos), "uv": np.zeros((n, 6), np.float32), "mat": np.zeros(n, np.int32),
+            "objects": [{"start": 0, "end": n, "area": float(_tri_area(pos).sum()), "materials": [0], "name": "Soup"}],
+            "materials": mats, "camera": {"pos": [0.0, 0.0, -400.0], "forward": [0.0, 0.0, 1.0], "focus": 1.0, "dof": 0.0}}
+
+
+def soup_rays(n, seed=99):
+    """Config 5 rays: origin uniform on the sphere r = 250, direction towards a uniform point of [-100,100]^3
+    (incoherent), normalised in float32.  [n, 6] float32."""
+    rng = np.random.Generator(np.random.MT19937(seed))
+    o = rng.normal(size=(n, 3))
+    o = (250.0 * o / np.linalg.norm(o, axis=1, keepdims=True)).astype(np.float32)
+    tgt = rng.uniform(-100.0, 100.0, size=(n, 3)).astype(np.float32)
+    d = (tgt - o).astype(np.float32)
+    d = (d / np.sqrt((d * d).sum(1, keepdims=True), dtype=np.float32)).astype(np.float32)
+    return np.concatenate([o, d], 1).astype(np.float32)

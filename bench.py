@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""bench.py — the hot path of the thesis path tracer on N B200s, one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cornell|lucy]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[1], the single-GPU configuration the metric is quoted on):
+Cornell box (showcase/scenes/cornel.scene), BVH, 1024x1024, 64 spp, primary + 4 bounces
+(max_depth 5), NEE off like the reference's own --testing protocol (src/main.cpp:101).
+A "step" is one full 64-spp frame: initTracer (ptb_reset) + trace (ptb_render).  With N > 1 the
+same frame is tile-sharded over the ranks (strong scaling: total work fixed) and the radiance is
+sum-reduced to rank 0 over NCCL inside the timed region.
+
+  value      Mrays/s, rays = traversals executed (primary + bounce; the reference's re-traced
+             misses are NOT counted: SURVEY.md §8d "unique rays"), state resident in HBM, device time
+             (CUDA events on the context's stream, max over ranks)
+  e2e        same metric through the C ABI with host buffers: every step uploads the material table
+             and camera (what the reference's UI does before reset()), renders, and reads the fp32
+             frame back to host memory; wall clock around synchronous calls, max over ranks
+  roofline   dominant kernel k_extend<BVH>: algorithmic bytes (48 B ray+hit,
+             32 B per box test, 36 B per triangle test, from the instrumented counters) / its
+             CUDA-event time inside the timed region, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline / --impl reference
+             the UNMODIFIED reference compiled into oracle/_ref/ptref (trace(true), its 16
+             std::threads) on the host cores, bounded sample = same frame at fewer spp
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+CORNEL = os.path.join(ROOT, "tests", "golden", "cornel.ptbs")
+METRIC = "Mrays/s (primary+bounce), full path tracing"
+
+WORKLOADS = {
+    # name: (W, H, spp, max_depth, mode, description)
+    "cornell": dict(W=1024, H=1024, spp=64, max_depth=5, mode=1,
+                    name="Cornell box, BVH, 1024x1024, 64 spp, 4 bounces (BASELINE configs[1])"),
+    "lucy": dict(W=1920, H=1080, spp=16, max_depth=9, mode=1,
+                 name="Lucy stand-in (524,310 triangles), BVH, 1920x1080, 16 spp, 8 bounces (configs[3] at 1/16 of the samples)"),
+}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the unmodified reference on the host cores
+# --------------------------------------------------------------------------------------------------
+def scene_file(workload, tmpdir):
+    """Path of the workload's .ptbs (Cornell ships as a fixture; the Lucy stand-in is generated)."""
+    if workload == "cornell":
+        return CORNEL
+    import ptb_b200
+    path = os.path.join(tmpdir, "lucy_standin.ptbs")
+    if not os.path.isfile(path):
+        ptb_b200.scenes.write_ptbs(path, ptb_b200.scenes.lucy_standin(ptb_b200.scenes.read_ptbs(CORNEL)))
+    return path
+
+
+def cpu_reference_run(ptbs, wl, spp):
+    """One bounded sample on the CPU.  Returns (unique rays, seconds, kind, threads).
+    kind "reference": oracle/_ref/ptref = the reference's own sources; timing from an uninstrumented
+    run (--no-count), ray count from a counted run of the same deterministic sample.
+    kind "port": the C++ restatement (oracle/libptoracle.so) when the compiled reference is absent."""
+    import oracle_lib
+    ncpu = os.cpu_count() or 1
+    if oracle_lib.have_ref():
+        args = ["--ptbs", ptbs, "--mode", wl["mode"], "--width", wl["W"], "--height", wl["H"], "--spp", spp, "--max-depth",
+                wl["max_depth"], "--nee", 0]
+        timed = [r for r in oracle_lib.run_ptref(args + ["--no-count", "render", "-"]) if r["cmd"] == "render"][0]
+        counted = [r for r in oracle_lib.run_ptref(args + ["render", "-"]) if r["cmd"] == "render"][0]
+        return counted["rays_unique"], timed["trace_ms"] / 1e3, "reference", min(16, ncpu)
+    o = oracle_lib.Oracle(ptbs)
+    o.build()
+    o.configure(wl["W"], wl["H"], wl["mode"], nee=0, max_depth=wl["max_depth"])
+    t0 = time.perf_counter()
+    _, _, _, st = o.render(spp, threads=ncpu)
+    dt = time.perf_counter() - t0
+    o.close()
+    return st["rays_unique"], dt, "port", ncpu
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    wl = WORKLOADS[args.workload]
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    ptbs = scene_file(args.workload, os.path.join(ROOT, "gpurun_out"))
+    spp = args.ref_spp
+    for _ in range(args.warmup):
+        cpu_reference_run(ptbs, wl, 1)
+    rays = secs = 0.0
+    kind, cores = "port", 1
+    for _ in range(args.steps):
+        r, s, kind, cores = cpu_reference_run(ptbs, wl, spp)
+        rays += r
+        secs += s
+    v = rays / secs / 1e6
+    sample = f"{wl['W']}x{wl['H']} frame at {spp} spp per step (of {wl['spp']}), max_depth {wl['max_depth']}, NEE off"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "sample": sample},
+        "spp_per_s": spp * args.steps / secs,
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample, "host_cpus": os.cpu_count(),
+                         "threads": 16 if kind == "reference" else cores},
+        "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+    return 0
+
+
+# --------------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import ptb_b200
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (libptb has no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    wl = WORKLOADS[args.workload]
+    W, H, spp, mode = wl["W"], wl["H"], wl["spp"], wl["mode"]
+    sc = ptb_b200.scenes
+    scene = sc.read_ptbs(CORNEL)
+    if args.workload == "lucy":
+        scene = sc.lucy_standin(scene)
+    mats_bytes, n_mats = sc.pack_materials(scene["materials"]), len(scene["materials"])
+    cam = scene["camera"]
+
+    pt = ptb_b200.PathTracer(local)
+    sc.upload_scene(pt, scene)
+    t0 = time.perf_counter()
+    pt.build_bvh()
+    build_s = time.perf_counter() - t0
+    base = dict(width=W, height=H, mode=mode, nee=0, max_depth=wl["max_depth"], rank=rank, world=world, tile_w=32, tile_h=8)
+    stream = torch.cuda.ExternalStream(pt.stream_handle(), device=local)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")  # > 126 MB L2
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_frame():
+        if dist is None:
+            return
+        img = ptb_b200.multigpu.device_image_tensor(pt)
+        with torch.cuda.stream(stream):
+            ptb_b200.multigpu.reduce_image(img, dst=0)
+
+    # instrumented pass (outside the timed region): the per-ray visit counts behind the algorithmic bytes
+    pt.set_params(count_tests=1, **base)
+    pt.reset()
+    pt.render(2)
+    c = pt.counters()
+    boxes_per_ray = c["as_tests"] / max(1, c["rays"])
+    tris_per_ray = c["tri_tests"] / max(1, c["rays"])
+    bytes_per_ray = 48.0 + 32.0 * boxes_per_ray + 36.0 * tris_per_ray
+
+    pt.set_params(count_tests=0, **base)
+    pt.set_profiling(True)
+
+    def step():
+        pt.reset()
+        pt.render(spp)
+        reduce_frame()
+
+    for _ in range(args.warmup):
+        step()
+    # ---- value: device time, state resident in HBM --------------------------------------------
+    clocks = ClockSampler(local)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    rays = paths = kernels = 0
+    ext_ms = logic_ms = 0.0
+    ext_launches = 0
+    barrier()
+    clocks.start()
+    for k in range(args.steps):
+        flush.fill_(k & 0xFF)  # L2 flush between timed iterations (torch stream; not inside the event pair)
+        torch.cuda.synchronize()
+        ev[k][0].record(stream)
+        step()
+        ev[k][1].record(stream)
+        cc = pt.counters()
+        st = pt.stage_ms()
+        rays += cc["rays"]; paths += cc["paths"]; kernels += cc["kernels"]
+        ext_ms += st["extend_ms"]; logic_ms += st["logic_ms"]; ext_launches += st["extend_launches"]
+    barrier()
+    clk = clocks.stop()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+
+    # ---- e2e: through the C ABI with host buffers, copies inside the timed region ---------------
+    host_img = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
+    e2e_rays = 0
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        pt.upload_materials(mats_bytes, n_mats)                    # H2D: material table (UI edit + reset flow)
+        pt.set_camera(cam["pos"], cam["forward"], cam["focus"], cam["dof"])
+        pt.set_params(count_tests=0, **base)
+        pt.reset()
+        pt.render(spp)
+        reduce_frame()
+        if rank == 0:
+            pt.L.ptb_read_image(pt.h, host_img.ctypes.data)        # D2H: the fp32 frame
+        e2e_rays += pt.counters()["rays"]
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    h2d = len(mats_bytes) + 36 + 56
+    d2h = W * H * 16
+
+    # ---- aggregate over ranks -------------------------------------------------------------------
+    vals = torch.tensor([float(rays), float(paths), float(kernels), float(e2e_rays)], dtype=torch.float64, device=f"cuda:{local}")
+    tmax = torch.tensor([dev_ms, e2e_s, ext_ms, logic_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(vals, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    rays_all, paths_all, kernels_all, e2e_rays_all = (float(x) for x in vals.tolist())
+    dev_ms_max, e2e_s_max, ext_ms_max, logic_ms_max = (float(x) for x in tmax.tolist())
+
+    result = None
+    if rank == 0:
+        peak, peak_kind = peaks()
+        value = rays_all / (dev_ms_max / 1e3) / 1e6
+        # roofline of the dominant kernel on rank 0's own launches
+        ach = bytes_per_ray * rays / (ext_ms / 1e3) / 1e9 if ext_ms > 0 else None
+        result = {
+            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["name"], "width": W, "height": H, "spp": spp, "max_depth": wl["max_depth"], "nee": 0,
+                       "structure": "BVH2, 64-byte two-box nodes", "triangles": int(scene["pos"].shape[0]),
+                       "parallelism": f"tiles32x8 round-robin over {world} GPU(s), NCCL sum-reduce to rank 0" if world > 1 else "1 GPU",
+                       "l2": "flushed between timed steps (512 MiB fill)", "bvh_build_s": round(build_s, 3)},
+            "spp_per_s": spp * args.steps / (dev_ms_max / 1e3),
+            "mpaths_per_s": paths_all / (dev_ms_max / 1e3) / 1e6,
+            "rays_per_step": rays_all / args.steps,
+            "gpu_launches": int(kernels_all),
+            "clocks": clk,
+            "e2e": {"value": e2e_rays_all / e2e_s_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_s_max / args.steps * 1e3},
+            "roofline": {"bound": "hbm", "kernel": "k_extend<BVH>", "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": (ach / peak) if ach else None, "traffic": None, "peak_source": peak_kind,
+                         "bytes_per_ray": bytes_per_ray, "boxes_per_ray": boxes_per_ray, "tris_per_ray": tris_per_ray,
+                         "avg_launch_ms": ext_ms / max(1, ext_launches), "launches": ext_launches,
+                         "share_of_step": ext_ms / dev_ms if dev_ms > 0 else None,
+                         "logic_share_of_step": logic_ms / dev_ms if dev_ms > 0 else None},
+        }
+    pt.close()
+    if rank == 0 and world == 1 and not args.no_cpu:
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        ptbs = scene_file(args.workload, os.path.join(ROOT, "gpurun_out"))
+        r, s, kind, cores = cpu_reference_run(ptbs, wl, args.cpu_spp)
+        result["cpu_baseline"] = {
+            "value": r / s / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind, "host_cpus": os.cpu_count(),
+            "threads": 16 if kind == "reference" else cores, "seconds": s,
+            "sample": f"same {W}x{H} frame at {args.cpu_spp} spp (of {spp}), max_depth {wl['max_depth']}, NEE off, "
+                      f"{'reference trace(true), 16 std::threads' if kind == 'reference' else 'oracle port'}"}
+    if rank == 0:
+        print(json.dumps(result))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-spp", type=int, default=8, help="spp of the bounded cpu_baseline sample")
+    ap.add_argument("--ref-spp", type=int, default=4, help="spp per step of the --impl reference arm")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (profiling runs only)")
+    args = ap.parse_args()
+    if args.spp > 0:
+        WORKLOADS[args.workload] = dict(WORKLOADS[args.workload], spp=args.spp,
+                                        name=WORKLOADS[args.workload]["name"] + f" [spp overridden to {args.spp}]")
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch under torchrun like the driver does
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
+               "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -120,6 +120,12 @@ int ptb_read_rgba8(ptb_ctx *ctx, uint8_t *rgba8, int tone_mapping);  /* display 
 int ptb_read_counters(ptb_ctx *ctx, uint64_t out[PTB_CNT__N]);
 void *ptb_image_device_ptr(ptb_ctx *ctx);                            /* float4[W*H] in HBM, for an NCCL reduce by the caller */
 double ptb_last_render_ms(const ptb_ctx *ctx);                       /* device time of the last ptb_render (CUDA events) */
+/* per-stage device time, the GPU analogue of the -pg/gprof split the reference offers (Makefile:15-21):
+ * CUDA events on the launching stream around every traversal (extend) and shade/bounce (logic) launch.
+ * ms[0]/launches[0] = extend, [1] = logic, accumulated since ptb_reset. */
+void *ptb_stream(ptb_ctx *ctx); /* the cudaStream_t every launch and copy of this context is ordered on (for caller-side events / NCCL) */
+int ptb_set_profiling(ptb_ctx *ctx, int on);
+int ptb_read_stage_ms(ptb_ctx *ctx, double ms[2], uint64_t launches[2]);
 
 #ifdef __cplusplus
 }
