@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -26,6 +27,8 @@ const uint32_t kRing = 1u << 14; // per-iteration queue counters kept on the dev
 struct ptb_ctx {
     int device = 0;
     int sms = 148;
+    int extendCtas = 12; // resident 128-thread CTAs per SM of the persistent BVH extend (40 registers/thread)
+    int fetchKeep = 20;  // refill a warp's idle lanes when fewer than this many are still walking
     cudaStream_t stream = nullptr;
     std::string err;
     bool poisoned = false;
@@ -71,6 +74,7 @@ struct ptb_ctx {
     uint32_t *dShadowQ = nullptr;
     uint32_t *dCnt = nullptr;   // [kRing] main-queue sizes per iteration
     uint32_t *dShCnt = nullptr; // [kRing] shadow-queue sizes per iteration
+    uint32_t *dCursor = nullptr; // [kRing] work cursor of each iteration's persistent extend (dynamic ray fetch)
     uint32_t *hCnt = nullptr, *hShCnt = nullptr; // pinned mirrors
     unsigned long long *dCounters = nullptr;     // [8] paths, ref rays, tri tests, AS tests, no-extend queue entries
     int targetSamples = 0;
@@ -205,6 +209,7 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     cudaEventCreate(&c->evStop);
     cudaMalloc(&c->dCnt, kRing * sizeof(uint32_t));
     cudaMalloc(&c->dShCnt, kRing * sizeof(uint32_t));
+    cudaMalloc(&c->dCursor, kRing * sizeof(uint32_t));
     cudaMalloc(&c->dCounters, 8 * sizeof(unsigned long long));
     cudaMallocHost(&c->hCnt, kRing * sizeof(uint32_t));
     cudaMallocHost(&c->hShCnt, kRing * sizeof(uint32_t));
@@ -213,6 +218,8 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
         delete c;
         return fail(nullptr, PTB_ERR_CUDA, m);
     }
+    if (const char *e = getenv("PTB_EXTEND_CTAS")) c->extendCtas = std::max(1, std::min(16, atoi(e))); // tuning knobs
+    if (const char *e = getenv("PTB_FETCH_KEEP")) c->fetchKeep = std::max(1, std::min(32, atoi(e)));
     c->cam.fov_degrees = 70.0f;
     c->cam.focus = 1.0f;
     c->cam.forward[2] = 1.0f;
@@ -243,7 +250,7 @@ extern "C" void ptb_destroy(ptb_ctx *c) {
     devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
     devFree(c->dBeam); devFree(c->dBeamIdx);
     for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
-    devFree(c->dCnt); devFree(c->dShCnt); devFree(c->dCounters);
+    devFree(c->dCnt); devFree(c->dShCnt); devFree(c->dCursor); devFree(c->dCounters);
     devFree(c->dScratchF); devFree(c->dScratchI); devFree(c->dRays);
     if (c->hCnt) cudaFreeHost(c->hCnt);
     if (c->hShCnt) cudaFreeHost(c->hShCnt);
@@ -539,8 +546,12 @@ void launch_iteration(ptb_ctx *c, const ParamsDev &P, uint32_t it, bool nee, int
     // iteration `it`: extend rays of queue[it&1] (sizes dCnt[it], dShCnt[it]), then logic -> queue[(it+1)&1]
     const int g = grid_for(c);
     if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot], c->stream);
-    k_extend<MODE, COUNT><<<g, kThreads, 0, c->stream>>>(c->S, c->F, c->dQueue[it & 1], c->dShadowQ, c->dCnt + it,
-                                                         nee ? c->dShCnt + it : nullptr);
+    if (MODE == 1)
+        k_extend_bvh<COUNT><<<c->sms * c->extendCtas, kThreads, 0, c->stream>>>(c->S, c->F, c->dQueue[it & 1], c->dShadowQ, c->dCnt + it,
+                                                                                nee ? c->dShCnt + it : nullptr, c->dCursor + it, c->fetchKeep);
+    else
+        k_extend<MODE, COUNT><<<g, kThreads, 0, c->stream>>>(c->S, c->F, c->dQueue[it & 1], c->dShadowQ, c->dCnt + it,
+                                                             nee ? c->dShCnt + it : nullptr);
     if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot + 1], c->stream);
     k_logic<MODE, false, COUNT><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, c->dQueue[it & 1], c->dCnt + it,
                                                                c->dQueue[(it + 1) & 1], c->dCnt + it + 1,
@@ -563,6 +574,7 @@ int render_mode(ptb_ctx *c, int add) {
     for (;;) {
         // one ring pass: counters [0..kRing) zeroed, slot 1 (or 0) seeded
         CK(cudaMemsetAsync(c->dCnt, 0, kRing * sizeof(uint32_t), c->stream));
+        CK(cudaMemsetAsync(c->dCursor, 0, kRing * sizeof(uint32_t), c->stream));
         if (nee) CK(cudaMemsetAsync(c->dShCnt, 0, kRing * sizeof(uint32_t), c->stream));
         uint32_t it = 0;
         if (first) {

@@ -86,6 +86,15 @@ struct SceneDev {
 // ---- Moeller-Trumbore: src/primitives/triangle.cpp:7-52, positions only --------------------
 // Accept rule: !(t < 1e-5) && !(tmax < t); among bit-equal t the larger reference id wins
 // (the reference lets the later-tested one win; brute-force order == ascending id).
+//
+// The reference divides first (inv = 1/det) and then rejects on u, v.  Most tests fail on u or v,
+// so the sign/magnitude of the un-divided numerators is checked first and the IEEE division is
+// only paid by candidates that can still hit.  The pre-rejects are conservative: they fire only
+// where the exactly rounded u (or v) is certainly outside [0,1]:
+//   du*det < -1e-20  =>  du, det nonzero with opposite signs and |du/det| far above the smallest
+//                        denormal for any |det| < 3e12, so RN(du*RN(1/det)) < 0;
+//   |du| > |det|*(1+1e-6)  =>  RN(du*RN(1/det)) > 1  (two roundings, 2^-23 relative in total).
+// Everything that survives is evaluated in the reference's order, bit for bit.
 template <bool COUNT>
 __device__ __forceinline__ void intersect_tri(const float4 *__restrict__ tri, int idx, f3 o, f3 d, Hit &h, uint32_t &nTri) {
     const float4 a = __ldg(&tri[3 * idx]);
@@ -95,13 +104,18 @@ __device__ __forceinline__ void intersect_tri(const float4 *__restrict__ tri, in
     const f3 v0 = mk3(a.x, a.y, a.z), e1 = mk3(b.x, b.y, b.z), e2 = mk3(c.x, c.y, c.z);
     const f3 p = cross3(d, e2);
     const float det = dot3(e1, p);
-    if (fabsf(det) <= 0.01f) return; // fabs(det) < 0.01 evaluated in double (triangle.cpp:20)
-    const float inv = 1.0f / det;
+    const float adet = fabsf(det);
+    if (adet <= 0.01f) return; // fabs(det) < 0.01 evaluated in double (triangle.cpp:20)
     const f3 tv = o - v0;
-    const float u = dot3(tv, p) * inv;
-    if (0.0f > u || u > 1.0f) return;
+    const float du = dot3(tv, p);
+    if (du * det < -1e-20f || fabsf(du) > adet * 1.000001f) return;
     const f3 q = cross3(tv, e1);
-    const float v = dot3(d, q) * inv;
+    const float dv = dot3(d, q);
+    if (dv * det < -1e-20f || fabsf(dv) > adet * 1.000001f) return;
+    const float inv = 1.0f / det;
+    const float u = du * inv;
+    if (0.0f > u || u > 1.0f) return;
+    const float v = dv * inv;
     if (0.0f > v || u + v > 1.0f) return;
     const float t = dot3(e2, q) * inv;
     if (t < 0.00001f || h.t < t) return;
@@ -124,9 +138,24 @@ __device__ __forceinline__ bool slab(f3 lo, f3 hi, f3 o, f3 inv, float tmax, flo
     tn = t0;
     return t0 <= t1;
 }
+// Same test with FMNMX.  std::min/max (select form) and fminf/fmaxf differ only when an operand
+// is NaN or in the sign of a zero result.  A NaN needs (bound - origin) == 0 times an infinite
+// inv_dir component, so rays whose inv_dir is finite in all three components cannot produce one;
+// the sign of a zero never changes `t0 <= t1`, the child ordering `d1 >= d0` or the pop-time cull.
+__device__ __forceinline__ bool slab_fast(f3 lo, f3 hi, f3 o, f3 inv, float tmax, float &tn) {
+    const float tx1 = (lo.x - o.x) * inv.x, tx2 = (hi.x - o.x) * inv.x;
+    const float ty1 = (lo.y - o.y) * inv.y, ty2 = (hi.y - o.y) * inv.y;
+    const float tz1 = (lo.z - o.z) * inv.z, tz2 = (hi.z - o.z) * inv.z;
+    const float t0 = fmaxf(fmaxf(fmaxf(fminf(tx1, tx2), fminf(ty1, ty2)), fminf(tz1, tz2)), 0.0f);
+    const float t1 = fminf(fminf(fminf(fmaxf(tx1, tx2), fmaxf(ty1, ty2)), fmaxf(tz1, tz2)), tmax);
+    tn = t0;
+    return t0 <= t1;
+}
+__device__ __forceinline__ bool finite3(f3 v) { return fabsf(v.x) < PTB_INF && fabsf(v.y) < PTB_INF && fabsf(v.z) < PTB_INF; }
 
 #define PTB_STACK 64
 #define PTB_GSTACK 160 /* Subgrid: <= 16 children pushed per level */
+#define PTB_REF_DONE ((int)0x80000000) /* never a leaf reference: first < 2^27 - 1 */
 
 // leaf reference: ~((first << 4) | (count - 1)), count <= 16
 __device__ __forceinline__ void leaf_decode(int ref, int &first, int &count) {
@@ -140,51 +169,88 @@ __device__ __forceinline__ void leaf_decode(int ref, int &first, int &count) {
 // tests (the reference re-tests a node's own box after its parent already did).  Near child
 // first; the far child is pushed with its entry distance and culled against the shrunken tmax
 // when popped (same effect as the reference's pop-time re-test).
-template <bool COUNT>
-__device__ __forceinline__ void bvh_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nBox) {
-    const f3 inv = rcp3(d);
+//
+// The walk is a resumable state machine so that a warp can (a) run "while-while": every lane
+// descends inner nodes until it holds a leaf, then all lanes test their leaves together, and
+// (b) hand finished lanes new rays between rounds (k_extend's dynamic fetch).
+struct BvhWalk {
+    f3 o, d, inv;
+    Hit h;
+    int ref;   // >= 0 inner node, < 0 leaf, PTB_REF_DONE finished
+    int sp;
+    bool fast; // inv_dir finite: FMNMX slab test allowed
     int sref[PTB_STACK];
     float sdist[PTB_STACK];
-    int sp = 0;
-    int ref = S.bvh_root;
-    for (;;) {
-        if (ref >= 0) {
-            const float4 *n = S.nodes + 4 * (size_t)ref;
-            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
-            const int4 q3 = __ldg(reinterpret_cast<const int4 *>(n + 3));
-            if (COUNT) nBox += 2;
-            float d0, d1;
-            const bool h0 = slab(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
-            const bool h1 = slab(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
-            if (h0 && h1) {
-                // bvh.cpp:75-84: left first unless the right child is strictly nearer
-                const bool leftFirst = d1 >= d0;
-                const int nearRef = leftFirst ? q3.x : q3.y, farRef = leftFirst ? q3.y : q3.x;
-                sref[sp] = farRef;
-                sdist[sp] = leftFirst ? d1 : d0;
-                sp++;
-                ref = nearRef;
-                continue;
-            } else if (h0) {
-                ref = q3.x;
-                continue;
-            } else if (h1) {
-                ref = q3.y;
-                continue;
-            }
-        } else {
-            int first, count;
-            leaf_decode(ref, first, count);
-            for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
-        }
-        // pop
+
+    __device__ __forceinline__ void begin(const SceneDev &S, f3 o_, f3 d_, const Hit &h0) {
+        o = o_;
+        d = d_;
+        inv = rcp3(d_);
+        fast = finite3(inv);
+        h = h0;
+        sp = 0;
+        ref = S.n_tris ? S.bvh_root : PTB_REF_DONE;
+    }
+    __device__ __forceinline__ void pop() {
         for (;;) {
-            if (sp == 0) return;
+            if (sp == 0) {
+                ref = PTB_REF_DONE;
+                return;
+            }
             sp--;
             if (!(sdist[sp] > h.t)) break;
         }
         ref = sref[sp];
     }
+    // one round: descend to the next leaf (or finish), test it, pop.  Returns false when done.
+    template <bool COUNT>
+    __device__ __forceinline__ bool round(const SceneDev &S, uint32_t &nTri, uint32_t &nBox) {
+        while (ref >= 0) {
+            const float4 *n = S.nodes + 4 * (size_t)ref;
+            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
+            const int4 q3 = __ldg(reinterpret_cast<const int4 *>(n + 3));
+            if (COUNT) nBox += 2;
+            float d0, d1;
+            bool h0, h1;
+            if (fast) {
+                h0 = slab_fast(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
+                h1 = slab_fast(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
+            } else {
+                h0 = slab(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
+                h1 = slab(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
+            }
+            if (h0 && h1) {
+                // bvh.cpp:75-84: left first unless the right child is strictly nearer
+                const bool leftFirst = d1 >= d0;
+                sref[sp] = leftFirst ? q3.y : q3.x;
+                sdist[sp] = leftFirst ? d1 : d0;
+                sp++;
+                ref = leftFirst ? q3.x : q3.y;
+            } else if (h0) {
+                ref = q3.x;
+            } else if (h1) {
+                ref = q3.y;
+            } else {
+                pop();
+            }
+        }
+        if (ref != PTB_REF_DONE) {
+            int first, count;
+            leaf_decode(ref, first, count);
+            for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
+            pop();
+        }
+        return ref != PTB_REF_DONE;
+    }
+};
+
+template <bool COUNT>
+__device__ __forceinline__ void bvh_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nBox) {
+    BvhWalk w;
+    w.begin(S, o, d, h);
+    while (w.round<COUNT>(S, nTri, nBox)) {
+    }
+    h = w.h;
 }
 
 // ---- brute force: mode ALL (scene.cpp:77-86, object.cpp:19-34) ------------------------------

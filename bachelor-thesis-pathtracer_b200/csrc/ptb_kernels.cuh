@@ -290,6 +290,85 @@ __global__ void __launch_bounds__(128) k_extend(SceneDev S, FrameDev F, const ui
     }
 }
 
+// ---- extend, BVH mode: persistent warps with dynamic ray fetch ------------------------------
+// The v0 kernel above ran one ray per thread to completion: ncu showed 7 of 32 lanes active per
+// issued instruction (profiles/r1_ncu_extend_bvh_cornell_v0.txt) — the warp waits for its longest
+// ray and inner-node / leaf phases of different lanes serialise.  Here a warp keeps pulling
+// entries from the queue through one global cursor: lanes whose ray finished are refilled as soon
+// as fewer than `fetchKeep` lanes are still walking (warp ballot + popc + one atomicAdd per refill),
+// and each round is "while-while" (BvhWalk::round): all lanes descend to a leaf, then all test
+// their leaf triangles.  Results do not depend on which lane traces which ray.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_extend_bvh(SceneDev S, FrameDev F, const uint32_t *__restrict__ q, const uint32_t *__restrict__ qs,
+                                                    const uint32_t *__restrict__ nMainPtr, const uint32_t *__restrict__ nShadowPtr,
+                                                    uint32_t *__restrict__ cursor, int fetchKeep) {
+    const uint32_t nMain = *nMainPtr, nShadow = nShadowPtr ? *nShadowPtr : 0u;
+    const uint32_t total = nMain + nShadow;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    BvhWalk w;
+    bool active = false, more = true, shadow = false;
+    uint32_t slot = 0, nTri = 0, nAS = 0;
+    for (;;) {
+        const unsigned idle = __ballot_sync(full, !active);
+        if (more && idle) {
+            const int leader = __ffs(idle) - 1;
+            const uint32_t want = (uint32_t)__popc(idle);
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(cursor, want);
+            base = __shfl_sync(full, base, leader);
+            if (base + want >= total) more = false;
+            if (!active) {
+                const uint32_t e = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                if (e < nMain) {
+                    const uint32_t s = q[e];
+                    if (!(s & PTB_Q_NOEXTEND)) {
+                        slot = s;
+                        shadow = false;
+                        const float4 o4 = F.ray_o[slot], d4 = F.ray_d[slot];
+                        w.begin(S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), Hit{PTB_INF, -1, 0.0f, 0.0f, -1});
+                        nTri = nAS = 0;
+                        active = true;
+                    }
+                } else if (e < total) {
+                    slot = qs[e - nMain];
+                    shadow = true;
+                    const float4 o4 = F.sh_o[slot], d4 = F.sh_d[slot];
+                    const int lt = __float_as_int(d4.w);
+                    w.begin(S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z),
+                            Hit{o4.w, lt, 0.0f, 0.0f, __float_as_int(__ldg(&S.tri[3 * lt]).w)});
+                    active = true;
+                }
+            }
+        }
+        unsigned act = __ballot_sync(full, active);
+        if (!act) {
+            if (!more) break;
+            continue;
+        }
+        do {
+            if (active) {
+                bool cont;
+                if (COUNT && !shadow) cont = w.round<true>(S, nTri, nAS);
+                else cont = w.round<false>(S, nTri, nAS);
+                if (!cont) {
+                    if (shadow) {
+                        F.sh_hit[slot] = make_float4(w.h.t, __int_as_float(w.h.tri), 0.0f, 0.0f);
+                    } else {
+                        F.hit[slot] = make_float4(w.h.t, __int_as_float(w.h.tri), w.h.u, w.h.v);
+                        if (COUNT) {
+                            F.cnt_tri[slot] = nTri;
+                            F.cnt_as[slot] = nAS;
+                        }
+                    }
+                    active = false;
+                }
+            }
+            act = __ballot_sync(full, active);
+        } while (act && (!more || __popc(act) >= fetchKeep));
+    }
+}
+
 // Russian roulette of the NEXT findIntersection call (scene.cpp:67-72): one draw always;
 // for depth > 2 kill if xi*max(tp) < 0.15 (double compare <=> p < 0.15f), else rescale by
 // (float)(1.0f / ((1 - 0.15) * (double)max)).  Returns true when the ray was killed.
