@@ -7,7 +7,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libptb.so")
+LIB_PATH = os.environ.get("PTB_LIB") or os.path.join(_HERE, "libptb.so")  # PTB_LIB: tuning variants only
 
 MODE_ALL, MODE_BVH, MODE_TWO_PLANE, MODE_SUB_BEAMS = 0, 1, 2, 3
 MODE_NAMES = {0: "ALL", 1: "BVH", 2: "TWO_PLANE", 3: "SUB_BEAMS"}

@@ -35,14 +35,17 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_native(force=False, verbose=False):
-    """Compile csrc/ into libptb.so if sources are newer than the library."""
-    if not force and not _stale():
+def build_native(force=False, verbose=False, defines=(), out=None):
+    """Compile csrc/ into libptb.so if sources are newer than the library.  `defines`/`out` build a
+    tuning variant beside it (loaded with PTB_LIB=<path>; scripts/ only)."""
+    out = out or OUT
+    if not force and not defines and not _stale():
         return OUT
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-I", INCLUDE, "-o", OUT] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [_nvcc()] + NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + \
+        ["-I", INCLUDE, "-o", out] + [os.path.join(CSRC, s) for s in SOURCES]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + r.stdout[-6000:])
     if verbose:
         print(r.stdout)
-    return OUT
+    return out

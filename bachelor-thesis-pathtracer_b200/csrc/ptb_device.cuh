@@ -179,8 +179,9 @@ struct BvhWalk {
     int ref;   // >= 0 inner node, < 0 leaf, PTB_REF_DONE finished
     int sp;
     bool fast; // inv_dir finite: FMNMX slab test allowed
-    int sref[PTB_STACK];
-    float sdist[PTB_STACK];
+    // The stack itself (far child reference + its entry distance) is NOT a member: a dynamically
+    // indexed array inside the struct drags every scalar above into local memory with it (seen in
+    // ncu as 9 % LDL/STL).  Callers own `int2 stack[PTB_STACK]` and pass it to pop()/round().
 
     __device__ __forceinline__ void begin(const SceneDev &S, f3 o_, f3 d_, const Hit &h0) {
         o = o_;
@@ -191,20 +192,23 @@ struct BvhWalk {
         sp = 0;
         ref = S.n_tris ? S.bvh_root : PTB_REF_DONE;
     }
-    __device__ __forceinline__ void pop() {
+    __device__ __forceinline__ void pop(const int2 *stack) {
         for (;;) {
             if (sp == 0) {
                 ref = PTB_REF_DONE;
                 return;
             }
             sp--;
-            if (!(sdist[sp] > h.t)) break;
+            const int2 e = stack[sp];
+            if (!(__int_as_float(e.y) > h.t)) {
+                ref = e.x;
+                return;
+            }
         }
-        ref = sref[sp];
     }
     // one round: descend to the next leaf (or finish), test it, pop.  Returns false when done.
     template <bool COUNT>
-    __device__ __forceinline__ bool round(const SceneDev &S, uint32_t &nTri, uint32_t &nBox) {
+    __device__ __forceinline__ bool round(const SceneDev &S, int2 *stack, uint32_t &nTri, uint32_t &nBox) {
         while (ref >= 0) {
             const float4 *n = S.nodes + 4 * (size_t)ref;
             const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
@@ -222,23 +226,21 @@ struct BvhWalk {
             if (h0 && h1) {
                 // bvh.cpp:75-84: left first unless the right child is strictly nearer
                 const bool leftFirst = d1 >= d0;
-                sref[sp] = leftFirst ? q3.y : q3.x;
-                sdist[sp] = leftFirst ? d1 : d0;
-                sp++;
+                stack[sp++] = make_int2(leftFirst ? q3.y : q3.x, __float_as_int(leftFirst ? d1 : d0));
                 ref = leftFirst ? q3.x : q3.y;
             } else if (h0) {
                 ref = q3.x;
             } else if (h1) {
                 ref = q3.y;
             } else {
-                pop();
+                pop(stack);
             }
         }
         if (ref != PTB_REF_DONE) {
             int first, count;
             leaf_decode(ref, first, count);
             for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
-            pop();
+            pop(stack);
         }
         return ref != PTB_REF_DONE;
     }
@@ -247,8 +249,9 @@ struct BvhWalk {
 template <bool COUNT>
 __device__ __forceinline__ void bvh_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nBox) {
     BvhWalk w;
+    int2 stack[PTB_STACK];
     w.begin(S, o, d, h);
-    while (w.round<COUNT>(S, nTri, nBox)) {
+    while (w.round<COUNT>(S, stack, nTri, nBox)) {
     }
     h = w.h;
 }

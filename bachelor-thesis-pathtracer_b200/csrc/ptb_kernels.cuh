@@ -14,6 +14,10 @@
 #pragma once
 #include "ptb_device.cuh"
 
+#ifndef PTB_LOGIC_MINBLOCKS
+#define PTB_LOGIC_MINBLOCKS 8 /* resident CTAs/SM k_logic is register-capped for (64 regs, ~110 B spills): 4142 vs 3727 Mrays/s on Cornell at 4 */
+#endif
+
 namespace ptb {
 
 struct CamDev { // createCameraRay inputs, camera.cpp:47-66
@@ -307,6 +311,7 @@ __global__ void __launch_bounds__(128) k_extend_bvh(SceneDev S, FrameDev F, cons
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     BvhWalk w;
+    int2 stack[PTB_STACK];
     bool active = false, more = true, shadow = false;
     uint32_t slot = 0, nTri = 0, nAS = 0;
     for (;;) {
@@ -349,8 +354,8 @@ __global__ void __launch_bounds__(128) k_extend_bvh(SceneDev S, FrameDev F, cons
         do {
             if (active) {
                 bool cont;
-                if (COUNT && !shadow) cont = w.round<true>(S, nTri, nAS);
-                else cont = w.round<false>(S, nTri, nAS);
+                if (COUNT && !shadow) cont = w.round<true>(S, stack, nTri, nAS);
+                else cont = w.round<false>(S, stack, nTri, nAS);
                 if (!cont) {
                     if (shadow) {
                         F.sh_hit[slot] = make_float4(w.h.t, __int_as_float(w.h.tri), 0.0f, 0.0f);
@@ -387,7 +392,7 @@ __device__ __forceinline__ bool roulette(uint32_t &rng, int depth, f3 &tp) {
 // START = true: first launch of a render call; every owned pixel that still needs samples gets
 // its next primary ray (no hit to process).
 template <int MODE, bool START, bool COUNT>
-__global__ void __launch_bounds__(128) k_logic(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, const uint32_t *__restrict__ qin,
+__global__ void __launch_bounds__(128, PTB_LOGIC_MINBLOCKS) k_logic(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, const uint32_t *__restrict__ qin,
                                                const uint32_t *__restrict__ nInPtr, uint32_t *__restrict__ qout,
                                                uint32_t *__restrict__ nOutPtr, uint32_t *__restrict__ qsOut,
                                                uint32_t *__restrict__ nsOutPtr, unsigned long long *__restrict__ counters) {
