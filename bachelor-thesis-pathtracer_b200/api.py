@@ -21,7 +21,7 @@ SYMBOLS = (
     "ptb_load_ptbs", "ptb_set_camera", "ptb_build_bvh", "ptb_build_subgrid", "ptb_build_subbeams", "ptb_structure_bytes",
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
-    "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream",
+    "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
 )
 
 
@@ -66,10 +66,13 @@ def load_library():
     L.ptb_build_bvh.argtypes = [vp]
     L.ptb_build_subgrid.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_build_subbeams.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32]
+    L.ptb_set_build_limits.argtypes = [vp, ci]
     L.ptb_structure_bytes.argtypes = [vp, ci]
     L.ptb_structure_bytes.restype = cu64
     L.ptb_set_params.argtypes = [vp, ctypes.POINTER(Params)]
     L.ptb_reset.argtypes = [vp]
+    L.ptb_clear.argtypes = [vp]
+    L.ptb_set_camera_basis.argtypes = [vp, vp, vp, vp, vp, ctypes.c_float, ctypes.c_float, ctypes.c_float]
     L.ptb_render.argtypes = [vp, ci]
     L.ptb_render_async.argtypes = [vp, ci]
     L.ptb_sync.argtypes = [vp]
@@ -157,7 +160,9 @@ class PathTracer:
     def build_subgrid(self, gs=10, os_=5, m=40):
         self._ck(self.L.ptb_build_subgrid(self.h, gs, os_, m), "ptb_build_subgrid")
 
-    def build_subbeams(self, gs=10, m=40):
+    def build_subbeams(self, gs=10, m=40, max_depth=None):
+        if max_depth is not None:
+            self._ck(self.L.ptb_set_build_limits(self.h, max_depth), "ptb_set_build_limits")
         self._ck(self.L.ptb_build_subbeams(self.h, gs, m), "ptb_build_subbeams")
 
     def structure_bytes(self, mode):
@@ -173,6 +178,14 @@ class PathTracer:
 
     def reset(self):
         self._ck(self.L.ptb_reset(self.h), "ptb_reset")
+
+    def clear(self):
+        """reset() of the reference: image and sample counts zeroed, per-pixel RNG streams continue."""
+        self._ck(self.L.ptb_clear(self.h), "ptb_clear")
+
+    def set_camera_basis(self, origin, forward, right, up, focus, dof, fov_scale):
+        v = [(ctypes.c_float * 3)(*x) for x in (origin, forward, right, up)]
+        self._ck(self.L.ptb_set_camera_basis(self.h, *v, focus, dof, fov_scale), "ptb_set_camera_basis")
 
     def render(self, add_samples):
         self._ck(self.L.ptb_render(self.h, add_samples), "ptb_render")

@@ -28,7 +28,8 @@ struct ptb_ctx {
     int device = 0;
     int sms = 148;
     int extendCtas = 12; // resident 128-thread CTAs per SM of the persistent BVH extend (40 registers/thread)
-    int fetchKeep = 20;  // refill a warp's idle lanes when fewer than this many are still walking
+    int fetchKeep = 20;
+    int beamMaxDepth = 12; // guard on the reference's unbounded Subbeam recursion, ptb_set_build_limits  // refill a warp's idle lanes when fewer than this many are still walking
     cudaStream_t stream = nullptr;
     std::string err;
     bool poisoned = false;
@@ -41,6 +42,8 @@ struct ptb_ctx {
     std::vector<LightDev> lights;
     ptb_camera cam{};
     bool haveCam = false;
+    bool camBasis = false; // camDev was given verbatim (ptb_set_camera_basis): skip the orthonormalisation
+    CamDev camDev{};
     ptb_params prm{};
     bool haveParams = false;
 
@@ -178,7 +181,8 @@ ParamsDev make_params(const ptb_ctx *c) {
     P.debug_scale = c->prm.debug_scale;
     P.target_samples = c->targetSamples;
     P.n_lights = (uint32_t)c->lights.size();
-    make_camera(c->cam, P.cam);
+    if (c->camBasis) P.cam = c->camDev;
+    else make_camera(c->cam, P.cam);
     return P;
 }
 
@@ -336,6 +340,24 @@ extern "C" int ptb_set_camera(ptb_ctx *c, const ptb_camera *cam) {
     c->cam = *cam;
     if (c->cam.fov_degrees == 0.0f) c->cam.fov_degrees = 70.0f;
     c->haveCam = true;
+    c->camBasis = false;
+    return PTB_OK;
+}
+
+extern "C" int ptb_set_camera_basis(ptb_ctx *c, const float origin[3], const float forward[3], const float right[3], const float up[3],
+                                    float focus, float dof, float fov_scale) {
+    GUARD(c);
+    if (!origin || !forward || !right || !up) return fail(c, PTB_ERR_INVALID, "null camera vectors");
+    for (int k = 0; k < 3; ++k) {
+        c->camDev.origin[k] = origin[k];
+        c->camDev.forward[k] = forward[k];
+        c->camDev.right[k] = right[k];
+        c->camDev.up[k] = up[k];
+    }
+    c->camDev.focus = focus;
+    c->camDev.dof = dof;
+    c->camDev.fovScale = fov_scale;
+    c->haveCam = c->camBasis = true;
     return PTB_OK;
 }
 
@@ -430,6 +452,13 @@ extern "C" int ptb_build_bvh(ptb_ctx *c) {
     return PTB_OK;
 }
 
+extern "C" int ptb_set_build_limits(ptb_ctx *c, int beam_max_depth) {
+    GUARD(c);
+    if (beam_max_depth < 0 || beam_max_depth > 32) return fail(c, PTB_ERR_INVALID, "beam_max_depth must be 0..32 (0 = unbounded like the reference)");
+    c->beamMaxDepth = beam_max_depth;
+    return PTB_OK;
+}
+
 extern "C" uint64_t ptb_structure_bytes(const ptb_ctx *c, int mode) {
     if (!c) return 0;
     const uint64_t tris = (uint64_t)c->mat.size() * 48ull;
@@ -510,14 +539,19 @@ static int alloc_frame(ptb_ctx *c) {
     return PTB_OK;
 }
 
-extern "C" int ptb_reset(ptb_ctx *c) {
+static int reset_frame(ptb_ctx *c, int reseed);
+extern "C" int ptb_reset(ptb_ctx *c) { return reset_frame(c, 1); }
+extern "C" int ptb_clear(ptb_ctx *c) { return reset_frame(c, 0); }
+
+static int reset_frame(ptb_ctx *c, int reseed) {
     GUARD(c);
     if (!c->haveParams) return fail(c, PTB_ERR_INVALID, "ptb_set_params first");
     if (c->frameDirty) {
         int r = alloc_frame(c);
         if (r) return r;
+        reseed = 1; // a new frame has no streams to continue
     }
-    k_reset<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, c->F.samples, c->F.rng, c->W, c->H);
+    k_reset<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, c->F.samples, c->F.rng, c->W, c->H, reseed);
     CK(cudaMemsetAsync(c->dCounters, 0, 8 * sizeof(unsigned long long), c->stream));
     CK(cudaStreamSynchronize(c->stream));
     c->targetSamples = 0;
@@ -896,7 +930,7 @@ extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
     std::vector<float> leaf;
     leaf_positions(c, leaf);
     SubbeamResult R;
-    build_subbeams(leaf.data(), c->mat.size(), c->bvh.lo, c->bvh.hi, gs, m, 12, R);
+    build_subbeams(leaf.data(), c->mat.size(), c->bvh.lo, c->bvh.hi, gs, m, c->beamMaxDepth, R);
     devFree(c->dBeam); devFree(c->dBeamIdx);
     for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
     CK(cudaMalloc(&c->dBeam, std::max<size_t>(1, R.beams.size()) * sizeof(BeamRec)));

@@ -443,6 +443,16 @@ __global__ void __launch_bounds__(128, PTB_LOGIC_MINBLOCKS) k_logic(ParamsDev P,
                 const bool killed = (ps.flags & PTB_FLAG_KILLED) != 0u;
                 if (done) {
                     terminated = true;
+                } else if (COUNT && P.debug_view) {
+                    // heat-map view, tracer.cpp:136-142: shade() still runs (its draws advance the stream),
+                    // then the pixel becomes the test count of this one ray and the path ends
+                    if (tri >= 0) {
+                        ShadowOut sh;
+                        f3 pendingEm;
+                        shade_hit(P, S, A, ps, h4.x, tri, h4.z, h4.w, terminated, sh, pendingEm);
+                    }
+                    ps.depth++;
+                    terminated = true;
                 } else if (tri < 0) {
                     // miss: shade is a no-op and the reference re-traces the unchanged ray until
                     // roulette ends the path; replayed here without traversals.
@@ -496,12 +506,18 @@ __global__ void __launch_bounds__(128, PTB_LOGIC_MINBLOCKS) k_logic(ParamsDev P,
                 if (!fresh) { // tracer.cpp:145-155
                     const int n = F.samples[pixel] + 1;
                     F.samples[pixel] = n;
-                    const float cs = (float)n;
-                    const float4 prev = F.image[pixel];
-                    f3 color = ps.light;
-                    color = color + mk3(prev.x, prev.y, prev.z) * cs;
-                    color = color / (cs + 1.0f);
-                    F.image[pixel] = make_float4(color.x, color.y, color.z, 1.0f);
+                    if (COUNT && P.debug_view) {
+                        const float it = (float)(P.debug_view == 2 ? F.cnt_tri[slot] : F.cnt_as[slot]);
+                        const f3 color = (it > (float)P.debug_scale) ? mk3(1.0f, 0.0f, 0.0f) : mk3(it, it, it) / (float)P.debug_scale;
+                        F.image[pixel] = make_float4(color.x, color.y, color.z, 1.0f);
+                    } else {
+                        const float cs = (float)n;
+                        const float4 prev = F.image[pixel];
+                        f3 color = ps.light;
+                        color = color + mk3(prev.x, prev.y, prev.z) * cs;
+                        color = color / (cs + 1.0f);
+                        F.image[pixel] = make_float4(color.x, color.y, color.z, 1.0f);
+                    }
                     cPaths++;
                 }
                 if (F.samples[pixel] < P.target_samples) { // next sample of this pixel, in place
@@ -614,12 +630,13 @@ __global__ void __launch_bounds__(128) k_primary(ParamsDev P, SceneDev S, AttrDe
 }
 
 // initTracer (tracer.cpp:227-244) for a W x H frame
-__global__ void k_reset(float4 *image, int *samples, uint32_t *rng, int W, int H) {
+// reseed = 0: reset() (tracer.cpp:195-217) — image and sample counts only, the RNG streams continue
+__global__ void k_reset(float4 *image, int *samples, uint32_t *rng, int W, int H, int reseed) {
     const uint32_t n = (uint32_t)W * (uint32_t)H;
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         image[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         samples[p] = 0;
-        rng[p] = hash_coords((int)(p % (uint32_t)W), (int)(p / (uint32_t)W));
+        if (reseed) rng[p] = hash_coords((int)(p % (uint32_t)W), (int)(p / (uint32_t)W));
     }
 }
 

@@ -90,15 +90,34 @@ def upload_scene(pt, scene):
     pt.set_camera(c["pos"], c["forward"], c["focus"], c["dof"])
 
 
+# Bit-reproducibility: the generators use only +, -, *, /, sqrt, floor and comparisons on float64 (all
+# correctly rounded by IEEE 754, no libm transcendental, no BLAS reduction), so every machine produces
+# the same bytes and the committed reference digests (tests/golden/) stay valid on the GPU box.
+def _norm3(v):
+    return np.sqrt(v[..., 0] * v[..., 0] + v[..., 1] * v[..., 1] + v[..., 2] * v[..., 2])
+
+
+def _cross(a, b):
+    return np.stack([a[..., 1] * b[..., 2] - a[..., 2] * b[..., 1], a[..., 2] * b[..., 0] - a[..., 0] * b[..., 2],
+                     a[..., 0] * b[..., 1] - a[..., 1] * b[..., 0]], -1)
+
+
+def _psin(x):
+    """Parabolic stand-in for sin(x) (period 2*pi, peaks +-1) from exactly rounded operations only."""
+    t = x * (1.0 / 6.283185307179586)
+    t = t - np.floor(t)
+    return np.where(t < 0.5, 16.0 * t * (0.5 - t), -16.0 * (t - 0.5) * (1.0 - t))
+
+
 def _tri_area(pos):
     p = pos.reshape(-1, 3, 3).astype(np.float64)
-    return 0.5 * np.linalg.norm(np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]), axis=1)
+    return 0.5 * _norm3(_cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]))
 
 
 def _flat_normals(pos):
     p = pos.reshape(-1, 3, 3).astype(np.float64)
-    n = np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0])
-    l = np.linalg.norm(n, axis=1, keepdims=True)
+    n = _cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0])
+    l = _norm3(n)[..., None]
     n = np.where(l > 0, n / np.maximum(l, 1e-300), np.array([0.0, 1.0, 0.0]))
     return np.repeat(n[:, None, :], 3, axis=1).reshape(-1, 9).astype(np.float32)
 
@@ -127,19 +146,19 @@ def _octa_sphere(level):
                     p = p[:, ::-1, :]
                 faces.append(p)
     p = np.concatenate(faces)
-    return p / np.linalg.norm(p, axis=-1, keepdims=True)
+    return p / _norm3(p)[..., None]
 
 
 def _fractal(p, seed, octaves=6):
-    """Seeded sum-of-sines fractal on unit directions p[..., 3] (float64), range about [-1, 1]."""
-    rng = np.random.default_rng(seed)
+    """Seeded sum-of-waves fractal on unit directions p[..., 3] (float64), range about [-1, 1]."""
+    rng = np.random.Generator(np.random.MT19937(seed))
     out = np.zeros(p.shape[:-1])
     amp, freq, tot = 1.0, 2.0, 0.0
     for _ in range(octaves):
         for _ in range(3):
-            d = rng.normal(size=3)
-            d /= np.linalg.norm(d)
-            out += amp * np.sin(freq * (p @ d) + rng.uniform(0, 2 * np.pi))
+            d = rng.uniform(-1.0, 1.0, size=3)
+            d = d / np.sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2] + 1e-9)
+            out += amp * _psin(freq * (p[..., 0] * d[0] + p[..., 1] * d[1] + p[..., 2] * d[2]) + rng.uniform(0.0, 6.0))
         tot += 3 * amp
         amp *= 0.5
         freq *= 2.0
@@ -151,12 +170,13 @@ def statue_mesh(level=8, seed=0x1ACE, radius=(105.0, 225.0, 105.0), base=(0.0, -
     s = _octa_sphere(level)
     r = 1.0 + 0.22 * _fractal(s, seed)
     # a waist/shoulder profile along y so the silhouette is not a plain ellipsoid
-    prof = 0.75 + 0.25 * np.cos(3.0 * s[..., 1] + 0.6)
+    prof = 0.75 + 0.25 * _psin(3.0 * s[..., 1] + 2.2)
     p = s * r[..., None]
     p[..., 0] *= radius[0] * prof
     p[..., 2] *= radius[2] * prof
     p[..., 1] = p[..., 1] * radius[1] + radius[1] * 1.0
     p += np.array(base)
+    p[..., 1] += (base[1] + 1.0) - p[..., 1].min()  # stand on the floor
     return p.reshape(-1, 9).astype(np.float32)
 
 
@@ -212,9 +232,14 @@ def soup_rays(n, seed=99):
     """Config 5 rays: origin uniform on the sphere r = 250, direction towards a uniform point of [-100,100]^3
     (incoherent), normalised in float32.  [n, 6] float32."""
     rng = np.random.Generator(np.random.MT19937(seed))
-    o = rng.normal(size=(n, 3))
-    o = (250.0 * o / np.linalg.norm(o, axis=1, keepdims=True)).astype(np.float32)
+    o = np.zeros((0, 3))
+    while o.shape[0] < n:  # uniform directions by rejection from the cube (exact operations only)
+        c = rng.uniform(-1.0, 1.0, size=(2 * n + 64, 3))
+        r2 = c[:, 0] * c[:, 0] + c[:, 1] * c[:, 1] + c[:, 2] * c[:, 2]
+        o = np.concatenate([o, c[(r2 <= 1.0) & (r2 > 1e-4)]])
+    o = o[:n]
+    o = (250.0 * o / _norm3(o)[:, None]).astype(np.float32)
     tgt = rng.uniform(-100.0, 100.0, size=(n, 3)).astype(np.float32)
     d = (tgt - o).astype(np.float32)
-    d = (d / np.sqrt((d * d).sum(1, keepdims=True), dtype=np.float32)).astype(np.float32)
+    d = (d / np.sqrt(d[:, 0:1] * d[:, 0:1] + d[:, 1:2] * d[:, 1:2] + d[:, 2:3] * d[:, 2:3])).astype(np.float32)
     return np.concatenate([o, d], 1).astype(np.float32)

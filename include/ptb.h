@@ -87,6 +87,9 @@ int ptb_upload_objects(ptb_ctx *ctx, const ptbs_object *objects, uint32_t n);   
 int ptb_upload_materials(ptb_ctx *ctx, const ptbs_material *materials, uint32_t n); /* may be called again (UI edits + reset) */
 int ptb_load_ptbs(ptb_ctx *ctx, const char *path); /* the three uploads + camera from one .ptbs container */
 int ptb_set_camera(ptb_ctx *ctx, const ptb_camera *cam); /* cameraSetForward + origin/dof/focus, scene.cpp:127-130 */
+/* the Camera struct verbatim (camera.h:5-18) after the UI rotated it (camera.cpp:70-135): no re-orthonormalisation */
+int ptb_set_camera_basis(ptb_ctx *ctx, const float origin[3], const float forward[3], const float right[3], const float up[3],
+                         float focus, float dof, float fov_scale);
 
 /* ---- acceleration structures ---------------------------------------------------------------
  * Builders run on the host inside the library (construction is outside the timed path in the
@@ -94,11 +97,15 @@ int ptb_set_camera(ptb_ctx *ctx, const ptb_camera *cam); /* cameraSetForward + o
 int ptb_build_bvh(ptb_ctx *ctx);                                        /* constructBVH, bvh.h:33 (scene.cpp:113-120) */
 int ptb_build_subgrid(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m); /* setGridSettings + constructGrid, lightFieldGrid.h:24,26 */
 int ptb_build_subbeams(ptb_ctx *ctx, uint32_t gs, uint32_t m);          /* setGridBeamsSettings + buildGridsWithSubBeams, lightFieldGridSubBeams.h:28-29 */
+/* The reference's Subbeam recursion has no depth limit (lightFieldGridSubBeams.cpp:286-324) and does not
+ * terminate on dense clusters; beams at `beam_max_depth` become leaves (default 12, 0 = unbounded). */
+int ptb_set_build_limits(ptb_ctx *ctx, int beam_max_depth);
 uint64_t ptb_structure_bytes(const ptb_ctx *ctx, int mode);             /* getMemoryBVH / getMemory2Plane / getMemoryGridBeams */
 
 /* ---- rendering ------------------------------------------------------------------------------ */
 int ptb_set_params(ptb_ctx *ctx, const ptb_params *p); /* setWindowSize + setIntersectMode + getNEE() ... */
 int ptb_reset(ptb_ctx *ctx);                           /* initTracer, tracer.cpp:227-244: zero image/samples, reseed rng x<<16|y */
+int ptb_clear(ptb_ctx *ctx);                           /* reset(), tracer.cpp:195-217: zero image/samples, RNG streams continue */
 int ptb_render(ptb_ctx *ctx, int add_samples);         /* trace(true) with MAX_SAMPLE_COUNT += add_samples, tracer.cpp:164-185; synchronous */
 int ptb_render_async(ptb_ctx *ctx, int add_samples);   /* same, returns after enqueueing what can be enqueued; pair with ptb_sync */
 int ptb_sync(ptb_ctx *ctx);

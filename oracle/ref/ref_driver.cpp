@@ -72,6 +72,13 @@ static ThreadStats *stats() {
     return tl_stats;
 }
 
+#ifdef PTB_FACADE
+// Facade flavour (oracle/_ref/ptfacade): the same driver and the same reference objects, but
+// src/tracer.cpp is replaced by bachelor-thesis-pathtracer_b200/host/tracer_facade.cpp, so
+// trace() runs on the GPU through libptb.so.  No --wrap instrumentation (nothing calls
+// findIntersection on the host); the depth cap goes through the facade's own setter.
+#include "../../bachelor-thesis-pathtracer_b200/host/tracer_facade.h"
+#else
 extern "C" {
 bool __real__Z20triangleIntersectionR3RayR8Triangle(Ray &, Triangle &);
 bool __wrap__Z20triangleIntersectionR3RayR8Triangle(Ray &r, Triangle &t) {
@@ -112,6 +119,7 @@ Vector3 __wrap__Z5shadeR3Ray(Ray &r) {
     return v;
 }
 }
+#endif
 
 // ---- options -----------------------------------------------------------------------------
 struct Opts {
@@ -305,6 +313,10 @@ static void sumStats(uint64_t &calls, uint64_t &trav, uint64_t &uniq) {
 // Primary-ray hit records with the exact rays traceWF would generate for the first sample
 // (setupRay, src/tracer.cpp:72-88, seeded by initTracer :236-242).  Pixel index = y*W + x.
 static void cmdPrimaryHits(const Opts &o, const char *out) {
+#ifdef PTB_FACADE
+    (void)o; (void)out;
+    die("primary-hits needs the host tracer (setupRay); not part of the facade flavour");
+#else
     setWindowSize(o.W, o.H);
     initTracer();
     size_t n = (size_t)o.W * o.H;
@@ -345,6 +357,7 @@ static void cmdPrimaryHits(const Opts &o, const char *out) {
     fwrite(rayOD.data(), 4, n * 6, f);
     fclose(f);
     printf("PTREF_JSON {\"cmd\":\"primary-hits\",\"rays\":%zu,\"ms\":%.3f,\"threads\":%d,\"mode\":%d}\n", n, ms, T, o.mode);
+#endif
 }
 
 // Closest hit for externally supplied rays (config 5 / traversal-only CPU baseline).
@@ -402,6 +415,11 @@ static void cmdTraceRays(const Opts &o, const char *in, const char *out) {
 static void cmdRender(const Opts &o, const char *out) {
     getNEE() = o.nee != 0;
     g_maxDepth = o.maxDepth;
+#ifdef PTB_FACADE
+    ptbFacadeSetMaxDepth(o.maxDepth);
+    ptbFacadeSetGridSettings(o.gs, o.os, o.m);
+    ptbFacadeSetGridBeamsSettings(o.bgs, o.bm);
+#endif
     setWindowSize(o.W, o.H);
     getMaxSampleCount() = o.spp;
     getDebugView() = false;
@@ -412,6 +430,9 @@ static void cmdRender(const Opts &o, const char *out) {
     double t2 = nowMs();
     uint64_t calls, trav, uniq;
     sumStats(calls, trav, uniq);
+#ifdef PTB_FACADE
+    calls = trav = uniq = ptbFacadeRaysTraced();
+#endif
     size_t n = (size_t)o.W * o.H;
     if (out && strcmp(out, "-") != 0) {
         std::vector<float> img(n * 4);

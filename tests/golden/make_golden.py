@@ -11,7 +11,14 @@ build container (the reference sources do not travel); the outputs do:
         cnt{m}_nee{0,1}               [tri_tests, as_tests] (tracer.cpp:60-70)
         imgd{m}                       image with max_depth = 2, 3 spp, nee 1 (the cap is a --wrap of shade)
 
-    python tests/golden/make_golden.py
+  tests/golden/lucy_standin_ref_1080p.npz   (--lucy; the reference needs 25 s for its BVH, 16 min / 11 GB
+                                      for its Subgrids (gs 8, os 8, m 50) on the 524,310-triangle stand-in)
+        scene_sha256                  digest of the generated positions (the generator is bit-reproducible)
+        tri                           primary hit triangle ids, 1920x1080, reference BVH mode
+        t_sha256                      digest of the hit distances (bit pattern)
+        two_plane_equal               1 if the reference's TWO_PLANE run gave identical t and ids
+
+    python tests/golden/make_golden.py [--lucy [--lucy-two-plane]]
 """
 import os
 import sys
@@ -26,7 +33,34 @@ REF_SHOWCASE = "/root/reference/showcase"
 W = H = 64
 
 
+def lucy():
+    import hashlib
+    import tempfile
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    import ptb_b200
+    sc = ptb_b200.scenes
+    scene = sc.lucy_standin(sc.read_ptbs(os.path.join(HERE, "cornel.ptbs")))
+    with tempfile.TemporaryDirectory() as d:
+        ptbs = os.path.join(d, "lucy.ptbs")
+        sc.write_ptbs(ptbs, scene)
+        t, tri, mat, rays, recs = ptref_primary_hits(ptbs, 1920, 1080, 1)
+        out = {"scene_sha256": hashlib.sha256(scene["pos"].tobytes()).hexdigest(), "tri": tri,
+               "t_sha256": hashlib.sha256(t.tobytes()).hexdigest(), "hit_fraction": float((t < np.inf).mean()),
+               "ref_bvh_ms": [r for r in recs if r["cmd"] == "primary-hits"][0]["ms"],
+               "ref_threads": [r for r in recs if r["cmd"] == "primary-hits"][0]["threads"], "two_plane_equal": -1}
+        if "--lucy-two-plane" in sys.argv:
+            t2, tri2, _, _, recs2 = ptref_primary_hits(ptbs, 1920, 1080, 2, extra=["--gs", 8, "--os", 8, "--m", 50])
+            out["two_plane_equal"] = int((t2.view(np.uint32) == t.view(np.uint32)).all() and (tri2 == tri).all())
+            out["ref_two_plane_ms"] = [r for r in recs2 if r["cmd"] == "primary-hits"][0]["ms"]
+            out["ref_two_plane_build"] = [r for r in recs2 if r["cmd"] == "build"][0]["grid_ms"]
+            out["ref_two_plane_bytes"] = [r for r in recs2 if r["cmd"] == "build"][0]["grid_bytes"]
+    np.savez_compressed(os.path.join(HERE, "lucy_standin_ref_1080p.npz"), **out)
+    print("wrote lucy_standin_ref_1080p.npz", {k: v for k, v in out.items() if k != "tri"})
+
+
 def main():
+    if "--lucy" in sys.argv:
+        return lucy()
     if not os.path.isfile(PTREF):
         raise SystemExit("oracle/_ref/ptref missing: make -C oracle ref (needs /root/reference)")
     ptbs = os.path.join(HERE, "cornel.ptbs")

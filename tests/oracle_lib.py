@@ -150,3 +150,24 @@ def ptref_trace_rays(ptbs, od, mode, extra=()):
         t = raw[: 4 * n].view(np.float32).copy()
         tri = raw[4 * n:].view(np.int32).copy()
     return t, tri, recs
+
+
+PTFACADE = os.path.join(ORACLE_DIR, "_ref", "ptfacade")
+
+
+def have_facade():
+    return os.path.isfile(PTFACADE) and os.access(PTFACADE, os.X_OK)
+
+
+def ptfacade_render(ptbs, W, H, mode, spp, max_depth=0, nee=0, extra=()):
+    """The reference's own objects with src/tracer.cpp replaced by host/tracer_facade.cpp: trace() on the GPU."""
+    with tempfile.TemporaryDirectory() as d:
+        o = os.path.join(d, "img.bin")
+        out = subprocess.run([PTFACADE] + [str(a) for a in ["--ptbs", ptbs, "--mode", mode, "--width", W, "--height", H, "--spp", spp,
+                                                           "--max-depth", max_depth, "--nee", nee, *extra, "render", o]],
+                             stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=1800)
+        if out.returncode != 0:
+            raise RuntimeError("ptfacade failed: " + out.stderr[-2000:])
+        recs = [json.loads(l[len("PTREF_JSON "):]) for l in out.stdout.splitlines() if l.startswith("PTREF_JSON ")]
+        img = np.fromfile(o, np.float32).reshape(H, W, 4)
+    return img, [r for r in recs if r["cmd"] == "render"][0]

@@ -1,0 +1,28 @@
+"""Drop-in check of the boundary: the reference's OWN compiled objects (scene.cpp, shader.cpp,
+camera.cpp, bvh.cpp ... from oracle/_ref/obj) linked with host/tracer_facade.cpp in place of
+src/tracer.cpp.  The reference-side driver calls setWindowSize / initTracer / trace(true) /
+tracerGetPixel exactly as src/main.cpp does; the frame must equal the CPU oracle's."""
+import numpy as np
+import pytest
+
+from oracle_lib import MODE_BVH, MODE_SUB_BEAMS, MODE_TWO_PLANE, Oracle, have_facade, ptfacade_render
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.skipif(not have_facade(), reason="oracle/_ref/ptfacade not built (needs the reference sources at build time)")
+@pytest.mark.parametrize("mode,nee,max_depth", [(MODE_BVH, 0, 0), (MODE_BVH, 1, 5), (MODE_TWO_PLANE, 1, 0), (MODE_SUB_BEAMS, 0, 3)])
+def test_reference_host_code_renders_through_the_facade(cornel_ptbs, ptb, mode, nee, max_depth):
+    W, H, spp = 96, 64, 3
+    img, rec = ptfacade_render(cornel_ptbs, W, H, mode, spp, max_depth, nee)
+    o = Oracle(cornel_ptbs)
+    o.build(grid=True, beams=True)
+    o.configure(W, H, mode, nee=nee, max_depth=max_depth)
+    rimg, _, _, st = o.render(spp)
+    o.close()
+    diff = np.abs(img[..., :3] - rimg[..., :3]) / np.maximum(np.abs(rimg[..., :3]), 1e-3)
+    nbits = int((img.view(np.uint32) != rimg.view(np.uint32)).any(axis=-1).sum())
+    assert diff.max() <= 2e-6 or nbits <= max(1, W * H // 2000), f"{nbits} pixels differ, max rel {diff.max():.3g}"
+    assert rec["paths"] == W * H * spp
+    if nee == 0:  # with NEE the GPU count also holds the shadow rays, which the path-ray statistic of the oracle does not
+        assert rec["rays_unique"] == st["rays_unique"], "GPU traversal count != the reference's unique-ray count"

@@ -145,3 +145,82 @@ def test_tile_partition_is_bitwise_identical(ptb, cornel_ptbs, gpu):
         acc += pt.read_image()  # non-owned pixels are exactly zero -> the sum is exact
         pt.close()
     assert (acc.view(np.uint32) == full.view(np.uint32)).all()
+
+
+def test_heat_map_view(gpu):
+    """Debug view (tracer.cpp:136-142): one ray per pixel, pixel = test count / scale.  In mode ALL every
+    ray tests every triangle (object.cpp:19-34), so the triangle heat map is flat at n_tris / scale; in
+    BVH mode the heat map must sum to the counters the same pass reports."""
+    scale = 404
+    gpu.set_params(width=W, height=H, mode=MODE_ALL, nee=0, max_depth=0, debug_view=2, debug_scale=scale, count_tests=1)
+    gpu.reset()
+    gpu.render(1)
+    img = gpu.read_image()
+    assert (img[..., 0] == np.float32(202) / np.float32(scale)).all() and (img[..., 1] == img[..., 0]).all()
+    scale = 1 << 20
+    gpu.set_params(mode=MODE_BVH, debug_view=1, debug_scale=scale)
+    gpu.reset()
+    gpu.render(1)
+    img = gpu.read_image()
+    s, _ = gpu.read_state()
+    c = gpu.counters()
+    assert (s == 1).all() and c["paths"] == W * H
+    assert int(np.rint(img[..., 0].astype(np.float64) * scale).sum()) == c["as_tests"]
+    over = 3
+    gpu.set_params(debug_view=1, debug_scale=over)
+    gpu.reset()
+    gpu.render(1)
+    red = gpu.read_image()
+    assert ((red[..., 0] == 1.0) & (red[..., 1] == 0.0)).any()  # count > scale -> red
+    gpu.set_params(debug_view=0, debug_scale=0, count_tests=0)
+
+
+def test_clear_keeps_rng_streams(gpu, oracle):
+    """reset() (tracer.cpp:195-217) zeroes image and sample counts but does not reseed: the next render
+    continues every pixel's stream, exactly like the oracle resumed from zeroed image + kept rng."""
+    gpu.set_params(width=W, height=H, mode=MODE_BVH, nee=0, max_depth=4)
+    gpu.reset()
+    gpu.render(2)
+    _, rng_a = gpu.read_state()
+    gpu.clear()
+    s, rng_b = gpu.read_state()
+    assert (s == 0).all() and (rng_a == rng_b).all() and (gpu.read_image() == 0).all()
+    gpu.render(1)
+    img = gpu.read_image()
+    oracle.configure(W, H, MODE_BVH, nee=0, max_depth=4)
+    _, _, r2, _ = oracle.render(2)
+    rimg, _, _, _ = oracle.render(1, state=(np.zeros((H, W, 4), np.float32), np.zeros(W * H, np.int32), r2.copy()))
+    rel, nbits = _img_close(img, rimg)
+    assert rel <= 2e-6 or nbits <= max(1, W * H // 2000)
+
+
+def test_camera_basis_equals_scene_camera(gpu, ptb, cornel_ptbs):
+    gpu.set_params(width=W, height=H, mode=MODE_BVH, nee=0, max_depth=3)
+    gpu.reset()
+    gpu.render(1)
+    a = gpu.read_image()
+    cam = ptb.scenes.read_ptbs(cornel_ptbs)["camera"]
+    # cornel.scene looks down +z: orthoNormalized((0,0,1),(0,1,0),(-1,0,0)) is the identity basis
+    import ctypes
+    libm = ctypes.CDLL("libm.so.6")
+    libm.tanf.restype = ctypes.c_float
+    libm.tanf.argtypes = [ctypes.c_float]
+    fov_scale = libm.tanf(ctypes.c_float(float(np.float32(np.float32(70 * np.float32(3.14)) / np.float32(180.0)) / np.float32(2.0))))
+    gpu.set_camera_basis(cam["pos"], [0, 0, 1], [-1, 0, 0], [0, 1, 0], cam["focus"], cam["dof"], fov_scale)
+    gpu.reset()
+    gpu.render(1)
+    b = gpu.read_image()
+    gpu.set_camera(cam["pos"], cam["forward"], cam["focus"], cam["dof"])
+    assert (a.view(np.uint32) == b.view(np.uint32)).all()
+
+
+def test_counters_match_oracle_ray_counts(gpu, oracle):
+    for mode in (MODE_BVH, MODE_TWO_PLANE):
+        gpu.set_params(width=W, height=H, mode=mode, nee=0, max_depth=0)
+        gpu.reset()
+        gpu.render(2)
+        c = gpu.counters()
+        oracle.configure(W, H, mode, nee=0, max_depth=0)
+        _, _, _, st = oracle.render(2)
+        assert c["rays"] == st["rays_unique"], f"mode {mode}: GPU traversals vs oracle unique rays"
+        assert c["ref_rays"] == st["rays_traversed"], f"mode {mode}: replayed reference ray count"
