@@ -15,6 +15,7 @@
 #include "ptb_bvh_build.h"
 #include "ptb_grid_build.h"
 #include "ptb_kernels.cuh"
+#include "ptb_mega.cuh"
 
 using namespace ptb;
 
@@ -24,11 +25,35 @@ const int kCtasPerSm = 8;      // persistent grid = SMs x this
 const uint32_t kRing = 1u << 14; // per-iteration queue counters kept on the device (ring)
 } // namespace
 
+// a sub-wavefront: slots [base, base+n) with their own queues, counter rings, stream and events
+struct Wave {
+    cudaStream_t stream = nullptr;
+    FrameDev F{};            // the frame with slot_base / n_slots of this wave
+    uint32_t *dQueue[2] = {nullptr, nullptr}; // views into ctx->dQueue[*] at `base`
+    uint32_t *dShadowQ = nullptr;
+    uint32_t *dCnt = nullptr, *dShCnt = nullptr, *dCursor = nullptr; // [kRing] each
+    uint32_t *hCnt = nullptr, *hShCnt = nullptr;                     // pinned mirrors
+    std::vector<cudaEvent_t> evPool;                                 // 3 per iteration of a batch (profiling)
+    cudaEvent_t evDone = nullptr;
+    bool done = false;
+    uint32_t carry = 0, carryShadow = 0;
+};
+
+struct WaveRange {
+    Wave *b, *e;
+    Wave *begin() const { return b; }
+    Wave *end() const { return e; }
+};
+
 struct ptb_ctx {
     int device = 0;
     int sms = 148;
     int extendCtas = 12; // resident 128-thread CTAs per SM of the persistent BVH extend (40 registers/thread)
     int fetchKeep = 20;
+    int useMega = 1;   // PTB_MEGA: 1 = persistent-lane path kernel (ptb_mega.cuh), 0 = wavefront pipeline (k_extend* + k_logic)
+    int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
+    int logicKeep = 28; // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
+    bool uniformSamples = true; // every owned pixel has the same sample count (false after ptb_write_state)
     int beamMaxDepth = 12; // guard on the reference's unbounded Subbeam recursion, ptb_set_build_limits  // refill a warp's idle lanes when fewer than this many are still walking
     cudaStream_t stream = nullptr;
     std::string err;
@@ -75,10 +100,11 @@ struct ptb_ctx {
     uint32_t *dSlotPixel = nullptr;
     uint32_t *dQueue[2] = {nullptr, nullptr};
     uint32_t *dShadowQ = nullptr;
-    uint32_t *dCnt = nullptr;   // [kRing] main-queue sizes per iteration
-    uint32_t *dShCnt = nullptr; // [kRing] shadow-queue sizes per iteration
-    uint32_t *dCursor = nullptr; // [kRing] work cursor of each iteration's persistent extend (dynamic ray fetch)
-    uint32_t *hCnt = nullptr, *hShCnt = nullptr; // pinned mirrors
+    uint32_t *dRings = nullptr; // maxWaves x 3 x kRing: per wave {main-queue sizes, shadow-queue sizes, extend work cursors} per iteration
+    uint32_t *hRings = nullptr; // pinned mirror, maxWaves x 2 x kRing
+    int maxWaves = 4;           // PTB_WAVES
+    std::vector<Wave> allWaves; // maxWaves of them, created once
+    int nWaves = 1;             // the first nWaves are in use (chosen per frame size in alloc_frame)
     unsigned long long *dCounters = nullptr;     // [8] paths, ref rays, tri tests, AS tests, no-extend queue entries
     int targetSamples = 0;
     uint64_t queueEntries = 0; // sum of main-queue sizes since reset
@@ -88,7 +114,6 @@ struct ptb_ctx {
     // per-stage device time (ptb_set_profiling): CUDA events around every k_extend / k_logic launch,
     // harvested at the scheduler's own batch syncs
     bool profile = false;
-    std::vector<cudaEvent_t> evPool; // 3 per iteration of a batch
     double stageMs[2] = {0.0, 0.0};  // extend, logic (since reset)
     uint64_t stageLaunches[2] = {0, 0};
     bool frameDirty = true; // params changed: (re)allocate the frame on next reset
@@ -101,6 +126,7 @@ struct ptb_ctx {
 };
 
 static std::string g_createErr = "";
+static WaveRange active_waves(ptb_ctx *c) { return WaveRange{c->allWaves.data(), c->allWaves.data() + c->nWaves}; }
 
 namespace {
 
@@ -211,12 +237,25 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     cudaEventCreate(&c->evStart);
     cudaEventCreate(&c->evStop);
-    cudaMalloc(&c->dCnt, kRing * sizeof(uint32_t));
-    cudaMalloc(&c->dShCnt, kRing * sizeof(uint32_t));
-    cudaMalloc(&c->dCursor, kRing * sizeof(uint32_t));
-    cudaMalloc(&c->dCounters, 8 * sizeof(unsigned long long));
-    cudaMallocHost(&c->hCnt, kRing * sizeof(uint32_t));
-    cudaMallocHost(&c->hShCnt, kRing * sizeof(uint32_t));
+    if (const char *e = getenv("PTB_MEGA")) c->useMega = atoi(e) != 0;
+    if (const char *e = getenv("PTB_MEGA_CTAS")) c->megaCtas = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("PTB_LOGIC_KEEP")) c->logicKeep = std::max(1, std::min(32, atoi(e)));
+    if (const char *e = getenv("PTB_WAVES")) c->maxWaves = std::max(1, std::min(16, atoi(e)));
+    cudaMalloc(&c->dRings, (size_t)c->maxWaves * 3 * kRing * sizeof(uint32_t));
+    cudaMallocHost(&c->hRings, (size_t)c->maxWaves * 2 * kRing * sizeof(uint32_t));
+    c->allWaves.resize(c->maxWaves);
+    for (int i = 0; i < c->maxWaves; ++i) {
+        Wave &w = c->allWaves[i];
+        cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking);
+        cudaEventCreateWithFlags(&w.evDone, cudaEventDisableTiming);
+        w.dCnt = c->dRings + (size_t)i * 3 * kRing;
+        w.dShCnt = w.dCnt + kRing;
+        w.dCursor = w.dShCnt + kRing;
+        w.hCnt = c->hRings + (size_t)i * 2 * kRing;
+        w.hShCnt = w.hCnt + kRing;
+    }
+    cudaMalloc(&c->dCounters, 16 * sizeof(unsigned long long));
+    cudaMemset(c->dCounters, 0, 16 * sizeof(unsigned long long));
     if ((e = cudaGetLastError()) != cudaSuccess) {
         std::string m = cudaGetErrorString(e);
         delete c;
@@ -254,13 +293,16 @@ extern "C" void ptb_destroy(ptb_ctx *c) {
     devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
     devFree(c->dBeam); devFree(c->dBeamIdx);
     for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
-    devFree(c->dCnt); devFree(c->dShCnt); devFree(c->dCursor); devFree(c->dCounters);
+    devFree(c->dRings); devFree(c->dCounters);
     devFree(c->dScratchF); devFree(c->dScratchI); devFree(c->dRays);
-    if (c->hCnt) cudaFreeHost(c->hCnt);
-    if (c->hShCnt) cudaFreeHost(c->hShCnt);
+    if (c->hRings) cudaFreeHost(c->hRings);
+    for (auto &w : c->allWaves) {
+        for (auto &e : w.evPool) cudaEventDestroy(e);
+        if (w.evDone) cudaEventDestroy(w.evDone);
+        if (w.stream) cudaStreamDestroy(w.stream);
+    }
     if (c->evStart) cudaEventDestroy(c->evStart);
     if (c->evStop) cudaEventDestroy(c->evStop);
-    for (auto &e : c->evPool) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -535,6 +577,21 @@ static int alloc_frame(ptb_ctx *c) {
     CK(cudaMalloc(&c->dShadowQ, s * sizeof(uint32_t)));
     c->F.slot_pixel = c->dSlotPixel;
     c->F.n_slots = c->nSlots;
+    c->F.slot_base = 0;
+    // waves: contiguous slot ranges (multiples of 32 so warps never straddle), at least 128 Ki slots each
+    int nw = (int)std::max<uint32_t>(1u, std::min<uint32_t>((uint32_t)c->maxWaves, c->nSlots / (128u << 10)));
+    const uint32_t per = ((c->nSlots + nw - 1) / nw + 31u) & ~31u;
+    c->nWaves = nw;
+    for (int i = 0; i < nw; ++i) {
+        Wave &w = c->allWaves[i];
+        const uint32_t base = std::min<uint32_t>(c->nSlots, (uint32_t)i * per), end = std::min<uint32_t>(c->nSlots, base + per);
+        w.F = c->F;
+        w.F.slot_base = base;
+        w.F.n_slots = end - base;
+        w.dQueue[0] = c->dQueue[0] + base;
+        w.dQueue[1] = c->dQueue[1] + base;
+        w.dShadowQ = c->dShadowQ + base;
+    }
     c->frameDirty = false;
     return PTB_OK;
 }
@@ -552,7 +609,8 @@ static int reset_frame(ptb_ctx *c, int reseed) {
         reseed = 1; // a new frame has no streams to continue
     }
     k_reset<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, c->F.samples, c->F.rng, c->W, c->H, reseed);
-    CK(cudaMemsetAsync(c->dCounters, 0, 8 * sizeof(unsigned long long), c->stream));
+    CK(cudaMemsetAsync(c->dCounters, 0, 16 * sizeof(unsigned long long), c->stream));
+    c->uniformSamples = true;
     CK(cudaStreamSynchronize(c->stream));
     c->targetSamples = 0;
     c->stageMs[0] = c->stageMs[1] = 0.0;
@@ -575,23 +633,26 @@ static int check_mode_ready(ptb_ctx *c, int mode) {
 // =============================================================================================
 namespace {
 
+// One wave = one contiguous range of slots with its own queues, counter rings and stream.  Waves are
+// independent (a slot never leaves its wave), so their iterations overlap on the device: the end of
+// wave A's extend launch — a few long rays on an otherwise empty GPU, ~0.03-0.1 ms per launch by
+// measurement — is filled by wave B's CTAs instead of idling the machine.
 template <int MODE, bool COUNT>
-void launch_iteration(ptb_ctx *c, const ParamsDev &P, uint32_t it, bool nee, int evSlot) {
+void launch_iteration(ptb_ctx *c, Wave &w, const ParamsDev &P, uint32_t it, bool nee, int evSlot) {
     // iteration `it`: extend rays of queue[it&1] (sizes dCnt[it], dShCnt[it]), then logic -> queue[(it+1)&1]
     const int g = grid_for(c);
-    if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot], c->stream);
+    if (evSlot >= 0) cudaEventRecord(w.evPool[3 * evSlot], w.stream);
     if (MODE == 1)
-        k_extend_bvh<COUNT><<<c->sms * c->extendCtas, kThreads, 0, c->stream>>>(c->S, c->F, c->dQueue[it & 1], c->dShadowQ, c->dCnt + it,
-                                                                                nee ? c->dShCnt + it : nullptr, c->dCursor + it, c->fetchKeep);
+        k_extend_bvh<COUNT><<<c->sms * c->extendCtas, kThreads, 0, w.stream>>>(c->S, w.F, w.dQueue[it & 1], w.dShadowQ, w.dCnt + it,
+                                                                               nee ? w.dShCnt + it : nullptr, w.dCursor + it, c->fetchKeep);
     else
-        k_extend<MODE, COUNT><<<g, kThreads, 0, c->stream>>>(c->S, c->F, c->dQueue[it & 1], c->dShadowQ, c->dCnt + it,
-                                                             nee ? c->dShCnt + it : nullptr);
-    if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot + 1], c->stream);
-    k_logic<MODE, false, COUNT><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, c->dQueue[it & 1], c->dCnt + it,
-                                                               c->dQueue[(it + 1) & 1], c->dCnt + it + 1,
-                                                               nee ? c->dShadowQ : nullptr, nee ? c->dShCnt + it + 1 : nullptr,
-                                                               c->dCounters);
-    if (evSlot >= 0) cudaEventRecord(c->evPool[3 * evSlot + 2], c->stream);
+        k_extend<MODE, COUNT><<<g, kThreads, 0, w.stream>>>(c->S, w.F, w.dQueue[it & 1], w.dShadowQ, w.dCnt + it,
+                                                            nee ? w.dShCnt + it : nullptr);
+    if (evSlot >= 0) cudaEventRecord(w.evPool[3 * evSlot + 1], w.stream);
+    k_logic<MODE, false, COUNT><<<g, kThreads, 0, w.stream>>>(P, c->S, c->A, w.F, w.dQueue[it & 1], w.dCnt + it, w.dQueue[(it + 1) & 1],
+                                                              w.dCnt + it + 1, nee ? w.dShadowQ : nullptr,
+                                                              nee ? w.dShCnt + it + 1 : nullptr, c->dCounters);
+    if (evSlot >= 0) cudaEventRecord(w.evPool[3 * evSlot + 2], w.stream);
 }
 
 template <int MODE, bool COUNT>
@@ -601,64 +662,90 @@ int render_mode(ptb_ctx *c, int add) {
     const bool nee = P.nee && P.n_lights > 0;
     const int g = grid_for(c);
     CK(cudaEventRecord(c->evStart, c->stream));
+    for (auto &w : active_waves(c)) CK(cudaStreamWaitEvent(w.stream, c->evStart, 0));
     uint64_t kernels = 0, iterations = 0, rays = 0, shadowRays = 0;
-    uint32_t carry = 0, carryShadow = 0; // live queue sizes entering a ring pass (the first pass is filled by START)
+    for (auto &w : active_waves(c)) {
+        w.done = false;
+        w.carry = w.carryShadow = 0;
+    }
     bool first = true;
     int batch = 8;
     for (;;) {
         // one ring pass: counters [0..kRing) zeroed, slot 1 (or 0) seeded
-        CK(cudaMemsetAsync(c->dCnt, 0, kRing * sizeof(uint32_t), c->stream));
-        CK(cudaMemsetAsync(c->dCursor, 0, kRing * sizeof(uint32_t), c->stream));
-        if (nee) CK(cudaMemsetAsync(c->dShCnt, 0, kRing * sizeof(uint32_t), c->stream));
-        uint32_t it = 0;
-        if (first) {
-            // START: every owned pixel that needs samples gets its primary ray -> queue[1], count dCnt[1]
-            k_logic<MODE, true, COUNT><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, nullptr, nullptr, c->dQueue[1], c->dCnt + 1,
-                                                                      nullptr, nullptr, c->dCounters);
-            kernels++;
-            it = 1;
-            first = false;
-        } else {
-            // continue a previous pass: the live queue is queue[0] by construction (see below)
-            CK(cudaMemcpyAsync(c->dCnt, &carry, sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-            if (nee) CK(cudaMemcpyAsync(c->dShCnt, &carryShadow, sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-            it = 0;
+        uint32_t it = first ? 1u : 0u;
+        for (auto &w : active_waves(c)) {
+            if (w.done) continue;
+            CK(cudaMemsetAsync(w.dCnt, 0, kRing * sizeof(uint32_t), w.stream));
+            CK(cudaMemsetAsync(w.dCursor, 0, kRing * sizeof(uint32_t), w.stream));
+            if (nee) CK(cudaMemsetAsync(w.dShCnt, 0, kRing * sizeof(uint32_t), w.stream));
+            if (first) {
+                // START: every owned pixel that needs samples gets its primary ray -> queue[1], count dCnt[1]
+                k_logic<MODE, true, COUNT><<<g, kThreads, 0, w.stream>>>(P, c->S, c->A, w.F, nullptr, nullptr, w.dQueue[1], w.dCnt + 1, nullptr,
+                                                                         nullptr, c->dCounters);
+                kernels++;
+            } else {
+                // continue a previous pass: the live queue is queue[0] by construction (see below)
+                CK(cudaMemcpyAsync(w.dCnt, &w.carry, sizeof(uint32_t), cudaMemcpyHostToDevice, w.stream));
+                if (nee) CK(cudaMemcpyAsync(w.dShCnt, &w.carryShadow, sizeof(uint32_t), cudaMemcpyHostToDevice, w.stream));
+            }
         }
-        bool done = false;
+        first = false;
+        bool allDone = false;
         uint32_t checked = it;
-        while (!done && it + (uint32_t)batch + 2 < kRing) {
-            for (int b = 0; b < batch; ++b, ++it) launch_iteration<MODE, COUNT>(c, P, it, nee, c->profile ? b : -1);
-            kernels += 2ull * batch;
-            CK(cudaMemcpyAsync(c->hCnt + checked, c->dCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-            if (nee) CK(cudaMemcpyAsync(c->hShCnt + checked, c->dShCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-            CK(cudaStreamSynchronize(c->stream));
-            if (c->profile)
-                for (int b = 0; b < batch; ++b) {
-                    float e = 0.0f, l = 0.0f;
-                    cudaEventElapsedTime(&e, c->evPool[3 * b], c->evPool[3 * b + 1]);
-                    cudaEventElapsedTime(&l, c->evPool[3 * b + 1], c->evPool[3 * b + 2]);
-                    c->stageMs[0] += e;
-                    c->stageMs[1] += l;
-                    c->stageLaunches[0]++;
-                    c->stageLaunches[1]++;
+        while (!allDone && it + (uint32_t)batch + 2 < kRing) {
+            const uint32_t it0 = it;
+            for (int b = 0; b < batch; ++b, ++it)
+                for (auto &w : active_waves(c))
+                    if (!w.done) {
+                        launch_iteration<MODE, COUNT>(c, w, P, it, nee, c->profile ? b : -1);
+                        kernels += 2;
+                    }
+            for (auto &w : active_waves(c)) {
+                if (w.done) continue;
+                CK(cudaMemcpyAsync(w.hCnt + checked, w.dCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, w.stream));
+                if (nee) CK(cudaMemcpyAsync(w.hShCnt + checked, w.dShCnt + checked, (it + 1 - checked) * sizeof(uint32_t), cudaMemcpyDeviceToHost, w.stream));
+            }
+            allDone = true;
+            for (auto &w : active_waves(c)) {
+                if (w.done) continue;
+                CK(cudaStreamSynchronize(w.stream));
+                if (c->profile)
+                    for (uint32_t b = 0; b < it - it0; ++b) {
+                        float e = 0.0f, l = 0.0f;
+                        cudaEventElapsedTime(&e, w.evPool[3 * b], w.evPool[3 * b + 1]);
+                        cudaEventElapsedTime(&l, w.evPool[3 * b + 1], w.evPool[3 * b + 2]);
+                        c->stageMs[0] += e;
+                        c->stageMs[1] += l;
+                        c->stageLaunches[0]++;
+                        c->stageLaunches[1]++;
+                    }
+                uint32_t live = 0;
+                for (uint32_t k = checked; k < it; ++k) {
+                    rays += w.hCnt[k];
+                    if (nee) shadowRays += w.hShCnt[k];
+                    live = std::max(live, w.hCnt[k]);
                 }
-            for (uint32_t k = checked; k < it; ++k) {
-                rays += c->hCnt[k];
-                if (nee) shadowRays += c->hShCnt[k];
-                if (c->hCnt[k]) iterations++;
+                if (live && &w == c->allWaves.data()) iterations += it - checked;
+                if (w.hCnt[it] == 0 && (!nee || w.hShCnt[it] == 0)) w.done = true;
+                else allDone = false;
             }
             checked = it;
-            if (c->hCnt[it] == 0 && (!nee || c->hShCnt[it] == 0)) done = true;
             if (batch < 64) batch *= 2;
         }
-        if (done) break;
+        if (allDone) break;
         // ring exhausted: make the live queue queue[0] for the next pass
-        carry = c->hCnt[it];
-        if (it & 1) {
-            CK(cudaMemcpyAsync(c->dQueue[0], c->dQueue[1], (size_t)carry * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
+        for (auto &w : active_waves(c)) {
+            if (w.done) continue;
+            w.carry = w.hCnt[it];
+            if (it & 1) CK(cudaMemcpyAsync(w.dQueue[0], w.dQueue[1], (size_t)w.carry * sizeof(uint32_t), cudaMemcpyDeviceToDevice, w.stream));
+            w.carryShadow = nee ? w.hShCnt[it] : 0u; // the single shadow queue buffer is position independent
+            CK(cudaStreamSynchronize(w.stream));
         }
-        carryShadow = nee ? c->hShCnt[it] : 0u; // the single shadow queue buffer is position independent
-        CK(cudaStreamSynchronize(c->stream));
+    }
+    // everything the waves did is ordered before whatever follows on the context's stream
+    for (auto &w : active_waves(c)) {
+        CK(cudaEventRecord(w.evDone, w.stream));
+        CK(cudaStreamWaitEvent(c->stream, w.evDone, 0));
     }
     CK(cudaEventRecord(c->evStop, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -679,8 +766,57 @@ int render_mode(ptb_ctx *c, int add) {
     return PTB_OK;
 }
 
+// One launch per render: the persistent-lane path kernel of ptb_mega.cuh.
+template <int MODE, bool COUNT>
+int render_mega(ptb_ctx *c, int add) {
+    const int first = c->targetSamples;
+    c->targetSamples += add;
+    const ParamsDev P = make_params(c);
+    const int grid = c->sms * c->megaCtas;
+    const uint64_t lanes = (uint64_t)grid * kThreads;
+    MegaArgs M{};
+    // sample-granular work items (the frame ends within one path of all lanes; a lane whose pixel's previous
+    // sample is still in flight parks the item), or one item per pixel for non-uniform resumed state
+    (void)lanes;
+    const bool chunked = c->uniformSamples && (uint64_t)c->nSlots * (uint64_t)add < (1ull << 32);
+    M.chunk_samples = chunked ? 1u : (uint32_t)add;
+    M.n_items = chunked ? c->nSlots * (uint32_t)add : c->nSlots;
+    M.first_sample = first;
+    M.check_ready = chunked ? 1 : 0;
+    M.logic_keep = c->logicKeep;
+    M.cursor = c->dCounters + 8;
+    M.counters = c->dCounters;
+    CK(cudaMemsetAsync(c->dCounters + 8, 0, sizeof(unsigned long long), c->stream));
+    CK(cudaEventRecord(c->evStart, c->stream));
+    k_mega<MODE, COUNT><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+    CK(cudaEventRecord(c->evStop, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, c->evStart, c->evStop);
+    c->lastMs = ms;
+    c->stageMs[0] += ms; // one fused stage
+    c->stageLaunches[0]++;
+    unsigned long long dc[16];
+    CK(cudaMemcpy(dc, c->dCounters, sizeof dc, cudaMemcpyDeviceToHost));
+    c->counters[PTB_CNT_SHADOW_RAYS] = dc[6];
+    c->counters[PTB_CNT_RAYS] = dc[5] + dc[6];
+    c->counters[PTB_CNT_ITERATIONS] += 1;
+    c->counters[PTB_CNT_KERNELS] += 1;
+    c->counters[PTB_CNT_PATHS] = dc[0];
+    c->counters[PTB_CNT_REF_RAYS] = dc[1] + dc[6];
+    c->counters[PTB_CNT_TRI_TESTS] = dc[2];
+    c->counters[PTB_CNT_AS_TESTS] = dc[3];
+    return PTB_OK;
+}
+
 template <bool COUNT>
 int render_dispatch(ptb_ctx *c, int add) {
+    if (c->useMega) switch (c->prm.mode) {
+        case PTB_MODE_ALL: return render_mega<0, COUNT>(c, add);
+        case PTB_MODE_BVH: return render_mega<1, COUNT>(c, add);
+        case PTB_MODE_TWO_PLANE: return render_mega<2, COUNT>(c, add);
+        default: return render_mega<3, COUNT>(c, add);
+        }
     switch (c->prm.mode) {
     case PTB_MODE_ALL: return render_mode<0, COUNT>(c, add);
     case PTB_MODE_BVH: return render_mode<1, COUNT>(c, add);
@@ -717,10 +853,12 @@ extern "C" void *ptb_stream(ptb_ctx *c) { return c ? (void *)c->stream : nullptr
 
 extern "C" int ptb_set_profiling(ptb_ctx *c, int on) {
     GUARD(c);
-    if (on && c->evPool.empty()) {
-        c->evPool.resize(3 * 64);
-        for (auto &e : c->evPool) CK(cudaEventCreate(&e));
-    }
+    if (on)
+        for (auto &w : c->allWaves)
+            if (w.evPool.empty()) {
+                w.evPool.resize(3 * 64);
+                for (auto &e : w.evPool) CK(cudaEventCreate(&e));
+            }
     c->profile = on != 0;
     return PTB_OK;
 }
@@ -789,13 +927,21 @@ extern "C" int ptb_trace_rays_device(ptb_ctx *c, const float *od6, uint64_t n, i
     if (!od6 || !t || !tri) return fail(c, PTB_ERR_INVALID, "null ray / result pointers");
     const int g = (int)std::min<uint64_t>((uint64_t)grid_for(c), (n + 127) / 128);
     const bool count = c->prm.count_tests != 0;
+    CK(cudaMemsetAsync(c->dCounters + 7, 0, sizeof(unsigned long long), c->stream));
+    if (count) CK(cudaMemsetAsync(c->dCounters + 2, 0, 2 * sizeof(unsigned long long), c->stream)); // test counters = this call's
     CK(cudaEventRecord(c->evStart, c->stream));
 #define PTB_TRACE(M)                                                                                                    \
     if (count) k_trace<M, true><<<g, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters);             \
     else k_trace<M, false><<<g, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters)
     switch (mode) {
     case PTB_MODE_ALL: PTB_TRACE(0); break;
-    case PTB_MODE_BVH: PTB_TRACE(1); break;
+    case PTB_MODE_BVH: {
+        unsigned long long *cur = c->dCounters + 7; // slot 7 of the counter block: work cursor of this launch (zeroed above)
+        const int gp = (int)std::min<uint64_t>((uint64_t)c->sms * c->extendCtas, (n + 127) / 128);
+        if (count) k_trace_bvh<true><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep);
+        else k_trace_bvh<false><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep);
+        break;
+    }
     case PTB_MODE_TWO_PLANE: PTB_TRACE(2); break;
     default: PTB_TRACE(3); break;
     }
@@ -863,6 +1009,7 @@ extern "C" int ptb_write_state(ptb_ctx *c, const float *rgba, const int32_t *sam
     int mx = 0;
     for (size_t i = 0; i < n; ++i) mx = std::max(mx, samples[i]);
     c->targetSamples = mx;
+    c->uniformSamples = false;
     return PTB_OK;
 }
 
@@ -931,6 +1078,8 @@ extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
     leaf_positions(c, leaf);
     SubbeamResult R;
     build_subbeams(leaf.data(), c->mat.size(), c->bvh.lo, c->bvh.hi, gs, m, c->beamMaxDepth, R);
+    if (R.beams.size() >= (1ull << 32) || R.idx.size() >= (1ull << 32))
+        return fail(c, PTB_ERR_INVALID, "Subbeam pools exceed 2^32 entries: lower beam_max_depth (ptb_set_build_limits) or the grid size");
     devFree(c->dBeam); devFree(c->dBeamIdx);
     for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
     CK(cudaMalloc(&c->dBeam, std::max<size_t>(1, R.beams.size()) * sizeof(BeamRec)));

@@ -56,7 +56,8 @@ struct FrameDev {
     int *samples;       // [W*H]
     uint32_t *rng;      // [W*H]
     const uint32_t *slot_pixel; // [n_slots] pixel index y*W+x of each owned slot
-    uint32_t n_slots;
+    uint32_t n_slots;        // slots of this wave: [slot_base, slot_base + n_slots)
+    uint32_t slot_base;
     float4 *ray_o, *ray_d;  // [n_slots] origin / direction of the ray being extended
     float4 *hit;            // [n_slots] (t, tri bits, u, v)
     float4 *tp;             // [n_slots] throughput.xyz, depth bits
@@ -404,7 +405,7 @@ __global__ void __launch_bounds__(128, PTB_LOGIC_MINBLOCKS) k_logic(ParamsDev P,
         bool cont = false, shadow = false, noExtend = false;
         uint32_t slot = 0;
         if (valid) {
-            slot = START ? e : (qin[e] & ~PTB_Q_NOEXTEND);
+            slot = START ? (F.slot_base + e) : (qin[e] & ~PTB_Q_NOEXTEND);
             const uint32_t pixel = F.slot_pixel[slot];
             PathState ps;
             ps.rng = F.rng[pixel];
@@ -604,6 +605,69 @@ __global__ void __launch_bounds__(128) k_trace(SceneDev S, const float *__restri
             cAS += __shfl_down_sync(0xffffffffu, cAS, off);
         }
         if ((threadIdx.x & 31) == 0) {
+            if (cTri) atomicAdd(&counters[2], cTri);
+            if (cAS) atomicAdd(&counters[3], cAS);
+        }
+    }
+}
+
+// ptb_trace_rays in BVH mode: the persistent dynamic-fetch loop of k_extend_bvh over caller rays.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_trace_bvh(SceneDev S, const float *__restrict__ od6, uint64_t n, float *__restrict__ tOut,
+                                                   int *__restrict__ triOut, const uint32_t *__restrict__ idOfTri,
+                                                   unsigned long long *__restrict__ counters, unsigned long long *__restrict__ cursor,
+                                                   int fetchKeep) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    BvhWalk w;
+    int2 stack[PTB_STACK];
+    bool active = false, more = true;
+    uint64_t ray = 0;
+    uint32_t nTri = 0, nAS = 0;
+    unsigned long long cTri = 0, cAS = 0;
+    for (;;) {
+        const unsigned idle = __ballot_sync(full, !active);
+        if (more && idle) {
+            const int leader = __ffs(idle) - 1;
+            const unsigned long long want = (unsigned long long)__popc(idle);
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(cursor, want);
+            base = __shfl_sync(full, base, leader);
+            if (base + want >= n) more = false;
+            if (!active) {
+                const uint64_t e = base + (uint64_t)__popc(idle & ((1u << lane) - 1u));
+                if (e < n) {
+                    ray = e;
+                    const float2 *r = reinterpret_cast<const float2 *>(od6 + 6 * e); // 24-byte records are 8-byte aligned
+                    const float2 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2);
+                    w.begin(S, mk3(a.x, a.y, b.x), mk3(b.y, c.x, c.y), Hit{PTB_INF, -1, 0.0f, 0.0f, -1});
+                    nTri = nAS = 0;
+                    active = true;
+                }
+            }
+        }
+        unsigned act = __ballot_sync(full, active);
+        if (!act) {
+            if (!more) break;
+            continue;
+        }
+        do {
+            if (active && !w.round<COUNT>(S, stack, nTri, nAS)) {
+                tOut[ray] = w.h.t;
+                triOut[ray] = w.h.tri >= 0 ? (int)idOfTri[w.h.tri] : -1;
+                cTri += nTri;
+                cAS += nAS;
+                active = false;
+            }
+            act = __ballot_sync(full, active);
+        } while (act && (!more || __popc(act) >= fetchKeep));
+    }
+    if (COUNT) {
+        for (int off = 16; off > 0; off >>= 1) {
+            cTri += __shfl_down_sync(full, cTri, off);
+            cAS += __shfl_down_sync(full, cAS, off);
+        }
+        if (lane == 0) {
             if (cTri) atomicAdd(&counters[2], cTri);
             if (cAS) atomicAdd(&counters[3], cAS);
         }

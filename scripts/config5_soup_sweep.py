@@ -1,0 +1,58 @@
+#!/usr/bin/env python
+"""BASELINE config 5: triangle-soup sweep, incoherent rays, traversal Mrays/s and algorithmic GB/s per
+structure.  usage: config5_soup_sweep.py [max_log10_n=7] [log2_rays=24].  Writes gpurun_out/config5.json."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import ptb_b200  # noqa: E402
+
+max_log = int(sys.argv[1]) if len(sys.argv) > 1 else 7
+nrays = 1 << (int(sys.argv[2]) if len(sys.argv) > 2 else 24)
+sc = ptb_b200.scenes
+rays = torch.from_numpy(sc.soup_rays(nrays)).cuda()
+t_out = torch.empty(nrays, dtype=torch.float32, device="cuda")
+tri_out = torch.empty(nrays, dtype=torch.int32, device="cuda")
+res = []
+for lg in range(4, max_log + 1):
+    n = 10 ** lg
+    t0 = time.perf_counter()
+    scene = sc.triangle_soup(n)
+    gen_s = time.perf_counter() - t0
+    pt = ptb_b200.PathTracer(0)
+    sc.upload_scene(pt, scene)
+    del scene
+    structs = [("BVH", 1, lambda: pt.build_bvh())]
+    if lg <= 5:
+        structs.append(("Subgrid gs6 os4 m40", 2, lambda: pt.build_subgrid(6, 4, 40)))
+    if lg <= 4:
+        structs.append(("Subbeams gs4 m40 depth2", 3, lambda: pt.build_subbeams(4, 40, max_depth=2)))
+    for name, mode, build in structs:
+        t0 = time.perf_counter()
+        build()
+        bs = time.perf_counter() - t0
+        pt.set_params(width=64, height=64, mode=mode, count_tests=1)
+        sub = min(nrays, 1 << 20)
+        pt.trace_rays_device(rays.data_ptr(), sub, mode, t_out.data_ptr(), tri_out.data_ptr())
+        c = pt.counters()
+        boxes, tris = c["as_tests"] / sub, c["tri_tests"] / sub
+        pt.set_params(count_tests=0)
+        ms = []
+        for _ in range(4):
+            ms.append(pt.trace_rays_device(rays.data_ptr(), nrays, mode, t_out.data_ptr(), tri_out.data_ptr()))
+        best = min(ms[1:])
+        bpr = 24 + 8 + 32 * boxes + 36 * tris
+        rec = {"n": n, "structure": name, "build_s": bs, "bytes": pt.structure_bytes(mode), "ms": best, "mrays_s": nrays / best / 1e3,
+               "as_tests_per_ray": boxes, "tri_tests_per_ray": tris, "algorithmic_bytes_per_ray": bpr,
+               "algorithmic_gb_s": bpr * nrays / best / 1e6, "hit_fraction": float((t_out < float("inf")).float().mean())}
+        res.append(rec)
+        print(rec, flush=True)
+    pt.close()
+os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+json.dump(res, open(os.path.join(ROOT, "gpurun_out", "config5.json"), "w"), indent=1)
