@@ -33,7 +33,7 @@ class Camera(ctypes.Structure):
 class Params(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "width", "height", "mode", "nee", "primary_only", "max_depth", "reference_quirks", "debug_view", "debug_scale",
-        "rank", "world", "tile_w", "tile_h", "count_tests")]
+        "rank", "world", "tile_w", "tile_h", "count_tests", "seed_offset")]
 
 
 class PtbError(RuntimeError):

@@ -52,7 +52,8 @@ struct ptb_ctx {
     int fetchKeep = 20;
     int useMega = 1;   // PTB_MEGA: 1 = persistent-lane path kernel (ptb_mega.cuh), 0 = wavefront pipeline (k_extend* + k_logic)
     int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
-    int logicKeep = 28; // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
+    int logicKeep = 28;
+    int megaChunk = 0;  // PTB_MEGA_CHUNK: samples per work item, 0 = chosen from pixels/lanes // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
     bool uniformSamples = true; // every owned pixel has the same sample count (false after ptb_write_state)
     int beamMaxDepth = 12; // guard on the reference's unbounded Subbeam recursion, ptb_set_build_limits  // refill a warp's idle lanes when fewer than this many are still walking
     cudaStream_t stream = nullptr;
@@ -239,6 +240,7 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     cudaEventCreate(&c->evStop);
     if (const char *e = getenv("PTB_MEGA")) c->useMega = atoi(e) != 0;
     if (const char *e = getenv("PTB_MEGA_CTAS")) c->megaCtas = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("PTB_MEGA_CHUNK")) c->megaChunk = std::max(0, atoi(e));
     if (const char *e = getenv("PTB_LOGIC_KEEP")) c->logicKeep = std::max(1, std::min(32, atoi(e)));
     if (const char *e = getenv("PTB_WAVES")) c->maxWaves = std::max(1, std::min(16, atoi(e)));
     cudaMalloc(&c->dRings, (size_t)c->maxWaves * 3 * kRing * sizeof(uint32_t));
@@ -608,7 +610,8 @@ static int reset_frame(ptb_ctx *c, int reseed) {
         if (r) return r;
         reseed = 1; // a new frame has no streams to continue
     }
-    k_reset<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, c->F.samples, c->F.rng, c->W, c->H, reseed);
+    k_reset<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, c->F.samples, c->F.rng, c->W, c->H, reseed,
+                                                     (uint32_t)c->prm.seed_offset * 0x9E3779B9u);
     CK(cudaMemsetAsync(c->dCounters, 0, 16 * sizeof(unsigned long long), c->stream));
     c->uniformSamples = true;
     CK(cudaStreamSynchronize(c->stream));
@@ -772,15 +775,22 @@ int render_mega(ptb_ctx *c, int add) {
     const int first = c->targetSamples;
     c->targetSamples += add;
     const ParamsDev P = make_params(c);
-    const int grid = c->sms * c->megaCtas;
+    // no more lanes than owned pixels: a pixel's samples are serial, so pixels bound the parallelism
+    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * c->megaCtas, ((uint64_t)c->nSlots + kThreads - 1) / kThreads));
     const uint64_t lanes = (uint64_t)grid * kThreads;
     MegaArgs M{};
-    // sample-granular work items (the frame ends within one path of all lanes; a lane whose pixel's previous
-    // sample is still in flight parks the item), or one item per pixel for non-uniform resumed state
-    (void)lanes;
-    const bool chunked = c->uniformSamples && (uint64_t)c->nSlots * (uint64_t)add < (1ull << 32);
-    M.chunk_samples = chunked ? 1u : (uint32_t)add;
-    M.n_items = chunked ? c->nSlots * (uint32_t)add : c->nSlots;
+    // Work items are (pixel, chunk of samples); a lane whose pixel's previous chunk is still in flight parks
+    // the item.  With many more pixels than lanes that never happens and 1-sample chunks end the frame within
+    // one path of all lanes; when pixels are scarce (small frames, 1/N of a frame per GPU) longer chunks make
+    // hand-offs rare at the price of a tail of `chunk` paths.  Non-uniform resumed state: one item per pixel.
+    const uint64_t ratio = (uint64_t)c->nSlots / lanes;
+    uint32_t chunk = ratio >= 2 ? 1u : 8u; // profiles/r1_sweep_mega_chunk.txt: 1-sample items keep neighbouring pixels in step (coherent primary rays)
+    if (c->megaChunk > 0) chunk = (uint32_t)c->megaChunk;
+    chunk = std::min<uint32_t>(chunk, (uint32_t)add);
+    const uint32_t nChunks = ((uint32_t)add + chunk - 1) / chunk;
+    const bool chunked = c->uniformSamples && (uint64_t)c->nSlots * (uint64_t)nChunks < (1ull << 32);
+    M.chunk_samples = chunked ? chunk : (uint32_t)add;
+    M.n_items = chunked ? c->nSlots * nChunks : c->nSlots;
     M.first_sample = first;
     M.check_ready = chunked ? 1 : 0;
     M.logic_keep = c->logicKeep;

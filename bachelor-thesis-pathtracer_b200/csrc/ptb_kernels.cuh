@@ -695,12 +695,12 @@ __global__ void __launch_bounds__(128) k_primary(ParamsDev P, SceneDev S, AttrDe
 
 // initTracer (tracer.cpp:227-244) for a W x H frame
 // reseed = 0: reset() (tracer.cpp:195-217) — image and sample counts only, the RNG streams continue
-__global__ void k_reset(float4 *image, int *samples, uint32_t *rng, int W, int H, int reseed) {
+__global__ void k_reset(float4 *image, int *samples, uint32_t *rng, int W, int H, int reseed, uint32_t seedAdd) {
     const uint32_t n = (uint32_t)W * (uint32_t)H;
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         image[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         samples[p] = 0;
-        if (reseed) rng[p] = hash_coords((int)(p % (uint32_t)W), (int)(p / (uint32_t)W));
+        if (reseed) rng[p] = hash_coords((int)(p % (uint32_t)W), (int)(p / (uint32_t)W)) + seedAdd;
     }
 }
 

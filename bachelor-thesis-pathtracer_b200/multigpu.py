@@ -54,3 +54,27 @@ def reduce_image(image, dst=0, group=None):
 def configure_rank(pt, rank, world, tile_w=TILE_W, tile_h=TILE_H, **params):
     """ptb_set_params with this rank's share of the frame."""
     pt.set_params(rank=rank, world=world, tile_w=tile_w, tile_h=tile_h, **params)
+
+
+# ---- sample-range sharding (opt-in) -----------------------------------------------------------------
+# When 1/N of the frame leaves a GPU fewer pixels than lanes, tile sharding starves it: the samples of a
+# pixel are serial in the reference (RNG stream + order-dependent running mean), so pixels bound the
+# parallelism.  Sample-range sharding gives every rank ALL pixels and spp/N of the samples from its own
+# seeds (ptb_params.seed_offset = rank; rank 0 keeps the reference's seeds).  The result is the same
+# estimator with different random numbers: parity is statistical (per-pixel RMSE), not bitwise.
+def sample_share(spp, rank, world):
+    """Samples rank `rank` takes out of `spp` (differences of at most one)."""
+    return spp // world + (1 if rank < spp % world else 0)
+
+
+def combine_sample_shards(image, n_local, n_total, dst=0, group=None):
+    """Each rank holds the reference's running mean over its n_local samples, sum(L)/(n_local+1)
+    (tracer.cpp:147-154).  Rebuild sum(L), sum-reduce, and apply the same law over all samples:
+    sum(L)/(n_total+1).  In place; the result is valid on `dst`."""
+    import torch.distributed as dist
+    image.mul_(float(n_local + 1))
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.reduce(image, dst=dst, op=dist.ReduceOp.SUM, group=group)
+    image.div_(float(n_total + 1))
+    image[..., 3] = 1.0
+    return image

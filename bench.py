@@ -203,7 +203,19 @@ def run_ours(args):
     t0 = time.perf_counter()
     pt.build_bvh()
     build_s = time.perf_counter() - t0
-    base = dict(width=W, height=H, mode=mode, nee=0, max_depth=wl["max_depth"], rank=rank, world=world, tile_w=32, tile_h=8)
+    # Sharding: tiles (bit-identical to the 1-GPU frame) while every GPU keeps >= 400k pixels in flight; below
+    # that the serial samples of a pixel starve the lanes and the frame is sharded by sample ranges instead
+    # (every rank renders all pixels, spp/N samples from its own seeds; statistical parity)
+    shard = args.shard
+    if shard == "auto":
+        shard = "tiles" if world == 1 or (W * H) // world >= 400_000 else "samples"
+    if shard == "samples" and world > 1:
+        base = dict(width=W, height=H, mode=mode, nee=0, max_depth=wl["max_depth"], rank=0, world=1, tile_w=32, tile_h=8, seed_offset=rank)
+        my_spp = ptb_b200.multigpu.sample_share(spp, rank, world)
+    else:
+        shard = "tiles"
+        base = dict(width=W, height=H, mode=mode, nee=0, max_depth=wl["max_depth"], rank=rank, world=world, tile_w=32, tile_h=8)
+        my_spp = spp
     stream = torch.cuda.ExternalStream(pt.stream_handle(), device=local)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")  # > 126 MB L2
 
@@ -217,7 +229,10 @@ def run_ours(args):
             return
         img = ptb_b200.multigpu.device_image_tensor(pt)
         with torch.cuda.stream(stream):
-            ptb_b200.multigpu.reduce_image(img, dst=0)
+            if shard == "samples":
+                ptb_b200.multigpu.combine_sample_shards(img, my_spp, spp, dst=0)
+            else:
+                ptb_b200.multigpu.reduce_image(img, dst=0)
 
     # instrumented pass (outside the timed region): the per-ray visit counts behind the algorithmic bytes
     pt.set_params(count_tests=1, **base)
@@ -233,7 +248,7 @@ def run_ours(args):
 
     def step():
         pt.reset()
-        pt.render(spp)
+        pt.render(my_spp)
         reduce_frame()
 
     for _ in range(args.warmup):
@@ -270,7 +285,7 @@ def run_ours(args):
         pt.set_camera(cam["pos"], cam["forward"], cam["focus"], cam["dof"])
         pt.set_params(count_tests=0, **base)
         pt.reset()
-        pt.render(spp)
+        pt.render(my_spp)
         reduce_frame()
         if rank == 0:
             pt.L.ptb_read_image(pt.h, host_img.ctypes.data)        # D2H: the fp32 frame
@@ -306,7 +321,9 @@ def run_ours(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["name"], "width": W, "height": H, "spp": spp, "max_depth": wl["max_depth"], "nee": 0,
                        "structure": "BVH2, 64-byte two-box nodes", "triangles": int(scene["pos"].shape[0]),
-                       "parallelism": f"tiles32x8 round-robin over {world} GPU(s), NCCL sum-reduce to rank 0" if world > 1 else "1 GPU",
+                       "parallelism": "1 GPU" if world == 1 else (f"tiles32x8 round-robin over {world} GPUs, NCCL sum-reduce to rank 0 (bit-identical to 1 GPU)"
+                                                                 if shard == "tiles" else
+                                                                 f"sample ranges: {world} GPUs x all pixels x spp/{world} from per-rank seeds, NCCL sum-reduce (statistical parity)"),
                        "l2": "flushed between timed steps (512 MiB fill)", "bvh_build_s": round(build_s, 3)},
             "spp_per_s": spp * args.steps / (dev_ms_max / 1e3),
             "mpaths_per_s": paths_all / (dev_ms_max / 1e3) / 1e6,
@@ -344,18 +361,24 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-spp", type=int, default=8, help="spp of the bounded cpu_baseline sample")
     ap.add_argument("--ref-spp", type=int, default=4, help="spp per step of the --impl reference arm")
+    ap.add_argument("--shard", default="auto", choices=["auto", "tiles", "samples"], help="multi-GPU partition of the frame")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--res", default="", help="override the frame size WxH (experiments only)")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (profiling runs only)")
     args = ap.parse_args()
     if args.spp > 0:
         WORKLOADS[args.workload] = dict(WORKLOADS[args.workload], spp=args.spp,
                                         name=WORKLOADS[args.workload]["name"] + f" [spp overridden to {args.spp}]")
+    if args.res:
+        rw, rh = (int(v) for v in args.res.lower().split("x"))
+        WORKLOADS[args.workload] = dict(WORKLOADS[args.workload], W=rw, H=rh,
+                                        name=WORKLOADS[args.workload]["name"] + f" [frame overridden to {rw}x{rh}]")
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
     if args.impl == "reference":

@@ -61,6 +61,9 @@ typedef struct ptb_params {
      * (ty*tiles_x + tx) % world.  world = 1 -> the whole frame. */
     int32_t rank, world, tile_w, tile_h;
     int32_t count_tests;      /* 1: accumulate the reference's two counters (tracer.cpp:131-132) */
+    /* sample-range sharding (opt-in; statistical parity only): ptb_reset seeds pixel (x,y) with
+     * (x<<16|y) + seed_offset * 0x9E3779B9.  0 = the reference's seeds (tracer.cpp:240). */
+    int32_t seed_offset;
 } ptb_params;
 
 /* counters, ptb_read_counters */

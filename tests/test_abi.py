@@ -25,9 +25,9 @@ def test_header_symbols_are_exported(ptb):
 
 
 def test_struct_sizes_match_header(ptb):
-    # ptb_camera: 9 floats; ptb_params: 14 int32 (include/ptb.h)
+    # ptb_camera: 9 floats; ptb_params: 15 int32 (include/ptb.h)
     assert ctypes.sizeof(ptb.Camera) == 36
-    assert ctypes.sizeof(ptb.Params) == 14 * 4
+    assert ctypes.sizeof(ptb.Params) == 15 * 4
 
 
 def test_create_fails_loudly_without_gpu(ptb):

@@ -224,3 +224,35 @@ def test_counters_match_oracle_ray_counts(gpu, oracle):
         _, _, _, st = oracle.render(2)
         assert c["rays"] == st["rays_unique"], f"mode {mode}: GPU traversals vs oracle unique rays"
         assert c["ref_rays"] == st["rays_traversed"], f"mode {mode}: replayed reference ray count"
+
+
+def test_sample_sharded_frame_is_statistically_equivalent(gpu, ptb):
+    """Opt-in sample-range sharding (multigpu.combine_sample_shards): 4 shards x 16 spp from per-shard seeds
+    against single 64-spp frames from three other seed sets and a 2048-spp reference.  Stated bar: per-pixel
+    RMSE of linear radiance (clamped to 4 to keep single fireflies from deciding the test) against the
+    reference no worse than 1.15x the worst of the single runs — same estimator, different random numbers."""
+    mg = ptb.multigpu
+    Wd = Hd = 96
+    spp, shards = 64, 4
+
+    def frame(n, seed_offset):
+        gpu.set_params(width=Wd, height=Hd, mode=MODE_BVH, nee=1, max_depth=5, seed_offset=seed_offset)
+        gpu.reset()
+        gpu.render(n)
+        return gpu.read_image().astype(np.float64)[..., :3] * (n + 1) / n  # undo the N+1 law
+
+    def rmse(a, b):
+        return float(np.sqrt(((np.minimum(a, 4.0) - np.minimum(b, 4.0)) ** 2).mean()))
+
+    ref = frame(2048, 99)
+    singles = [rmse(frame(spp, s), ref) for s in (0, 21, 22)]
+    total = np.zeros_like(ref)
+    for r in range(shards):
+        n = mg.sample_share(spp, r, shards)
+        total += frame(n, r) * n
+    sharded = total / spp
+    gpu.set_params(seed_offset=0)
+    r_sh = rmse(sharded, ref)
+    print(f"RMSE vs 2048 spp: single 64-spp runs {singles}, 4 sample shards {r_sh:.4f}")
+    assert r_sh <= 1.15 * max(singles)
+    assert abs(sharded.mean() - ref.mean()) <= 0.03 * ref.mean()

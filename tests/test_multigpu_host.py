@@ -62,3 +62,60 @@ def test_two_rank_reduce_reproduces_full_frame(tmp_path, cornel_ptbs, ptb):
     out = str(tmp_path / "result.txt")
     mp.spawn(_worker, args=(2, port, cornel_ptbs, out), nprocs=2, join=True)
     assert open(out).read() == "ok"
+
+
+def _worker_samples(rank, world, port, ptbs, out):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch
+    import torch.distributed as dist
+    import ptb_b200
+    from oracle_lib import MODE_BVH, Oracle
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    mg = ptb_b200.multigpu
+    W, H, spp = 48, 32, 7
+    o = Oracle(ptbs)
+    o.build()
+    o.configure(W, H, MODE_BVH, nee=1, max_depth=4)
+    yy, xx = np.mgrid[0:H, 0:W]
+    seeds = ((xx.astype(np.uint32) << 16) | yy.astype(np.uint32)).reshape(-1)
+
+    def shard(r):  # what rank r renders: all pixels, its share of the samples, seeds offset by r (ptb_params.seed_offset)
+        n = mg.sample_share(spp, r, world)
+        rng = (seeds + np.uint32((r * 0x9E3779B9) & 0xFFFFFFFF)).astype(np.uint32)
+        img, _, _, _ = o.render(n, state=(np.zeros((H, W, 4), np.float32), np.zeros(W * H, np.int32), rng))
+        return img.copy(), n
+
+    mine, n_local = shard(rank)
+    t = torch.from_numpy(mine.copy())
+    mg.combine_sample_shards(t, n_local, spp, dst=0)
+    if rank == 0:
+        total = np.zeros((H, W, 4), np.float64)
+        for r in range(world):
+            img, n = shard(r)
+            total += img.astype(np.float64) * (n + 1)
+        want = total / (spp + 1)
+        got = t.numpy().astype(np.float64)
+        ok = np.allclose(got[..., :3], want[..., :3], rtol=1e-5, atol=1e-6) and (got[..., 3] == 1.0).all()
+        # rank 0 alone reproduces the reference's own first samples (seed_offset 0)
+        ref, _, _, _ = o.render(n_local)
+        ok = ok and (ref.view(np.uint32) == mine.view(np.uint32)).all()
+        open(out, "w").write("ok" if ok else "mismatch")
+    o.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sample_range_sharding_combines_to_the_n_plus_1_law(tmp_path, cornel_ptbs, ptb):
+    import torch.multiprocessing as mp
+    assert [ptb.multigpu.sample_share(7, r, 2) for r in range(2)] == [4, 3]
+    assert sum(ptb.multigpu.sample_share(64, r, 8) for r in range(8)) == 64
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    out = str(tmp_path / "result.txt")
+    mp.spawn(_worker_samples, args=(2, port, cornel_ptbs, out), nprocs=2, join=True)
+    assert open(out).read() == "ok"
