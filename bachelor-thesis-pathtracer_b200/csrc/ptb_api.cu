@@ -16,6 +16,11 @@
 #include "ptb_grid_build.h"
 #include "ptb_kernels.cuh"
 #include "ptb_mega.cuh"
+#include "ptb_pool.cuh"
+
+#ifndef PTB_POOL_NP
+#define PTB_POOL_NP 64 /* paths per warp pool */
+#endif
 
 using namespace ptb;
 
@@ -50,7 +55,10 @@ struct ptb_ctx {
     int sms = 148;
     int extendCtas = 12; // resident 128-thread CTAs per SM of the persistent BVH extend (40 registers/thread)
     int fetchKeep = 20;
-    int useMega = 1;   // PTB_MEGA: 1 = persistent-lane path kernel (ptb_mega.cuh), 0 = wavefront pipeline (k_extend* + k_logic)
+    int useMega = 1;   // PTB_MEGA: 2 = warp-pool path kernel (ptb_pool.cuh), 1 = persistent-lane path kernel (ptb_mega.cuh), 0 = wavefront pipeline
+    int poolCtas = PTB_POOL_MINBLOCKS;
+    ShadowRec *dShScratch = nullptr; // NEE shadow records of the pool kernel (grid warps x NP)
+    size_t shScratchN = 0;
     int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
     int logicKeep = 28;
     int megaChunk = 0;  // PTB_MEGA_CHUNK: samples per work item, 0 = chosen from pixels/lanes // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
@@ -238,10 +246,11 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     cudaEventCreate(&c->evStart);
     cudaEventCreate(&c->evStop);
-    if (const char *e = getenv("PTB_MEGA")) c->useMega = atoi(e) != 0;
+    if (const char *e = getenv("PTB_MEGA")) c->useMega = std::max(0, std::min(2, atoi(e)));
+    if (const char *e = getenv("PTB_POOL_CTAS")) c->poolCtas = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_MEGA_CTAS")) c->megaCtas = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_MEGA_CHUNK")) c->megaChunk = std::max(0, atoi(e));
-    if (const char *e = getenv("PTB_LOGIC_KEEP")) c->logicKeep = std::max(1, std::min(32, atoi(e)));
+    if (const char *e = getenv("PTB_LOGIC_KEEP")) c->logicKeep = std::max(1, std::min(64, atoi(e)));
     if (const char *e = getenv("PTB_WAVES")) c->maxWaves = std::max(1, std::min(16, atoi(e)));
     cudaMalloc(&c->dRings, (size_t)c->maxWaves * 3 * kRing * sizeof(uint32_t));
     cudaMallocHost(&c->hRings, (size_t)c->maxWaves * 2 * kRing * sizeof(uint32_t));
@@ -295,7 +304,7 @@ extern "C" void ptb_destroy(ptb_ctx *c) {
     devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
     devFree(c->dBeam); devFree(c->dBeamIdx);
     for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
-    devFree(c->dRings); devFree(c->dCounters);
+    devFree(c->dRings); devFree(c->dCounters); devFree(c->dShScratch);
     devFree(c->dScratchF); devFree(c->dScratchI); devFree(c->dRays);
     if (c->hRings) cudaFreeHost(c->hRings);
     for (auto &w : c->allWaves) {
@@ -775,9 +784,12 @@ int render_mega(ptb_ctx *c, int add) {
     const int first = c->targetSamples;
     c->targetSamples += add;
     const ParamsDev P = make_params(c);
-    // no more lanes than owned pixels: a pixel's samples are serial, so pixels bound the parallelism
-    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * c->megaCtas, ((uint64_t)c->nSlots + kThreads - 1) / kThreads));
-    const uint64_t lanes = (uint64_t)grid * kThreads;
+    // no more paths in flight than owned pixels: a pixel's samples are serial, so pixels bound the parallelism
+    const bool pool = c->useMega == 2;
+    const uint64_t perCta = pool ? 4ull * PTB_POOL_NP : (uint64_t)kThreads; // paths a CTA keeps in flight
+    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * (pool ? c->poolCtas : c->megaCtas),
+                                                                   ((uint64_t)c->nSlots + perCta - 1) / perCta));
+    const uint64_t lanes = (uint64_t)grid * perCta;
     MegaArgs M{};
     // Work items are (pixel, chunk of samples); a lane whose pixel's previous chunk is still in flight parks
     // the item.  With many more pixels than lanes that never happens and 1-sample chunks end the frame within
@@ -798,7 +810,26 @@ int render_mega(ptb_ctx *c, int add) {
     M.counters = c->dCounters;
     CK(cudaMemsetAsync(c->dCounters + 8, 0, sizeof(unsigned long long), c->stream));
     CK(cudaEventRecord(c->evStart, c->stream));
-    k_mega<MODE, COUNT><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+    if (pool) {
+        const bool nee = P.nee && P.n_lights > 0;
+        const size_t need = nee ? (size_t)grid * 4 * PTB_POOL_NP : 0;
+        if (need > c->shScratchN) {
+            devFree(c->dShScratch);
+            c->shScratchN = 0;
+            CK(cudaMalloc(&c->dShScratch, need * sizeof(ShadowRec)));
+            c->shScratchN = need;
+        }
+        const size_t smem = 4 * sizeof(PoolSmem<PTB_POOL_NP>);
+        static bool attrSet[4][2] = {};
+        if (!attrSet[MODE][COUNT ? 1 : 0]) {
+            CK(cudaFuncSetAttribute(k_pool<MODE, COUNT, PTB_POOL_NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CK(cudaFuncSetAttribute(k_pool<MODE, COUNT, PTB_POOL_NP>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+            attrSet[MODE][COUNT ? 1 : 0] = true;
+        }
+        k_pool<MODE, COUNT, PTB_POOL_NP><<<grid, kThreads, smem, c->stream>>>(P, c->S, c->A, c->F, M, nee ? c->dShScratch : nullptr);
+    } else {
+        k_mega<MODE, COUNT><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+    }
     CK(cudaEventRecord(c->evStop, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     float ms = 0.0f;
