@@ -60,7 +60,7 @@ struct ptb_ctx {
     ShadowRec *dShScratch = nullptr; // NEE shadow records of the pool kernel (grid warps x NP)
     size_t shScratchN = 0;
     int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
-    int logicKeep = 28;
+    int logicKeep = 26;
     int megaChunk = 0;  // PTB_MEGA_CHUNK: samples per work item, 0 = chosen from pixels/lanes // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
     bool uniformSamples = true; // every owned pixel has the same sample count (false after ptb_write_state)
     int beamMaxDepth = 12; // guard on the reference's unbounded Subbeam recursion, ptb_set_build_limits  // refill a warp's idle lanes when fewer than this many are still walking
@@ -828,7 +828,8 @@ int render_mega(ptb_ctx *c, int add) {
         }
         k_pool<MODE, COUNT, PTB_POOL_NP><<<grid, kThreads, smem, c->stream>>>(P, c->S, c->A, c->F, M, nee ? c->dShScratch : nullptr);
     } else {
-        k_mega<MODE, COUNT><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+        if (P.nee && P.n_lights > 0) k_mega<MODE, COUNT, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+        else k_mega<MODE, COUNT, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
     }
     CK(cudaEventRecord(c->evStop, c->stream));
     CK(cudaStreamSynchronize(c->stream));

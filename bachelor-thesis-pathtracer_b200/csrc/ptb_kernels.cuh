@@ -181,6 +181,7 @@ struct ShadowOut {
 // Returns with the path's next ray in (o,d).  When NEE fires a shadow ray, `light` is left
 // BEFORE the two adds of shader.cpp:233 and :275; they are applied in order by the shadow
 // resolve (pendingEm = emission*throughput).
+template <bool NEE = true>
 __device__ __forceinline__ void shade_hit(const ParamsDev &P, const SceneDev &S, const AttrDev &A, PathState &ps, float t, int tri,
                                           float u, float v, bool &terminated, ShadowOut &sh, f3 &pendingEm) {
     f3 n, tg, bt;
@@ -200,7 +201,7 @@ __device__ __forceinline__ void shade_hit(const ParamsDev &P, const SceneDev &S,
         ps.d = normalize3(rd.x * tg + rd.y * bt + rd.z * n);
         ps.o = ps.o + ps.d * PTB_EPS;
         ps.tp = ps.tp * color;
-        if (P.nee && P.n_lights > 0) { // nextEventEstimation, shader.cpp:69-113
+        if (NEE && P.nee && P.n_lights > 0) { // nextEventEstimation, shader.cpp:69-113
             const float f = fast_random(ps.rng);
             uint32_t li = (uint32_t)floorf(f * (float)P.n_lights);
             if (li >= P.n_lights) li = P.n_lights - 1; // f == 1.0: the reference reads past the end (A.12)

@@ -28,7 +28,7 @@
 #include "ptb_kernels.cuh"
 
 #ifndef PTB_MEGA_MINBLOCKS
-#define PTB_MEGA_MINBLOCKS 10 /* 48 registers/thread, ~370 B of spills: 40 warps/SM beat fewer, fatter warps (profiles/r1_sweep_mega.txt) */
+#define PTB_MEGA_MINBLOCKS 12 /* 40 registers/thread: 48 warps/SM beat fewer, fatter warps despite the spills (profiles/r1_sweep_mega.txt) */
 #endif
 
 namespace ptb {
@@ -52,7 +52,9 @@ struct MegaArgs {
     unsigned long long *counters; // [0] paths [1] reference rays [2] tri tests [3] AS tests [5] path rays [6] shadow rays
 };
 
-template <int MODE, bool COUNT>
+// NEE = false compiles the shadow-ray state machine and its 19 words of per-lane state out (the reference's
+// own --testing protocol renders with NEE off, main.cpp:101).
+template <int MODE, bool COUNT, bool NEE>
 __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, MegaArgs M) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -70,7 +72,8 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
     BvhWalk w;
     int2 stack[PTB_STACK];
     uint32_t nTri = 0, nAS = 0;
-    unsigned long long cTri = 0, cAS = 0, cPaths = 0, cRef = 0, cRays = 0, cShadow = 0;
+    uint32_t cPaths = 0, cRef = 0, cRays = 0, cShadow = 0; // per lane and launch: far below 2^32
+    unsigned long long cTri = 0, cAS = 0;
 
     // begin the traversal of the lane's current ray
     auto begin_main = [&]() {
@@ -141,7 +144,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
             // ---- B. logic pass: the body of k_logic on register state ---------------------------
             if (phase == LANE_LOGIC) {
                 bool terminated = false, shadow = false;
-                if (ps.flags & PTB_FLAG_SHADOW) { // finish nextEventEstimation, shader.cpp:102-112 + :233 + :275
+                if (NEE && (ps.flags & PTB_FLAG_SHADOW)) { // finish nextEventEstimation, shader.cpp:102-112 + :233 + :275
                     const float distance = sr.distance, tAfter = shadowT;
                     if (!(distance <= tAfter - 0.01f || distance >= tAfter + 0.01f)) {
                         const float inv_sq = smin(1.0f, (1.0f / (distance * distance)));
@@ -168,7 +171,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                     if (tri >= 0) {
                         ShadowOut sh;
                         f3 pendingEm;
-                        shade_hit(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
+                        shade_hit<NEE>(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
                     }
                     ps.depth++;
                     terminated = true;
@@ -193,8 +196,8 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                 } else {
                     ShadowOut sh;
                     f3 pendingEm;
-                    shade_hit(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
-                    if (sh.emit) {
+                    shade_hit<NEE>(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
+                    if (NEE && sh.emit) {
                         sr.o = sh.o;
                         sr.d = sh.d;
                         sr.tmax0 = sh.tmax0;
@@ -249,7 +252,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                         F.samples[pixel] = n;
                         phase = LANE_IDLE;
                     }
-                } else if (shadow) {
+                } else if (NEE && shadow) {
                     if (terminated) ps.flags |= PTB_FLAG_DONE; // only the NEE term is awaited before accumulation
                     begin_shadow();
                 } else {
@@ -273,7 +276,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                         cont = false;
                     }
                     if (!cont) {
-                        if (phase == LANE_SHADOW) {
+                        if (NEE && phase == LANE_SHADOW) {
                             shadowT = w.h.t;
                             shadowTri = w.h.tri;
                             if (ps.flags & PTB_FLAG_DONE) phase = LANE_LOGIC; // the DONE branch of the logic pass ignores the path hit
@@ -290,21 +293,22 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
         }
     }
 
+    unsigned long long tPaths = cPaths, tRef = cRef, tRays = cRays, tShadow = cShadow;
     for (int off = 16; off > 0; off >>= 1) {
         cTri += __shfl_down_sync(full, cTri, off);
         cAS += __shfl_down_sync(full, cAS, off);
-        cPaths += __shfl_down_sync(full, cPaths, off);
-        cRef += __shfl_down_sync(full, cRef, off);
-        cRays += __shfl_down_sync(full, cRays, off);
-        cShadow += __shfl_down_sync(full, cShadow, off);
+        tPaths += __shfl_down_sync(full, tPaths, off);
+        tRef += __shfl_down_sync(full, tRef, off);
+        tRays += __shfl_down_sync(full, tRays, off);
+        tShadow += __shfl_down_sync(full, tShadow, off);
     }
     if (lane == 0) {
-        if (cPaths) atomicAdd(&M.counters[0], cPaths);
-        if (cRef) atomicAdd(&M.counters[1], cRef);
+        if (tPaths) atomicAdd(&M.counters[0], tPaths);
+        if (tRef) atomicAdd(&M.counters[1], tRef);
         if (COUNT && cTri) atomicAdd(&M.counters[2], cTri);
         if (COUNT && cAS) atomicAdd(&M.counters[3], cAS);
-        if (cRays) atomicAdd(&M.counters[5], cRays);
-        if (cShadow) atomicAdd(&M.counters[6], cShadow);
+        if (tRays) atomicAdd(&M.counters[5], tRays);
+        if (tShadow) atomicAdd(&M.counters[6], tShadow);
     }
 }
 

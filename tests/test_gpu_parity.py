@@ -256,3 +256,31 @@ def test_sample_sharded_frame_is_statistically_equivalent(gpu, ptb):
     print(f"RMSE vs 2048 spp: single 64-spp runs {singles}, 4 sample shards {r_sh:.4f}")
     assert r_sh <= 1.15 * max(singles)
     assert abs(sharded.mean() - ref.mean()) <= 0.03 * ref.mean()
+
+
+def test_three_schedulers_give_identical_frames(ptb, cornel_ptbs, monkeypatch):
+    """The path kernels (PTB_MEGA=1 persistent lanes [default], 2 warp pools) and the wavefront pipeline (0)
+    share the arithmetic and differ only in scheduling: frames, RNG states and counters must be bit-identical."""
+    outs = []
+    for sched in ("1", "2", "0"):
+        monkeypatch.setenv("PTB_MEGA", sched)
+        pt = ptb.PathTracer(0)
+        pt.load_ptbs(cornel_ptbs)
+        pt.build_bvh()
+        pt.build_subgrid(GS, OS, M)
+        res = []
+        for mode, nee, md in ((MODE_BVH, 1, 0), (MODE_BVH, 0, 5), (MODE_TWO_PLANE, 1, 4)):
+            pt.set_params(width=W, height=H, mode=mode, nee=nee, max_depth=md)
+            pt.reset()
+            pt.render(2)
+            pt.render(1)
+            s, r = pt.read_state()
+            c = pt.counters()
+            res.append((pt.read_image().copy(), s, r, c["rays"], c["paths"], c["ref_rays"], c["shadow_rays"]))
+        pt.close()
+        outs.append(res)
+    for other in outs[1:]:
+        for a, b in zip(outs[0], other):
+            assert (a[0].view(np.uint32) == b[0].view(np.uint32)).all()
+            assert (a[1] == b[1]).all() and (a[2] == b[2]).all()
+            assert a[3:] == b[3:]
