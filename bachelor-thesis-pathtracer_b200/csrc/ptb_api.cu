@@ -61,6 +61,7 @@ struct ptb_ctx {
     size_t shScratchN = 0;
     int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
     int logicKeep = 26;
+    int leafMax = 3;    // PTB_LEAF_MAX: triangles per BVH leaf (<= 16)
     int megaChunk = 0;  // PTB_MEGA_CHUNK: samples per work item, 0 = chosen from pixels/lanes // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
     bool uniformSamples = true; // every owned pixel has the same sample count (false after ptb_write_state)
     int beamMaxDepth = 12; // guard on the reference's unbounded Subbeam recursion, ptb_set_build_limits  // refill a warp's idle lanes when fewer than this many are still walking
@@ -249,6 +250,7 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     if (const char *e = getenv("PTB_MEGA")) c->useMega = std::max(0, std::min(2, atoi(e)));
     if (const char *e = getenv("PTB_POOL_CTAS")) c->poolCtas = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_MEGA_CTAS")) c->megaCtas = std::max(1, std::min(16, atoi(e)));
+    if (const char *e = getenv("PTB_LEAF_MAX")) c->leafMax = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_MEGA_CHUNK")) c->megaChunk = std::max(0, atoi(e));
     if (const char *e = getenv("PTB_LOGIC_KEEP")) c->logicKeep = std::max(1, std::min(64, atoi(e)));
     if (const char *e = getenv("PTB_WAVES")) c->maxWaves = std::max(1, std::min(16, atoi(e)));
@@ -455,7 +457,7 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
 extern "C" int ptb_build_bvh(ptb_ctx *c) {
     GUARD(c);
     const uint64_t n = c->mat.size();
-    build_bvh(c->pos9.data(), n, 4, c->bvh);
+    build_bvh(c->pos9.data(), n, c->leafMax, c->bvh);
     // leaf-ordered device arrays: positions as (v0, e1, e2) with the reference id in v0.w,
     // normals as (n0, n1, n2) with the material index in n0.w
     std::vector<float4> tri(3 * n), nrm(3 * n);

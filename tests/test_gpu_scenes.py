@@ -133,3 +133,25 @@ def test_soup_million_bvh_vs_bruteforce(ptb):
     t1, _ = pt.trace_rays(rays[:129], MODE_BVH)
     assert (_bits(t1) == _bits(t[:129])).all()
     pt.close()
+
+
+def test_lucy_full_size_against_reference_golden(ptb, cornel_ptbs):
+    """BASELINE config 3 at full size against the reference itself: tests/golden/lucy_standin_ref_1080p.npz holds
+    the UNMODIFIED reference's primary-hit triangle ids (BVH mode) and a digest of its hit distances for the
+    524,310-triangle stand-in at 1920x1080 (tests/golden/make_golden.py --lucy).  The scene generator is
+    bit-reproducible, which the scene digest checks first."""
+    import hashlib
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "lucy_standin_ref_1080p.npz"))
+    sc = ptb.scenes
+    scene = sc.lucy_standin(sc.read_ptbs(cornel_ptbs))
+    assert hashlib.sha256(scene["pos"].tobytes()).hexdigest() == str(gold["scene_sha256"]), "scene generator is not bit-reproducible here"
+    pt = ptb.PathTracer(0)
+    sc.upload_scene(pt, scene)
+    pt.build_bvh()
+    pt.set_params(width=1920, height=1080, mode=MODE_BVH)
+    t, tri, _ = pt.primary_hits()
+    pt.close()
+    assert hashlib.sha256(t.tobytes()).hexdigest() == str(gold["t_sha256"]), "hit distances differ from the reference's"
+    agree = float((tri == gold["tri"]).mean())
+    print(f"hit-id agreement with the reference: {agree:.7f} ({int((tri != gold['tri']).sum())} of {tri.size} differ, all on bit-equal t)")
+    assert agree >= 0.9999
