@@ -147,8 +147,8 @@ def run_reference(args):
     if rank != 0:
         return 0
     wl = WORKLOADS[args.workload]
-    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    ptbs = scene_file(args.workload, os.path.join(ROOT, "gpurun_out"))
+    import tempfile
+    ptbs = scene_file(args.workload, tempfile.gettempdir())
     spp = args.ref_spp
     for _ in range(args.warmup):
         cpu_reference_run(ptbs, wl, 1)
@@ -307,6 +307,13 @@ def run_ours(args):
     result = None
     if rank == 0:
         peak, peak_kind = peaks()
+        traffic = traffic_src = None
+        try:  # dram__bytes_read.sum + dram__bytes_write.sum of the same kernel from the committed ncu capture, scaled to this launch
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")))[args.workload]
+            traffic = tr["dram_bytes_per_ray"] * rays / max(1, ext_launches)
+            traffic_src = tr["source"]
+        except Exception:
+            pass
         value = rays_all / (dev_ms_max / 1e3) / 1e6
         # roofline of the dominant kernel on rank 0's own launches.  The waves of a render overlap on the device,
         # so the per-launch CUDA-event durations of concurrent kernels overlap too: the step's device time is
@@ -333,7 +340,7 @@ def run_ours(args):
             "e2e": {"value": e2e_rays_all / e2e_s_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_s_max / args.steps * 1e3},
             "roofline": {"bound": "hbm", "kernel": "k_mega<BVH> (fused traversal + shade)" if ext_launches == args.steps else "k_extend_bvh", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": (ach / peak) if ach else None, "traffic": None, "peak_source": peak_kind,
+                         "frac": (ach / peak) if ach else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_kind,
                          "bytes_per_ray": bytes_per_ray, "boxes_per_ray": boxes_per_ray, "tris_per_ray": tris_per_ray,
                          "avg_launch_ms": ext_time_ms / max(1, ext_launches), "launches": ext_launches,
                          "avg_launch_event_ms": ext_ms / max(1, ext_launches),
@@ -342,8 +349,8 @@ def run_ours(args):
         }
     pt.close()
     if rank == 0 and world == 1 and not args.no_cpu:
-        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-        ptbs = scene_file(args.workload, os.path.join(ROOT, "gpurun_out"))
+        import tempfile
+        ptbs = scene_file(args.workload, tempfile.gettempdir())
         r, s, kind, cores = cpu_reference_run(ptbs, wl, args.cpu_spp)
         result["cpu_baseline"] = {
             "value": r / s / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind, "host_cpus": os.cpu_count(),
