@@ -191,6 +191,13 @@ class PathTracer:
         self._ck(self.L.ptb_render(self.h, add_samples), "ptb_render")
         return self.last_ms()
 
+    def render_async(self, add_samples):
+        """Enqueue only (path kernels); finish with sync()."""
+        self._ck(self.L.ptb_render_async(self.h, add_samples), "ptb_render_async")
+
+    def sync(self):
+        self._ck(self.L.ptb_sync(self.h), "ptb_sync")
+
     def last_ms(self):
         return float(self.L.ptb_last_render_ms(self.h))
 

@@ -63,6 +63,7 @@ struct ptb_ctx {
     int logicKeep = 26;
     int leafMax = 3;    // PTB_LEAF_MAX: triangles per BVH leaf (<= 16)
     int megaChunk = 0;  // PTB_MEGA_CHUNK: samples per work item, 0 = chosen from pixels/lanes // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
+    bool pendingRender = false, asyncRequested = false; // ptb_render_async: a path-kernel launch awaits ptb_sync
     bool uniformSamples = true; // every owned pixel has the same sample count (false after ptb_write_state)
     int beamMaxDepth = 12; // guard on the reference's unbounded Subbeam recursion, ptb_set_build_limits  // refill a warp's idle lanes when fewer than this many are still walking
     cudaStream_t stream = nullptr;
@@ -136,6 +137,17 @@ struct ptb_ctx {
 };
 
 static std::string g_createErr = "";
+namespace {
+int finish_mega(ptb_ctx *c);
+}
+// an enqueued ptb_render_async is completed before anything else touches the frame or the counters
+#define SETTLE(c)                                   \
+    do {                                            \
+        if ((c)->pendingRender) {                   \
+            const int rs_ = finish_mega(c);         \
+            if (rs_) return rs_;                    \
+        }                                           \
+    } while (0)
 static WaveRange active_waves(ptb_ctx *c) { return WaveRange{c->allWaves.data(), c->allWaves.data() + c->nWaves}; }
 
 namespace {
@@ -458,6 +470,8 @@ extern "C" int ptb_build_bvh(ptb_ctx *c) {
     GUARD(c);
     const uint64_t n = c->mat.size();
     build_bvh(c->pos9.data(), n, c->leafMax, c->bvh);
+    // the walk pushes one deferred child per level: the tree must fit the per-lane stack
+    if (c->bvh.max_depth >= PTB_STACK) return fail(c, PTB_ERR_INVALID, "BVH deeper than the traversal stack (PTB_STACK): degenerate input?");
     // leaf-ordered device arrays: positions as (v0, e1, e2) with the reference id in v0.w,
     // normals as (n0, n1, n2) with the material index in n0.w
     std::vector<float4> tri(3 * n), nrm(3 * n);
@@ -528,6 +542,7 @@ extern "C" uint64_t ptb_structure_bytes(const ptb_ctx *c, int mode) {
 // =============================================================================================
 extern "C" int ptb_set_params(ptb_ctx *c, const ptb_params *p) {
     GUARD(c);
+    SETTLE(c);
     if (!p) return fail(c, PTB_ERR_INVALID, "null params");
     if (p->width <= 0 || p->height <= 0 || p->width > 65535 || p->height > 65535)
         return fail(c, PTB_ERR_INVALID, "width/height out of range (1..65535: the seed packs x<<16|y)");
@@ -615,6 +630,7 @@ extern "C" int ptb_clear(ptb_ctx *c) { return reset_frame(c, 0); }
 
 static int reset_frame(ptb_ctx *c, int reseed) {
     GUARD(c);
+    SETTLE(c);
     if (!c->haveParams) return fail(c, PTB_ERR_INVALID, "ptb_set_params first");
     if (c->frameDirty) {
         int r = alloc_frame(c);
@@ -780,6 +796,8 @@ int render_mode(ptb_ctx *c, int add) {
     return PTB_OK;
 }
 
+int finish_mega(ptb_ctx *c);
+
 // One launch per render: the persistent-lane path kernel of ptb_mega.cuh.
 template <int MODE, bool COUNT>
 int render_mega(ptb_ctx *c, int add) {
@@ -834,6 +852,15 @@ int render_mega(ptb_ctx *c, int add) {
         else k_mega<MODE, COUNT, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
     }
     CK(cudaEventRecord(c->evStop, c->stream));
+    c->pendingRender = true;
+    if (c->asyncRequested) return PTB_OK; // ptb_render_async: ptb_sync finishes the bookkeeping
+    return finish_mega(c);
+}
+
+// waits for an enqueued k_mega / k_pool launch and folds its counters into the context
+int finish_mega(ptb_ctx *c) {
+    if (!c->pendingRender) return PTB_OK;
+    c->pendingRender = false;
     CK(cudaStreamSynchronize(c->stream));
     float ms = 0.0f;
     cudaEventElapsedTime(&ms, c->evStart, c->evStop);
@@ -873,6 +900,7 @@ int render_dispatch(ptb_ctx *c, int add) {
 
 extern "C" int ptb_render(ptb_ctx *c, int add_samples) {
     GUARD(c);
+    SETTLE(c);
     if (!c->haveParams) return fail(c, PTB_ERR_INVALID, "ptb_set_params first");
     if (add_samples <= 0) return fail(c, PTB_ERR_INVALID, "add_samples must be positive");
     int r = check_mode_ready(c, c->prm.mode);
@@ -885,9 +913,22 @@ extern "C" int ptb_render(ptb_ctx *c, int add_samples) {
     const bool count = c->prm.count_tests || c->prm.debug_view;
     return count ? render_dispatch<true>(c, add_samples) : render_dispatch<false>(c, add_samples);
 }
-extern "C" int ptb_render_async(ptb_ctx *c, int add_samples) { return ptb_render(c, add_samples); }
+// Enqueues the render and returns: with the path kernels (one launch per render) nothing is read back until
+// ptb_sync; the wavefront pipeline needs its queue sizes on the host and renders synchronously.
+extern "C" int ptb_render_async(ptb_ctx *c, int add_samples) {
+    GUARD(c);
+    if (c->pendingRender) {
+        int r = finish_mega(c);
+        if (r) return r;
+    }
+    c->asyncRequested = true;
+    const int r = ptb_render(c, add_samples);
+    c->asyncRequested = false;
+    return r;
+}
 extern "C" int ptb_sync(ptb_ctx *c) {
     GUARD(c);
+    if (c->pendingRender) return finish_mega(c);
     CK(cudaStreamSynchronize(c->stream));
     return PTB_OK;
 }
@@ -934,6 +975,7 @@ static int ensure_scratch(ptb_ctx *c, uint64_t n, bool rays) {
 
 extern "C" int ptb_primary_hits(ptb_ctx *c, float *t, int32_t *tri, int32_t *mat) {
     GUARD(c);
+    SETTLE(c);
     if (!c->haveParams) return fail(c, PTB_ERR_INVALID, "ptb_set_params first");
     int r = check_mode_ready(c, c->prm.mode);
     if (r) return r;
@@ -964,6 +1006,7 @@ extern "C" int ptb_primary_hits(ptb_ctx *c, float *t, int32_t *tri, int32_t *mat
 
 extern "C" int ptb_trace_rays_device(ptb_ctx *c, const float *od6, uint64_t n, int mode, float *t, int32_t *tri) {
     GUARD(c);
+    SETTLE(c);
     if (mode < 0 || mode > 3) return fail(c, PTB_ERR_INVALID, "mode must be 0..3");
     int r = check_mode_ready(c, mode);
     if (r) return r;
@@ -1025,6 +1068,7 @@ extern "C" int ptb_trace_rays(ptb_ctx *c, const float *od6, uint64_t n, int mode
 // =============================================================================================
 extern "C" int ptb_read_image(ptb_ctx *c, float *rgba) {
     GUARD(c);
+    SETTLE(c);
     if (!rgba || !c->F.image) return fail(c, PTB_ERR_INVALID, "no frame / null buffer");
     CK(cudaMemcpyAsync(rgba, c->F.image, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -1033,6 +1077,7 @@ extern "C" int ptb_read_image(ptb_ctx *c, float *rgba) {
 
 extern "C" int ptb_read_state(ptb_ctx *c, int32_t *samples, uint32_t *rng) {
     GUARD(c);
+    SETTLE(c);
     if (!c->F.image) return fail(c, PTB_ERR_INVALID, "no frame");
     const size_t n = (size_t)c->W * c->H;
     if (samples) CK(cudaMemcpyAsync(samples, c->F.samples, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -1043,6 +1088,7 @@ extern "C" int ptb_read_state(ptb_ctx *c, int32_t *samples, uint32_t *rng) {
 
 extern "C" int ptb_write_state(ptb_ctx *c, const float *rgba, const int32_t *samples, const uint32_t *rng) {
     GUARD(c);
+    SETTLE(c);
     if (!c->F.image) return fail(c, PTB_ERR_INVALID, "no frame (ptb_reset first)");
     if (!rgba || !samples || !rng) return fail(c, PTB_ERR_INVALID, "null state arrays");
     const size_t n = (size_t)c->W * c->H;
@@ -1059,6 +1105,7 @@ extern "C" int ptb_write_state(ptb_ctx *c, const float *rgba, const int32_t *sam
 
 extern "C" int ptb_read_rgba8(ptb_ctx *c, uint8_t *rgba8, int tone_mapping) {
     GUARD(c);
+    SETTLE(c);
     if (!rgba8 || !c->F.image) return fail(c, PTB_ERR_INVALID, "no frame / null buffer");
     const uint32_t n = (uint32_t)c->W * c->H;
     uchar4 *d = nullptr;
@@ -1074,6 +1121,7 @@ extern "C" int ptb_read_rgba8(ptb_ctx *c, uint8_t *rgba8, int tone_mapping) {
 
 extern "C" int ptb_read_counters(ptb_ctx *c, uint64_t out[PTB_CNT__N]) {
     GUARD(c);
+    SETTLE(c);
     if (!out) return fail(c, PTB_ERR_INVALID, "null");
     memcpy(out, c->counters, sizeof c->counters);
     return PTB_OK;

@@ -50,6 +50,8 @@ WORKLOADS = {
                     name="Cornell box, BVH, 1024x1024, 64 spp, 4 bounces (BASELINE configs[1])"),
     "lucy": dict(W=1920, H=1080, spp=16, max_depth=9, mode=1,
                  name="Lucy stand-in (524,310 triangles), BVH, 1920x1080, 16 spp, 8 bounces (configs[3] at 1/16 of the samples)"),
+    "lucy256": dict(W=1920, H=1080, spp=256, max_depth=9, mode=1,
+                    name="Lucy stand-in (524,310 triangles), BVH, 1920x1080, 256 spp, 8 bounces (BASELINE configs[3] frame)"),
 }
 
 
@@ -112,6 +114,7 @@ def scene_file(workload, tmpdir):
     """Path of the workload's .ptbs (Cornell ships as a fixture; the Lucy stand-in is generated)."""
     if workload == "cornell":
         return CORNEL
+    workload = "lucy"
     import ptb_b200
     path = os.path.join(tmpdir, "lucy_standin.ptbs")
     if not os.path.isfile(path):
@@ -193,7 +196,7 @@ def run_ours(args):
     W, H, spp, mode = wl["W"], wl["H"], wl["spp"], wl["mode"]
     sc = ptb_b200.scenes
     scene = sc.read_ptbs(CORNEL)
-    if args.workload == "lucy":
+    if args.workload.startswith("lucy"):
         scene = sc.lucy_standin(scene)
     mats_bytes, n_mats = sc.pack_materials(scene["materials"]), len(scene["materials"])
     cam = scene["camera"]
@@ -202,6 +205,12 @@ def run_ours(args):
     sc.upload_scene(pt, scene)
     t0 = time.perf_counter()
     pt.build_bvh()
+    if args.structure == "subgrid":
+        pt.build_subgrid(8, 8, 50)
+        mode = 2
+    elif args.structure == "subbeams":
+        pt.build_subbeams(6, 50, max_depth=1)
+        mode = 3
     build_s = time.perf_counter() - t0
     # Sharding: tiles (bit-identical to the 1-GPU frame) while every GPU keeps >= 400k pixels in flight; below
     # that the serial samples of a pixel starve the lanes and the frame is sharded by sample ranges instead
@@ -242,6 +251,8 @@ def run_ours(args):
     boxes_per_ray = c["as_tests"] / max(1, c["rays"])
     tris_per_ray = c["tri_tests"] / max(1, c["rays"])
     bytes_per_ray = 48.0 + 32.0 * boxes_per_ray + 36.0 * tris_per_ray
+    if args.structure != "bvh":  # per structure test ~ half a 64-B header + half an 8-B LUT cell; 4-B index + 36-B triangle
+        bytes_per_ray = 48.0 + 36.0 * boxes_per_ray + 40.0 * tris_per_ray
 
     pt.set_params(count_tests=0, **base)
     pt.set_profiling(True)
@@ -251,16 +262,18 @@ def run_ours(args):
         pt.render(my_spp)
         reduce_frame()
 
+    # clocks + throttle reasons are sampled from the warm-up to the end of the e2e leg: the timed region can be
+    # shorter than nvidia-smi's sampling period (8 GPUs: 6 ms per step), the load before and after it is the same
+    clocks = ClockSampler(local)
+    clocks.start()
     for _ in range(args.warmup):
         step()
     # ---- value: device time, state resident in HBM --------------------------------------------
-    clocks = ClockSampler(local)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     rays = paths = kernels = 0
     ext_ms = logic_ms = 0.0
     ext_launches = 0
     barrier()
-    clocks.start()
     for k in range(args.steps):
         flush.fill_(k & 0xFF)  # L2 flush between timed iterations (torch stream; not inside the event pair)
         torch.cuda.synchronize()
@@ -272,7 +285,6 @@ def run_ours(args):
         rays += cc["rays"]; paths += cc["paths"]; kernels += cc["kernels"]
         ext_ms += st["extend_ms"]; logic_ms += st["logic_ms"]; ext_launches += st["extend_launches"]
     barrier()
-    clk = clocks.stop()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
 
     # ---- e2e: through the C ABI with host buffers, copies inside the timed region ---------------
@@ -292,6 +304,7 @@ def run_ours(args):
         e2e_rays += pt.counters()["rays"]
     barrier()
     e2e_s = time.perf_counter() - t0
+    clk = clocks.stop()
     h2d = len(mats_bytes) + 36 + 56
     d2h = W * H * 16
 
@@ -309,7 +322,7 @@ def run_ours(args):
         peak, peak_kind = peaks()
         traffic = traffic_src = None
         try:  # dram__bytes_read.sum + dram__bytes_write.sum of the same kernel from the committed ncu capture, scaled to this launch
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")))[args.workload]
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")))["lucy" if args.workload.startswith("lucy") else args.workload]
             traffic = tr["dram_bytes_per_ray"] * rays / max(1, ext_launches)
             traffic_src = tr["source"]
         except Exception:
@@ -327,7 +340,8 @@ def run_ours(args):
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["name"], "width": W, "height": H, "spp": spp, "max_depth": wl["max_depth"], "nee": 0,
-                       "structure": "BVH2, 64-byte two-box nodes", "triangles": int(scene["pos"].shape[0]),
+                       "structure": {"bvh": "BVH2, 64-byte two-box nodes", "subgrid": "Subgrid / 2Plane hierarchy gs 8 os 8 m 50",
+                                     "subbeams": "Subbeams gs 6 m 50 depth 1"}[args.structure], "triangles": int(scene["pos"].shape[0]),
                        "parallelism": "1 GPU" if world == 1 else (f"tiles32x8 round-robin over {world} GPUs, NCCL sum-reduce to rank 0 (bit-identical to 1 GPU)"
                                                                  if shard == "tiles" else
                                                                  f"sample ranges: {world} GPUs x all pixels x spp/{world} from per-rank seeds, NCCL sum-reduce (statistical parity)"),
@@ -374,6 +388,8 @@ def main():
     ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-spp", type=int, default=8, help="spp of the bounded cpu_baseline sample")
     ap.add_argument("--ref-spp", type=int, default=4, help="spp per step of the --impl reference arm")
+    ap.add_argument("--structure", default="bvh", choices=["bvh", "subgrid", "subbeams"],
+                    help="acceleration structure (subgrid: gs 8 / os 8 / m 50 like the published runs; subbeams: gs 6 / m 50 / depth 1)")
     ap.add_argument("--shard", default="auto", choices=["auto", "tiles", "samples"], help="multi-GPU partition of the frame")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--res", default="", help="override the frame size WxH (experiments only)")

@@ -284,3 +284,51 @@ def test_three_schedulers_give_identical_frames(ptb, cornel_ptbs, monkeypatch):
             assert (a[0].view(np.uint32) == b[0].view(np.uint32)).all()
             assert (a[1] == b[1]).all() and (a[2] == b[2]).all()
             assert a[3:] == b[3:]
+
+
+def test_async_render_and_edge_cases(ptb, cornel_ptbs, gpu):
+    """ptb_render_async + ptb_sync equals ptb_render; reads settle a pending render; ragged frame sizes;
+    call-order errors are reported, not crashed on."""
+    pt = ptb.PathTracer(0)
+    with pytest.raises(ptb.PtbError):  # nothing uploaded / no params
+        pt.render(1)
+    pt.load_ptbs(cornel_ptbs)
+    pt.set_params(width=50, height=37, mode=MODE_BVH, nee=1, max_depth=3)  # not multiples of 4 or 32
+    with pytest.raises(ptb.PtbError) as e:
+        pt.render(1)
+    assert "ptb_build_bvh" in str(e.value)
+    pt.build_bvh()
+    pt.set_params(mode=MODE_TWO_PLANE)
+    with pytest.raises(ptb.PtbError):
+        pt.render(1)  # Subgrid not built
+    with pytest.raises(ptb.PtbError):
+        pt.set_params(width=0)
+    pt.set_params(width=50, height=37, mode=MODE_BVH)
+    pt.reset()
+    pt.render(3)
+    a = pt.read_image()
+    pt.reset()
+    pt.render_async(2)
+    pt.render_async(1)   # settles the first, enqueues the second
+    b = pt.read_image()  # settles the second
+    pt.sync()
+    assert (a.view(np.uint32) == b.view(np.uint32)).all()
+    assert pt.counters()["paths"] == 50 * 37 * 3
+    gpu.set_params(width=50, height=37, mode=MODE_BVH, nee=1, max_depth=3)
+    gpu.reset()
+    gpu.render(3)
+    assert (gpu.read_image().view(np.uint32) == a.view(np.uint32)).all()
+    # an empty scene renders black and never touches a structure
+    pt2 = ptb.PathTracer(0)
+    pt2.upload_triangles(np.zeros((0, 9), np.float32), np.zeros((0, 9), np.float32), None, np.zeros(0, np.int32))
+    pt2.upload_materials(b"", 0)
+    pt2.upload_objects(b"", 0)
+    pt2.set_camera([0, 0, -5], [0, 0, 1])
+    pt2.build_bvh()
+    pt2.set_params(width=16, height=8, mode=MODE_BVH, max_depth=4)
+    pt2.reset()
+    pt2.render(2)
+    img = pt2.read_image()
+    assert (img[..., :3] == 0).all() and (pt2.read_state()[0] == 2).all()
+    pt2.close()
+    pt.close()
