@@ -9,7 +9,7 @@ INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 OUT = os.path.join(_HERE, "libptb.so")
 
 SOURCES = ["ptb_api.cu", "ptb_bvh_build.cpp", "ptb_grid_build.cpp"]
-HEADERS = ["ptb_device.cuh", "ptb_kernels.cuh", "ptb_bvh_build.h", "ptb_grid_build.h"]
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h")))
 
 # -fmad=false / -prec-div / -prec-sqrt / -ftz=false: the arithmetic contract of ptb_device.cuh
 NVCC_FLAGS = [

@@ -195,10 +195,21 @@ __device__ __forceinline__ void shade_hit(const ParamsDev &P, const SceneDev &S,
     const float xi = fast_random(ps.rng);
     const f3 color = ld3(m.gamma);
     sh.emit = false;
-    if (xi < m.wl) { // lambert
+    // All three lobes draw ONE cosine-weighted direction and rotate it into the hit frame with the same
+    // operations (shader.cpp:211-214, :127-131, :189-193); only refraction draws its Fresnel number first.
+    // Hoisted out of the branches: one copy of the double-precision sin/cos in the instruction stream instead
+    // of three, evaluated by all shading lanes together instead of once per material present in the warp.
+    const bool lambert = xi < m.wl, mirror = !lambert && xi < (m.wl + m.wr);
+    float x2 = 0.0f;
+    if (!lambert && !mirror) x2 = fast_random(ps.rng);
+    const f3 rd = cosine_dir(ps.rng);
+    f3 dir = rd.x * tg;
+    dir = dir + rd.y * bt;
+    dir = dir + rd.z * n;
+    dir = normalize3(dir);
+    if (lambert) {
         ps.o = ps.o + ps.d * t;
-        const f3 rd = cosine_dir(ps.rng);
-        ps.d = normalize3(rd.x * tg + rd.y * bt + rd.z * n);
+        ps.d = dir;
         ps.o = ps.o + ps.d * PTB_EPS;
         ps.tp = ps.tp * color;
         if (NEE && P.nee && P.n_lights > 0) { // nextEventEstimation, shader.cpp:69-113
@@ -239,49 +250,37 @@ __device__ __forceinline__ void shade_hit(const ParamsDev &P, const SceneDev &S,
                 }
             }
         }
-    } else if (xi < (m.wl + m.wr)) { // reflection
-        ps.o = ps.o + ps.d * t;
-        ps.d = ps.d - 2.0f * dot3(ps.d, n) * n;
-        const f3 rd = cosine_dir(ps.rng);
-        f3 dir = rd.x * tg;
-        dir = dir + rd.y * bt;
-        dir = dir + rd.z * n;
-        dir = normalize3(dir);
-        ps.d = normalize3(ps.d * (1 - m.roughness) + dir * m.roughness);
-        ps.tp = ps.tp * color;
-        ps.o = ps.o + ps.d * 0.01f;
-    } else { // refraction
-        f3 nn = n;
-        const float n1 = m.ior1, n2 = m.ior2;
-        float eta = n1 / n2;
-        float cs = dot3(ps.d, n);
-        if (cs >= PTB_EPS) {
-            cs *= -1;
-            eta = 1.0f / eta;
-            nn = n * -1.0f;
+    } else {
+        f3 base; // the lobe's ideal direction, blended with the cosine sample by roughness below
+        if (mirror) { // reflection
+            base = ps.d - 2.0f * dot3(ps.d, n) * n;
+            ps.o = ps.o + ps.d * t;
+        } else { // refraction
+            f3 nn = n;
+            const float n1 = m.ior1, n2 = m.ior2;
+            float eta = n1 / n2;
+            float cs = dot3(ps.d, n);
+            if (cs >= PTB_EPS) {
+                cs *= -1;
+                eta = 1.0f / eta;
+                nn = n * -1.0f;
+            }
+            const float disc = 1.0f - (eta * eta) * (1.0f - (cs * cs));
+            float r0 = ((n1 - n2) / (n1 + n2)); // calculateFresnelTerm, shader.cpp:46-50 (pow in double)
+            r0 *= r0;
+            // pow(1 - cos, 5) in double (shader.cpp:49): three multiplications, <= 1.5 ulp of the correctly rounded
+            // value before the narrowing to float below — no double pow() in the instruction stream
+            const double pb = (double)(1 - (-cs)), pb2 = pb * pb;
+            float refl = (float)((double)r0 + (double)(1 - r0) * (pb2 * pb2 * pb));
+            if (refl > 1) refl = 1;
+            if (refl < 0) refl = 0;
+            if (disc < PTB_EPS || x2 < refl) base = normalize3(ps.d - 2.0f * dot3(ps.d, n) * n);
+            else base = normalize3(eta * (ps.d - cs * nn) - nn * sqrtf(disc + PTB_EPS));
+            ps.o = ps.o + ps.d * t + base * PTB_EPS;
         }
-        const float disc = 1.0f - (eta * eta) * (1.0f - (cs * cs));
-        const float x2 = fast_random(ps.rng);
-        float r0 = ((n1 - n2) / (n1 + n2)); // calculateFresnelTerm, shader.cpp:46-50 (pow in double)
-        r0 *= r0;
-        // pow(1 - cos, 5) in double (shader.cpp:49): three multiplications, <= 1.5 ulp of the correctly rounded
-        // value before the narrowing to float below — no double pow() in the instruction stream
-        const double pb = (double)(1 - (-cs)), pb2 = pb * pb;
-        float refl = (float)((double)r0 + (double)(1 - r0) * (pb2 * pb2 * pb));
-        if (refl > 1) refl = 1;
-        if (refl < 0) refl = 0;
-        f3 rdir;
-        if (disc < PTB_EPS || x2 < refl) rdir = normalize3(ps.d - 2.0f * dot3(ps.d, n) * n);
-        else rdir = normalize3(eta * (ps.d - cs * nn) - nn * sqrtf(disc + PTB_EPS));
-        ps.o = ps.o + ps.d * t + rdir * PTB_EPS;
         ps.tp = ps.tp * color;
-        ps.d = rdir;
-        const f3 rd = cosine_dir(ps.rng);
-        f3 dir = rd.x * tg;
-        dir = dir + rd.y * bt;
-        dir = dir + rd.z * n;
-        dir = normalize3(dir);
-        ps.d = normalize3(ps.d * (1 - m.roughness) + dir * m.roughness);
+        ps.d = normalize3(base * (1 - m.roughness) + dir * m.roughness);
+        if (mirror) ps.o = ps.o + ps.d * 0.01f;
     }
     pendingEm = m.emission * ps.tp; // shader.cpp:275 (always added; with NEE after the NEE term)
 }

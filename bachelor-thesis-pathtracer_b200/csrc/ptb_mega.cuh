@@ -33,7 +33,7 @@
 
 namespace ptb {
 
-enum : int { LANE_IDLE = 0, LANE_WAIT = 1, LANE_LOGIC = 2, LANE_SHADOW = 3, LANE_MAIN = 4 };
+enum : int { LANE_IDLE = 0, LANE_WAIT = 1, LANE_LOGIC = 2, LANE_SHADOW = 3, LANE_MAIN = 4, LANE_NEXT = 5 /* next sample of the same pixel */ };
 
 struct ShadowRec { // what nextEventEstimation still needs once the shadow ray is back (shader.cpp:102-112)
     f3 o, d;
@@ -128,10 +128,11 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                     phase = LANE_IDLE;
                 } else {
                     ps.rng = __ldcg(&F.rng[pixel]);
-                    begin_sample();
+                    phase = LANE_NEXT;
                 }
             }
         }
+        if (phase == LANE_NEXT) begin_sample(); // the only copy of the raygen code in the kernel (I-cache)
 
         const unsigned needLogic = __ballot_sync(full, phase == LANE_LOGIC);
         const unsigned walking = __ballot_sync(full, phase == LANE_SHADOW || phase == LANE_MAIN);
@@ -245,7 +246,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                     samplesLeft--;
                     if (samplesLeft > 0 && n < P.target_samples) {
                         F.samples[pixel] = n;
-                        begin_sample();
+                        phase = LANE_NEXT;
                     } else {
                         F.rng[pixel] = ps.rng;
                         __threadfence(); // image + rng visible before the sample count releases the pixel's next chunk
