@@ -17,6 +17,7 @@
 #include "ptb_kernels.cuh"
 #include "ptb_mega.cuh"
 #include "ptb_pool.cuh"
+#include "ptb_duo.cuh"
 
 #ifndef PTB_POOL_NP
 #define PTB_POOL_NP 64 /* paths per warp pool */
@@ -57,10 +58,14 @@ struct ptb_ctx {
     int fetchKeep = 20;
     int useMega = 1;   // PTB_MEGA: 2 = warp-pool path kernel (ptb_pool.cuh), 1 = persistent-lane path kernel (ptb_mega.cuh), 0 = wavefront pipeline
     int poolCtas = PTB_POOL_MINBLOCKS;
+    int duoCtas = PTB_DUO_MINBLOCKS; // PTB_DUO_CTAS
+    int duoLogicKeep = 24, duoSampleKeep = 16, duoWalkMin = 20, duoRefillMin = 8, duoLeafKeep = 8; // PTB_DUO_LOGIC / _SAMPLE / _WALK / _REFILL
     ShadowRec *dShScratch = nullptr; // NEE shadow records of the pool kernel (grid warps x NP)
     size_t shScratchN = 0;
     int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
     int logicKeep = 26;
+    int traceLeafFrac = 0; // PTB_TRACE_LEAF: the same switch for ptb_trace_rays (k_trace_bvh)
+    int megaLeafFrac = -1; // PTB_MEGA_LEAF: k_mega leaves the node loop when fewer than walkers*this/32 lanes still descend; -1 = 16 for trees of >= 2^15 triangles, else off
     int leafMax = 3;    // PTB_LEAF_MAX: triangles per BVH leaf (<= 16)
     int megaChunk = 0;  // PTB_MEGA_CHUNK: samples per work item, 0 = chosen from pixels/lanes // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
     bool pendingRender = false, asyncRequested = false; // ptb_render_async: a path-kernel launch awaits ptb_sync
@@ -259,7 +264,15 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     cudaEventCreate(&c->evStart);
     cudaEventCreate(&c->evStop);
-    if (const char *e = getenv("PTB_MEGA")) c->useMega = std::max(0, std::min(2, atoi(e)));
+    if (const char *e = getenv("PTB_MEGA")) c->useMega = std::max(0, std::min(3, atoi(e)));
+    if (const char *e = getenv("PTB_DUO_CTAS")) c->duoCtas = std::max(1, std::min(PTB_DUO_MINBLOCKS, atoi(e)));
+    if (const char *e = getenv("PTB_DUO_LOGIC")) c->duoLogicKeep = std::max(1, std::min(33, atoi(e)));
+    if (const char *e = getenv("PTB_DUO_SAMPLE")) c->duoSampleKeep = std::max(1, std::min(33, atoi(e)));
+    if (const char *e = getenv("PTB_DUO_WALK")) c->duoWalkMin = std::max(0, std::min(32, atoi(e)));
+    if (const char *e = getenv("PTB_TRACE_LEAF")) c->traceLeafFrac = std::max(0, std::min(32, atoi(e)));
+    if (const char *e = getenv("PTB_MEGA_LEAF")) c->megaLeafFrac = std::max(0, std::min(32, atoi(e)));
+    if (const char *e = getenv("PTB_DUO_LEAF")) c->duoLeafKeep = std::max(1, std::min(33, atoi(e)));
+    if (const char *e = getenv("PTB_DUO_REFILL")) c->duoRefillMin = std::max(1, std::min(64, atoi(e)));
     if (const char *e = getenv("PTB_POOL_CTAS")) c->poolCtas = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_MEGA_CTAS")) c->megaCtas = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_LEAF_MAX")) c->leafMax = std::max(1, std::min(16, atoi(e)));
@@ -805,9 +818,9 @@ int render_mega(ptb_ctx *c, int add) {
     c->targetSamples += add;
     const ParamsDev P = make_params(c);
     // no more paths in flight than owned pixels: a pixel's samples are serial, so pixels bound the parallelism
-    const bool pool = c->useMega == 2;
-    const uint64_t perCta = pool ? 4ull * PTB_POOL_NP : (uint64_t)kThreads; // paths a CTA keeps in flight
-    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * (pool ? c->poolCtas : c->megaCtas),
+    const bool pool = c->useMega == 2, duo = c->useMega == 3;
+    const uint64_t perCta = pool ? 4ull * PTB_POOL_NP : (duo ? 2ull * kThreads : (uint64_t)kThreads); // paths a CTA keeps in flight
+    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * (pool ? c->poolCtas : (duo ? c->duoCtas : c->megaCtas)),
                                                                    ((uint64_t)c->nSlots + perCta - 1) / perCta));
     const uint64_t lanes = (uint64_t)grid * perCta;
     MegaArgs M{};
@@ -825,7 +838,11 @@ int render_mega(ptb_ctx *c, int add) {
     M.n_items = chunked ? c->nSlots * nChunks : c->nSlots;
     M.first_sample = first;
     M.check_ready = chunked ? 1 : 0;
-    M.logic_keep = c->logicKeep;
+    M.logic_keep = duo ? c->duoLogicKeep : c->logicKeep;
+    M.sample_keep = c->duoSampleKeep;
+    M.walk_min = c->duoWalkMin;
+    M.refill_min = c->duoRefillMin;
+    M.leaf_keep = duo ? c->duoLeafKeep : (c->megaLeafFrac >= 0 ? c->megaLeafFrac : (c->mat.size() >= (1u << 15) ? 16 : 0));
     M.cursor = c->dCounters + 8;
     M.counters = c->dCounters;
     CK(cudaMemsetAsync(c->dCounters + 8, 0, sizeof(unsigned long long), c->stream));
@@ -847,8 +864,15 @@ int render_mega(ptb_ctx *c, int add) {
             attrSet[MODE][COUNT ? 1 : 0] = true;
         }
         k_pool<MODE, COUNT, PTB_POOL_NP><<<grid, kThreads, smem, c->stream>>>(P, c->S, c->A, c->F, M, nee ? c->dShScratch : nullptr);
+    } else if (duo) {
+        if (P.nee && P.n_lights > 0) k_duo<MODE, COUNT, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+        else k_duo<MODE, COUNT, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
     } else {
-        if (P.nee && P.n_lights > 0) k_mega<MODE, COUNT, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+        const bool nee = P.nee && P.n_lights > 0;
+        if (MODE == 1 && M.leaf_keep > 0) { // deep tree: straggler exit in the node loop
+            if (nee) k_mega<MODE, COUNT, true, MODE == 1><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+            else k_mega<MODE, COUNT, false, MODE == 1><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+        } else if (nee) k_mega<MODE, COUNT, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
         else k_mega<MODE, COUNT, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
     }
     CK(cudaEventRecord(c->evStop, c->stream));
@@ -1025,8 +1049,12 @@ extern "C" int ptb_trace_rays_device(ptb_ctx *c, const float *od6, uint64_t n, i
     case PTB_MODE_BVH: {
         unsigned long long *cur = c->dCounters + 7; // slot 7 of the counter block: work cursor of this launch (zeroed above)
         const int gp = (int)std::min<uint64_t>((uint64_t)c->sms * c->extendCtas, (n + 127) / 128);
-        if (count) k_trace_bvh<true><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep);
-        else k_trace_bvh<false><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep);
+        const int leafFrac = c->traceLeafFrac; // off by default: coherent camera rays lose 10 % to it (config 3: 1533 -> 1383 Mrays/s)
+        if (leafFrac > 0) {
+            if (count) k_trace_bvh<true, true><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep, leafFrac);
+            else k_trace_bvh<false, true><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep, leafFrac);
+        } else if (count) k_trace_bvh<true, false><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep, 0);
+        else k_trace_bvh<false, false><<<gp, 128, 0, c->stream>>>(c->S, od6, n, t, tri, c->dIdOfTri, c->dCounters, cur, c->fetchKeep, 0);
         break;
     }
     case PTB_MODE_TWO_PLANE: PTB_TRACE(2); break;

@@ -206,42 +206,65 @@ struct BvhWalk {
             }
         }
     }
-    // one round: descend to the next leaf (or finish), test it, pop.  Returns false when done.
+    // same with the reciprocal direction computed elsewhere (k_duo prepares it in its batched passes)
+    __device__ __forceinline__ void begin_inv(const SceneDev &S, f3 o_, f3 d_, f3 inv_, const Hit &h0) {
+        o = o_;
+        d = d_;
+        inv = inv_;
+        fast = finite3(inv);
+        h = h0;
+        sp = 0;
+        ref = S.n_tris ? S.bvh_root : PTB_REF_DONE;
+    }
+    // one inner node (ref >= 0): both children's boxes, near child next, far child pushed
     template <bool COUNT>
-    __device__ __forceinline__ bool round(const SceneDev &S, int2 *stack, uint32_t &nTri, uint32_t &nBox) {
-        while (ref >= 0) {
-            const float4 *n = S.nodes + 4 * (size_t)ref;
-            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
-            const int4 q3 = __ldg(reinterpret_cast<const int4 *>(n + 3));
-            if (COUNT) nBox += 2;
-            float d0, d1;
-            bool h0, h1;
-            if (fast) {
-                h0 = slab_fast(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
-                h1 = slab_fast(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
-            } else {
-                h0 = slab(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
-                h1 = slab(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
-            }
-            if (h0 && h1) {
-                // bvh.cpp:75-84: left first unless the right child is strictly nearer
-                const bool leftFirst = d1 >= d0;
-                stack[sp++] = make_int2(leftFirst ? q3.y : q3.x, __float_as_int(leftFirst ? d1 : d0));
-                ref = leftFirst ? q3.x : q3.y;
-            } else if (h0) {
-                ref = q3.x;
-            } else if (h1) {
-                ref = q3.y;
-            } else {
-                pop(stack);
-            }
+    __device__ __forceinline__ void node_step(const SceneDev &S, int2 *stack, uint32_t &nBox) {
+        const float4 *n = S.nodes + 4 * (size_t)ref;
+        const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
+        const int4 q3 = __ldg(reinterpret_cast<const int4 *>(n + 3));
+        if (COUNT) nBox += 2;
+        float d0, d1;
+        bool h0, h1;
+        if (fast) {
+            h0 = slab_fast(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
+            h1 = slab_fast(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
+        } else {
+            h0 = slab(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
+            h1 = slab(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
         }
-        if (ref != PTB_REF_DONE) {
-            int first, count;
-            leaf_decode(ref, first, count);
-            for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
+        if (h0 && h1) {
+            // bvh.cpp:75-84: left first unless the right child is strictly nearer
+            const bool leftFirst = d1 >= d0;
+            stack[sp++] = make_int2(leftFirst ? q3.y : q3.x, __float_as_int(leftFirst ? d1 : d0));
+            ref = leftFirst ? q3.x : q3.y;
+        } else if (h0) {
+            ref = q3.x;
+        } else if (h1) {
+            ref = q3.y;
+        } else {
             pop(stack);
         }
+    }
+    // one leaf (ref < 0, not PTB_REF_DONE): its triangles, then the next reference from the stack
+    template <bool COUNT>
+    __device__ __forceinline__ void leaf(const SceneDev &S, const int2 *stack, uint32_t &nTri) {
+        int first, count;
+        leaf_decode(ref, first, count);
+        for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
+        pop(stack);
+    }
+    // one round: descend to the next leaf (or finish), test it, pop.  Returns false when done.
+    // EARLY: leave the node loop once fewer than `minActive` lanes of the warp are still descending — the lanes
+    // that already hold a leaf stop waiting for the last stragglers, which resume next round.  Pays on deep
+    // trees (Lucy stand-in +17 %); on a 100-node tree the vote per step costs more than it saves
+    // (profiles/r1_sweep_mega_leaf.txt), hence a compile-time switch.
+    template <bool COUNT, bool EARLY = false>
+    __device__ __forceinline__ bool round(const SceneDev &S, int2 *stack, uint32_t &nTri, uint32_t &nBox, int minActive = 0) {
+        while (ref >= 0) {
+            node_step<COUNT>(S, stack, nBox);
+            if (EARLY && __popc(__activemask()) < minActive) break;
+        }
+        if ((!EARLY || ref < 0) && ref != PTB_REF_DONE) leaf<COUNT>(S, stack, nTri);
         return ref != PTB_REF_DONE;
     }
 };

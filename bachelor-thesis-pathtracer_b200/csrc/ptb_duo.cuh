@@ -36,6 +36,7 @@ enum : int {
 
 struct DuoSlotBase {
     PathState ps;
+    f3 inv; // 1/direction of the prepared path ray: divided in the batched passes, not at walk set-up
     uint32_t pixel, item;
     int samplesLeft;
     float ht, hu, hv;
@@ -47,6 +48,7 @@ struct DuoSlot : DuoSlotBase {};
 template <>
 struct DuoSlot<true> : DuoSlotBase {
     ShadowRec sr;
+    f3 sinv; // 1/direction of the shadow ray
     float shadowT;
     int shadowTri;
 };
@@ -146,6 +148,7 @@ __global__ void __launch_bounds__(128, PTB_DUO_MINBLOCKS) k_duo(ParamsDev P, Sce
                 ps.flags = 0;
                 roulette(ps.rng, 0, ps.tp);
                 sl[k].ps = ps;
+                sl[k].inv = rcp3(ps.d);
                 set_state(k, SL_READY);
             }
         } else if (what == 1) {
@@ -225,6 +228,7 @@ __global__ void __launch_bounds__(128, PTB_DUO_MINBLOCKS) k_duo(ParamsDev P, Sce
                             sr.cosLight = sh.cosLight;
                             sr.area = sh.area;
                             sl[k].sr = sr;
+                            sl[k].sinv = rcp3(sr.d);
                             ps.flags |= PTB_FLAG_SHADOW;
                             shadow = true;
                             emitted = true;
@@ -275,11 +279,15 @@ __global__ void __launch_bounds__(128, PTB_DUO_MINBLOCKS) k_duo(ParamsDev P, Sce
                 } else {
                     if (NEE && shadow && terminated) ps.flags |= PTB_FLAG_DONE; // only the NEE term is awaited before accumulation
                     sl[k].ps = ps;
+                    sl[k].inv = rcp3(ps.d);
                     set_state(k, (NEE && shadow) ? SL_RSHADOW : SL_READY);
                 }
             }
         } else {
-            // ---- walk: rounds for the lanes that hold a ray, until a pass is due -----------------------
+            // ---- walk, until a pass is due ---------------------------------------------------------------
+            // Warp-synchronous while-while: the node loop is left as soon as `leaf_keep` lanes hold a leaf or
+            // a finished ray (instead of when the last lane does), so the box tests — three quarters of the
+            // traversal work — run with most lanes, and the triangle tests with the lanes that have one.
             for (;;) {
                 if (cur < 0) { // take the lane's next prepared ray (the only copy of the walk set-up)
                     const int k = (st0 == SL_READY || st0 == SL_RSHADOW) ? 0 : ((st1 == SL_READY || st1 == SL_RSHADOW) ? 1 : -1);
@@ -289,12 +297,12 @@ __global__ void __launch_bounds__(128, PTB_DUO_MINBLOCKS) k_duo(ParamsDev P, Sce
                         if (isShadow) {
                             if constexpr (NEE) {
                                 const int lt = sl[k].sr.lightTri;
-                                w.begin(S, sl[k].sr.o, sl[k].sr.d, Hit{sl[k].sr.tmax0, lt, 0.0f, 0.0f, __float_as_int(__ldg(&S.tri[3 * lt]).w)});
+                                w.begin_inv(S, sl[k].sr.o, sl[k].sr.d, sl[k].sinv, Hit{sl[k].sr.tmax0, lt, 0.0f, 0.0f, __float_as_int(__ldg(&S.tri[3 * lt]).w)});
                             }
                             cShadow++;
                             set_state(k, SL_WSHADOW);
                         } else {
-                            w.begin(S, sl[k].ps.o, sl[k].ps.d, Hit{PTB_INF, -1, 0.0f, 0.0f, -1});
+                            w.begin_inv(S, sl[k].ps.o, sl[k].ps.d, sl[k].inv, Hit{PTB_INF, -1, 0.0f, 0.0f, -1});
                             nTri = nAS = 0;
                             cRays++;
                             set_state(k, SL_WALK);
@@ -302,44 +310,52 @@ __global__ void __launch_bounds__(128, PTB_DUO_MINBLOCKS) k_duo(ParamsDev P, Sce
                         cur = k;
                     }
                 }
-                if (cur >= 0) {
-                    const bool isMain = state(cur) == SL_WALK;
-                    bool cont;
-                    if (MODE == 1) {
-                        if (COUNT && isMain) cont = w.round<true>(S, stack, nTri, nAS);
-                        else cont = w.round<false>(S, stack, nTri, nAS);
-                    } else {
-                        if (COUNT && isMain) closest_hit<MODE, true>(S, w.o, w.d, w.h, nTri, nAS);
-                        else {
-                            uint32_t a = 0, b = 0;
-                            closest_hit<MODE, false>(S, w.o, w.d, w.h, a, b);
+                const bool isMain = cur >= 0 && state(cur) == SL_WALK;
+                if (MODE == 1) {
+                    for (;;) {
+                        const bool inNode = cur >= 0 && w.ref >= 0;
+                        if (!__ballot_sync(full, inNode)) break;
+                        if (__popc(__ballot_sync(full, cur >= 0 && w.ref < 0)) >= M.leaf_keep) break;
+                        if (inNode) {
+                            if (COUNT && isMain) w.node_step<true>(S, stack, nAS);
+                            else w.node_step<false>(S, stack, nAS);
                         }
-                        cont = false;
                     }
-                    if (!cont) {
-                        bool park = true;
-                        if constexpr (NEE) {
-                            if (!isMain) {
-                                sl[cur].shadowT = w.h.t;
-                                sl[cur].shadowTri = w.h.tri;
-                                park = false;
-                                // the DONE branch of the logic pass ignores the path hit; otherwise the path ray is next
-                                set_state(cur, (sl[cur].ps.flags & PTB_FLAG_DONE) ? SL_LOGIC : SL_READY);
-                            }
-                        }
-                        if (park) {
-                            sl[cur].ht = w.h.t;
-                            sl[cur].htri = w.h.tri;
-                            sl[cur].hu = w.h.u;
-                            sl[cur].hv = w.h.v;
-                            if (COUNT) {
-                                sl[cur].nTri = nTri;
-                                sl[cur].nAS = nAS;
-                            }
-                            set_state(cur, SL_LOGIC);
-                        }
-                        cur = -1;
+                    if (cur >= 0 && w.ref < 0 && w.ref != PTB_REF_DONE) {
+                        if (COUNT && isMain) w.leaf<true>(S, stack, nTri);
+                        else w.leaf<false>(S, stack, nTri);
                     }
+                } else if (cur >= 0) {
+                    if (COUNT && isMain) closest_hit<MODE, true>(S, w.o, w.d, w.h, nTri, nAS);
+                    else {
+                        uint32_t a = 0, b = 0;
+                        closest_hit<MODE, false>(S, w.o, w.d, w.h, a, b);
+                    }
+                    w.ref = PTB_REF_DONE;
+                }
+                if (cur >= 0 && w.ref == PTB_REF_DONE) {
+                    bool park = true;
+                    if constexpr (NEE) {
+                        if (!isMain) {
+                            sl[cur].shadowT = w.h.t;
+                            sl[cur].shadowTri = w.h.tri;
+                            park = false;
+                            // the DONE branch of the logic pass ignores the path hit; otherwise the path ray is next
+                            set_state(cur, (sl[cur].ps.flags & PTB_FLAG_DONE) ? SL_LOGIC : SL_READY);
+                        }
+                    }
+                    if (park) {
+                        sl[cur].ht = w.h.t;
+                        sl[cur].htri = w.h.tri;
+                        sl[cur].hu = w.h.u;
+                        sl[cur].hv = w.h.v;
+                        if (COUNT) {
+                            sl[cur].nTri = nTri;
+                            sl[cur].nAS = nAS;
+                        }
+                        set_state(cur, SL_LOGIC);
+                    }
+                    cur = -1;
                 }
                 const int walkers = __popc(__ballot_sync(full, cur >= 0 || st0 == SL_READY || st0 == SL_RSHADOW || st1 == SL_READY || st1 == SL_RSHADOW));
                 const int waitL = __popc(__ballot_sync(full, st0 == SL_LOGIC || st1 == SL_LOGIC));

@@ -648,11 +648,11 @@ __global__ void __launch_bounds__(128) k_trace(SceneDev S, const float *__restri
 }
 
 // ptb_trace_rays in BVH mode: the persistent dynamic-fetch loop of k_extend_bvh over caller rays.
-template <bool COUNT>
+template <bool COUNT, bool EARLY>
 __global__ void __launch_bounds__(128) k_trace_bvh(SceneDev S, const float *__restrict__ od6, uint64_t n, float *__restrict__ tOut,
                                                    int *__restrict__ triOut, const uint32_t *__restrict__ idOfTri,
                                                    unsigned long long *__restrict__ counters, unsigned long long *__restrict__ cursor,
-                                                   int fetchKeep) {
+                                                   int fetchKeep, int leafFrac) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     BvhWalk w;
@@ -688,7 +688,7 @@ __global__ void __launch_bounds__(128) k_trace_bvh(SceneDev S, const float *__re
             continue;
         }
         do {
-            if (active && !w.round<COUNT>(S, stack, nTri, nAS)) {
+            if (active && !w.round<COUNT, EARLY>(S, stack, nTri, nAS, (__popc(act) * leafFrac) >> 5)) {
                 tOut[ray] = w.h.t;
                 triOut[ray] = w.h.tri >= 0 ? (int)idOfTri[w.h.tri] : -1;
                 cTri += nTri;

@@ -48,13 +48,15 @@ struct MegaArgs {
     int first_sample;       // sample count every owned pixel has when the render starts (uniform state)
     int check_ready;        // 1: chunked mode, wait for the pixel's previous chunk
     int logic_keep;
+    int sample_keep, walk_min, refill_min, leaf_keep; // k_duo only (ptb_duo.cuh)
     unsigned long long *cursor;   // work-item cursor (zeroed per launch)
     unsigned long long *counters; // [0] paths [1] reference rays [2] tri tests [3] AS tests [5] path rays [6] shadow rays
 };
 
+// EARLY (BVH only): BvhWalk::round leaves its node loop when fewer than leaf_keep/32 of the walking lanes still descend.
 // NEE = false compiles the shadow-ray state machine and its 19 words of per-lane state out (the reference's
 // own --testing protocol renders with NEE off, main.cpp:101).
-template <int MODE, bool COUNT, bool NEE>
+template <int MODE, bool COUNT, bool NEE, bool EARLY = false>
 __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, MegaArgs M) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -262,12 +264,13 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
             }
         } else {
             // ---- C. traversal rounds for the walking lanes, until enough lanes wait for logic ------
+            int minActive = EARLY ? (__popc(walking) * M.leaf_keep) >> 5 : 0; // fewer descending lanes than this: go test the leaves
             for (;;) {
                 if (phase == LANE_SHADOW || phase == LANE_MAIN) {
                     bool cont;
                     if (MODE == 1) {
-                        if (COUNT && phase == LANE_MAIN) cont = w.round<true>(S, stack, nTri, nAS);
-                        else cont = w.round<false>(S, stack, nTri, nAS);
+                        if (COUNT && phase == LANE_MAIN) cont = w.round<true, EARLY>(S, stack, nTri, nAS, minActive);
+                        else cont = w.round<false, EARLY>(S, stack, nTri, nAS, minActive);
                     } else {
                         if (COUNT && phase == LANE_MAIN) closest_hit<MODE, true>(S, w.o, w.d, w.h, nTri, nAS);
                         else {
@@ -290,6 +293,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                 const unsigned stillWalking = __ballot_sync(full, phase == LANE_SHADOW || phase == LANE_MAIN);
                 const unsigned waiting = __ballot_sync(full, phase == LANE_LOGIC);
                 if (!stillWalking || __popc(waiting) >= M.logic_keep) break;
+                if (EARLY) minActive = (__popc(stillWalking) * M.leaf_keep) >> 5;
             }
         }
     }

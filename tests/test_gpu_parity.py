@@ -258,11 +258,11 @@ def test_sample_sharded_frame_is_statistically_equivalent(gpu, ptb):
     assert abs(sharded.mean() - ref.mean()) <= 0.03 * ref.mean()
 
 
-def test_three_schedulers_give_identical_frames(ptb, cornel_ptbs, monkeypatch):
-    """The path kernels (PTB_MEGA=1 persistent lanes [default], 2 warp pools) and the wavefront pipeline (0)
+def test_schedulers_give_identical_frames(ptb, cornel_ptbs, monkeypatch):
+    """The path kernels (PTB_MEGA=1 persistent lanes, 3 two paths per lane, 2 warp pools) and the wavefront pipeline (0)
     share the arithmetic and differ only in scheduling: frames, RNG states and counters must be bit-identical."""
     outs = []
-    for sched in ("1", "2", "0"):
+    for sched in ("1", "3", "2", "0"):
         monkeypatch.setenv("PTB_MEGA", sched)
         pt = ptb.PathTracer(0)
         pt.load_ptbs(cornel_ptbs)
