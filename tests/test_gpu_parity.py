@@ -332,3 +332,40 @@ def test_async_render_and_edge_cases(ptb, cornel_ptbs, gpu):
     assert (img[..., :3] == 0).all() and (pt2.read_state()[0] == 2).all()
     pt2.close()
     pt.close()
+
+
+def test_full_size_config2_properties(ptb, cornel_ptbs, gpu):
+    """BASELINE config 2 at its full size (1024x1024, 64 spp, max_depth 5, NEE off) through properties that do not
+    need the CPU oracle to finish: exact path / sample / ray bookkeeping, finite non-negative radiance, the
+    one-shot frame equal to 16+48 progressive samples and to the union of 8 tile-sharded ranks.  (Bit equality
+    with the oracle for the same configuration at 128x128 is test_render_depth_capped[5].)"""
+    Wf = Hf = 1024
+    spp = 64
+    gpu.set_params(width=Wf, height=Hf, mode=MODE_BVH, nee=0, max_depth=5, rank=0, world=1)
+    gpu.reset()
+    gpu.render(spp)
+    full = gpu.read_image()
+    samples, rng = gpu.read_state()
+    c = gpu.counters()
+    assert (samples == spp).all()
+    assert c["paths"] == Wf * Hf * spp
+    assert Wf * Hf * spp < c["rays"] <= 5 * Wf * Hf * spp  # primary + at most 4 bounces
+    assert c["ref_rays"] >= c["rays"]                        # the reference re-traces misses
+    assert np.isfinite(full).all() and (full[..., :3] >= 0).all() and (full[..., 3] == 1).all()
+    assert 0.05 < full[..., :3].mean() < 5.0
+    # progressive == one shot (the RNG stream and the N+1 law carry across ptb_render calls)
+    gpu.reset()
+    gpu.render(16)
+    gpu.render(48)
+    again = gpu.read_image()
+    assert (again.view(np.uint32) == full.view(np.uint32)).all()
+    assert (gpu.read_state()[1] == rng).all()
+    # 8 ranks' tiles (the 8-GPU partition, rendered one after another on this device) == the frame
+    acc = np.zeros_like(full)
+    for r in range(8):
+        gpu.set_params(rank=r, world=8, tile_w=32, tile_h=8)
+        gpu.reset()
+        gpu.render(spp)
+        acc += gpu.read_image()
+    gpu.set_params(rank=0, world=1)
+    assert (acc.view(np.uint32) == full.view(np.uint32)).all()
