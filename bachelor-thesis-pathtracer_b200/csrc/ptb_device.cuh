@@ -166,7 +166,9 @@ __device__ __forceinline__ bool slab_fast(f3 lo, f3 hi, f3 o, f3 inv, float tmax
 }
 __device__ __forceinline__ bool finite3(f3 v) { return fabsf(v.x) < PTB_INF && fabsf(v.y) < PTB_INF && fabsf(v.z) < PTB_INF; }
 
+#ifndef PTB_STACK
 #define PTB_STACK 64
+#endif
 #define PTB_GSTACK 160 /* Subgrid: <= 16 children pushed per level */
 #define PTB_REF_DONE ((int)0x80000000) /* never a leaf reference: first < 2^27 - 1 */
 
