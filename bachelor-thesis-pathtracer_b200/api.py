@@ -22,6 +22,7 @@ SYMBOLS = (
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
     "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
+    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth",
 )
 
 
@@ -64,6 +65,10 @@ def load_library():
     L.ptb_load_ptbs.argtypes = [vp, ctypes.c_char_p]
     L.ptb_set_camera.argtypes = [vp, ctypes.POINTER(Camera)]
     L.ptb_build_bvh.argtypes = [vp]
+    L.ptb_build_bvh_gpu.argtypes = [vp]
+    L.ptb_last_build_ms.argtypes = [vp]
+    L.ptb_last_build_ms.restype = ctypes.c_double
+    L.ptb_bvh_depth.argtypes = [vp]
     L.ptb_build_subgrid.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_build_subbeams.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_set_build_limits.argtypes = [vp, ci]
@@ -154,8 +159,16 @@ class PathTracer:
         self._ck(self.L.ptb_set_camera(self.h, ctypes.byref(cam)), "ptb_set_camera")
 
     # ---- structures --------------------------------------------------------------------------
-    def build_bvh(self):
-        self._ck(self.L.ptb_build_bvh(self.h), "ptb_build_bvh")
+    def build_bvh(self, gpu=False):
+        """constructBVH: host binned-SAH builder, or (gpu=True) the Morton/radix-tree builder that runs in HBM."""
+        if gpu:
+            self._ck(self.L.ptb_build_bvh_gpu(self.h), "ptb_build_bvh_gpu")
+        else:
+            self._ck(self.L.ptb_build_bvh(self.h), "ptb_build_bvh")
+        return float(self.L.ptb_last_build_ms(self.h))
+
+    def bvh_depth(self):
+        return int(self.L.ptb_bvh_depth(self.h))
 
     def build_subgrid(self, gs=10, os_=5, m=40):
         self._ck(self.L.ptb_build_subgrid(self.h, gs, os_, m), "ptb_build_subgrid")

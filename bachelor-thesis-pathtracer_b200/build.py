@@ -1,22 +1,25 @@
-"""Builds libptb.so in-tree with nvcc for sm_100a (no JIT cache: the .so travels with the repo)."""
+"""Builds libptb.so in-tree with nvcc for sm_100a (no JIT cache: the .so travels with the repo).
+One object per translation unit under csrc/build/ (git-ignored), recompiled only when the unit or a
+header it includes changed, then one link."""
 import os
+import re
 import shutil
 import subprocess
+from concurrent.futures import ThreadPoolExecutor
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 OUT = os.path.join(_HERE, "libptb.so")
+OBJDIR = os.path.join(CSRC, "build")
 
-SOURCES = ["ptb_api.cu", "ptb_bvh_build.cpp", "ptb_grid_build.cpp"]
-HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h")))
+SOURCES = ["ptb_api.cu", "ptb_lbvh.cu", "ptb_bvh_build.cpp", "ptb_grid_build.cpp"]
 
 # -fmad=false / -prec-div / -prec-sqrt / -ftz=false: the arithmetic contract of ptb_device.cuh
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
     "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-pthread",
-    "-shared",
 ]
 
 
@@ -27,25 +30,56 @@ def _nvcc():
     raise RuntimeError("nvcc not found")
 
 
-def _stale():
-    if not os.path.isfile(OUT):
+_INC = re.compile(r'^\s*#\s*include\s+"([^"]+)"', re.M)
+
+
+def _deps(path, seen=None):
+    """the file plus every quoted include reachable from it (csrc/ and include/)"""
+    seen = set() if seen is None else seen
+    if path in seen or not os.path.isfile(path):
+        return seen
+    seen.add(path)
+    with open(path) as f:
+        for name in _INC.findall(f.read()):
+            for d in (CSRC, INCLUDE):
+                _deps(os.path.join(d, name), seen)
+    return seen
+
+
+def _newer(deps, target):
+    if not os.path.isfile(target):
         return True
-    t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS] + [os.path.join(INCLUDE, "ptb.h"), os.path.join(INCLUDE, "ptbs_format.h")]
+    t = os.path.getmtime(target)
     return any(os.path.getmtime(d) > t for d in deps)
+
+
+def _run(cmd):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + r.stdout[-6000:])
+    return r.stdout
 
 
 def build_native(force=False, verbose=False, defines=(), out=None):
     """Compile csrc/ into libptb.so if sources are newer than the library.  `defines`/`out` build a
     tuning variant beside it (loaded with PTB_LIB=<path>; scripts/ only)."""
+    variant = bool(defines) or bool(out)
     out = out or OUT
-    if not force and not defines and not _stale():
-        return OUT
-    cmd = [_nvcc()] + NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + \
-        ["-I", INCLUDE, "-o", out] + [os.path.join(CSRC, s) for s in SOURCES]
-    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-    if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + r.stdout[-6000:])
+    objdir = OBJDIR + ("_variant" if variant else "")
+    os.makedirs(objdir, exist_ok=True)
+    flags = NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else [])
+    jobs = []
+    for s in SOURCES:
+        src = os.path.join(CSRC, s)
+        obj = os.path.join(objdir, os.path.splitext(s)[0] + ".o")
+        if force or variant or _newer(_deps(src) | {os.path.abspath(__file__)}, obj):
+            jobs.append([_nvcc()] + flags + ["-I", INCLUDE, "-c", "-o", obj, src])
+    objs = [os.path.join(objdir, os.path.splitext(s)[0] + ".o") for s in SOURCES]
+    if not jobs and not _newer(objs, out):
+        return out
+    with ThreadPoolExecutor(max_workers=4) as ex:
+        logs = list(ex.map(_run, jobs))
     if verbose:
-        print(r.stdout)
+        print("\n".join(logs))
+    _run([_nvcc(), "-shared", "-Xcompiler", "-pthread", "-o", out] + objs)
     return out

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -14,6 +15,7 @@
 #include "ptb.h"
 #include "ptb_bvh_build.h"
 #include "ptb_grid_build.h"
+#include "ptb_lbvh.h"
 #include "ptb_kernels.cuh"
 #include "ptb_mega.cuh"
 #include "ptb_pool.cuh"
@@ -91,6 +93,9 @@ struct ptb_ctx {
     // structures
     BvhResult bvh;
     bool bvhBuilt = false, gridBuilt = false, beamBuilt = false;
+    bool bvhOnGpu = false;   // built by ptb_build_bvh_gpu: no host copy of the nodes (c->bvh holds order + bounds only)
+    uint64_t bvhNodes = 0;   // inner nodes of the tree in HBM
+    double lastBuildMs = 0.0; // ptb_last_build_ms
     std::vector<uint32_t> triOfId; // reference id -> leaf position
     uint64_t gridBytes = 0, beamBytes = 0;
 
@@ -482,7 +487,9 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
 extern "C" int ptb_build_bvh(ptb_ctx *c) {
     GUARD(c);
     const uint64_t n = c->mat.size();
+    const auto t0 = std::chrono::steady_clock::now();
     build_bvh(c->pos9.data(), n, c->leafMax, c->bvh);
+    c->lastBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     // the walk pushes one deferred child per level: the tree must fit the per-lane stack
     if (c->bvh.max_depth >= PTB_STACK) return fail(c, PTB_ERR_INVALID, "BVH deeper than the traversal stack (PTB_STACK): degenerate input?");
     // leaf-ordered device arrays: positions as (v0, e1, e2) with the reference id in v0.w,
@@ -530,9 +537,70 @@ extern "C" int ptb_build_bvh(ptb_ctx *c) {
     c->A.id_of_tri = c->dIdOfTri;
     c->A.vtx = c->dVtx;
     c->bvhBuilt = true;
+    c->bvhOnGpu = false;
+    c->bvhNodes = c->bvh.nodes.size();
     c->gridBuilt = c->beamBuilt = false;
     return PTB_OK;
 }
+
+// constructBVH on the device (ptb_lbvh.cu): the triangles go up once in reference order, everything else —
+// keys, sort, hierarchy, boxes, nodes, leaf-ordered arrays — is produced in HBM.  The only host copies
+// kept are the leaf order (Subbeam builder input) and the scene bounds.
+extern "C" int ptb_build_bvh_gpu(ptb_ctx *c) {
+    GUARD(c);
+    SETTLE(c);
+    const uint64_t n = c->mat.size();
+    devFree(c->dTri); devFree(c->dNrm); devFree(c->dNodes); devFree(c->dTriOfId); devFree(c->dIdOfTri); devFree(c->dVtx);
+    c->bvhBuilt = c->gridBuilt = c->beamBuilt = false;
+    float *dNrm9 = nullptr;
+    int32_t *dMat = nullptr;
+    CK(cudaMalloc(&c->dVtx, std::max<size_t>(1, 9 * n) * sizeof(float)));
+    cudaError_t e = cudaMalloc(&dNrm9, std::max<size_t>(1, 9 * n) * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&dMat, std::max<size_t>(1, n) * sizeof(int32_t));
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(c->dVtx, c->pos9.data(), 9 * n * sizeof(float), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(dNrm9, c->nrm9.data(), 9 * n * sizeof(float), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(dMat, c->mat.data(), n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream);
+    LbvhResult R;
+    std::string msg;
+    if (e == cudaSuccess) e = lbvh_build(c->dVtx, dNrm9, dMat, n, c->leafMax, PTB_STACK, c->stream, R, msg);
+    else msg = std::string("staging the triangles: ") + cudaGetErrorString(e);
+    cudaFree(dNrm9);
+    cudaFree(dMat);
+    if (e != cudaSuccess) {
+        if (e != cudaErrorInvalidValue) c->poisoned = true;
+        return fail(c, e == cudaErrorInvalidValue ? PTB_ERR_INVALID : PTB_ERR_CUDA, msg);
+    }
+    c->dTri = R.tri; c->dNrm = R.nrm; c->dNodes = R.nodes; c->dTriOfId = R.tri_of_id; c->dIdOfTri = R.id_of_tri;
+    if (R.height >= PTB_STACK) {
+        devFree(c->dTri); devFree(c->dNrm); devFree(c->dNodes); devFree(c->dTriOfId); devFree(c->dIdOfTri);
+        return fail(c, PTB_ERR_INVALID, "BVH deeper than the traversal stack (PTB_STACK): degenerate input?");
+    }
+    c->bvh = BvhResult();
+    c->bvh.root = R.root;
+    c->bvh.max_depth = R.height;
+    c->bvh.order.resize(n);
+    if (n) CK(cudaMemcpy(c->bvh.order.data(), c->dIdOfTri, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 3; ++k) {
+        c->bvh.lo[k] = R.lo[k];
+        c->bvh.hi[k] = R.hi[k];
+    }
+    c->triOfId.clear();
+    c->S.tri = c->dTri;
+    c->S.nodes = c->dNodes;
+    c->S.bvh_root = R.root;
+    c->S.n_tris = (uint32_t)n;
+    c->A.nrm = c->dNrm;
+    c->A.tri_of_id = c->dTriOfId;
+    c->A.id_of_tri = c->dIdOfTri;
+    c->A.vtx = c->dVtx;
+    c->bvhBuilt = c->bvhOnGpu = true;
+    c->bvhNodes = R.n_nodes;
+    c->lastBuildMs = R.ms;
+    return PTB_OK;
+}
+
+extern "C" double ptb_last_build_ms(const ptb_ctx *c) { return c ? c->lastBuildMs : 0.0; }
+extern "C" int ptb_bvh_depth(const ptb_ctx *c) { return (c && c->bvhBuilt) ? c->bvh.max_depth : -1; }
 
 extern "C" int ptb_set_build_limits(ptb_ctx *c, int beam_max_depth) {
     GUARD(c);
@@ -544,7 +612,7 @@ extern "C" int ptb_set_build_limits(ptb_ctx *c, int beam_max_depth) {
 extern "C" uint64_t ptb_structure_bytes(const ptb_ctx *c, int mode) {
     if (!c) return 0;
     const uint64_t tris = (uint64_t)c->mat.size() * 48ull;
-    if (mode == PTB_MODE_BVH) return c->bvhBuilt ? c->bvh.nodes.size() * sizeof(BvhNode64) + tris : 0;
+    if (mode == PTB_MODE_BVH) return c->bvhBuilt ? c->bvhNodes * sizeof(BvhNode64) + tris : 0;
     if (mode == PTB_MODE_TWO_PLANE) return c->gridBuilt ? c->gridBytes + tris : 0;
     if (mode == PTB_MODE_SUB_BEAMS) return c->beamBuilt ? c->beamBytes + tris : 0;
     return tris;
@@ -1166,10 +1234,51 @@ static void leaf_positions(const ptb_ctx *c, std::vector<float> &out) {
     for (size_t k = 0; k < n; ++k) memcpy(&out[9 * k], &c->pos9[9 * (size_t)c->bvh.order[k]], 36);
 }
 
+// A tree built by ptb_build_bvh_gpu exists only in HBM; the Subgrid builder walks it on the host, so mirror the
+// nodes once and derive the leaf-order range of every child (ranges are contiguous: children cover
+// [first, first+count) of their parent's range, a leaf reference carries its own).
+static int mirror_gpu_bvh(ptb_ctx *c) {
+    if (!c->bvhOnGpu || c->bvh.nodes.size() == c->bvhNodes) return PTB_OK;
+    c->bvh.nodes.resize(c->bvhNodes);
+    if (c->bvhNodes) CK(cudaMemcpy(c->bvh.nodes.data(), c->dNodes, c->bvhNodes * sizeof(BvhNode64), cudaMemcpyDeviceToHost));
+    c->bvh.ranges.assign(2 * c->bvhNodes, BvhRange{0, 0});
+    auto leaf_range = [](int32_t ref) {
+        const uint32_t r = (uint32_t)~ref;
+        return BvhRange{r >> 4, (r & 15u) + 1u};
+    };
+    // children have larger indices than their parent only in the SAH builder; here use an explicit post-order
+    std::vector<std::pair<int32_t, int>> st;
+    if (c->bvh.root >= 0) st.push_back({c->bvh.root, 0});
+    while (!st.empty()) {
+        auto &[node, phase] = st.back();
+        const BvhNode64 &nd = c->bvh.nodes[node];
+        if (phase == 0) {
+            phase = 1;
+            const int32_t a = nd.c0, b = nd.c1;
+            if (a >= 0) st.push_back({a, 0});
+            if (b >= 0) st.push_back({b, 0});
+            continue;
+        }
+        for (int w = 0; w < 2; ++w) {
+            const int32_t ch = w ? nd.c1 : nd.c0;
+            BvhRange r;
+            if (ch < 0) r = leaf_range(ch);
+            else {
+                const BvhRange &a = c->bvh.ranges[2 * (size_t)ch], &b = c->bvh.ranges[2 * (size_t)ch + 1];
+                r = BvhRange{std::min(a.first, b.first), a.count + b.count};
+            }
+            c->bvh.ranges[2 * (size_t)node + w] = r;
+        }
+        st.pop_back();
+    }
+    return PTB_OK;
+}
+
 extern "C" int ptb_build_subgrid(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
     GUARD(c);
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (the Subgrid hierarchy derives from the BVH)");
     if (gs < 1 || gs > 64 || os < 1 || os > 64) return fail(c, PTB_ERR_INVALID, "grid sizes must be 1..64");
+    if (int r = mirror_gpu_bvh(c)) return r;
     std::vector<float> leaf;
     leaf_positions(c, leaf);
     SubgridResult R;

@@ -228,6 +228,19 @@ def triangle_soup(n, seed=None):
             "materials": mats, "camera": {"pos": [0.0, 0.0, -400.0], "forward": [0.0, 0.0, 1.0], "focus": 1.0, "dof": 0.0}}
 
 
+def scene_from_triangles(pos):
+    """A one-object, one-material lambert scene over explicit triangles (n x 9 floats; n may be 0) — edge-case tests."""
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 9)
+    n = pos.shape[0]
+    mats = [{"albedo": [0.8, 0.8, 0.8], "ior1": 1.0, "ior2": 1.5, "emission": 0.0, "roughness": 0.5, "weights": [1, 0, 0],
+             "name": "Plain"}]
+    nrm = _flat_normals(pos) if n else np.zeros((0, 9), np.float32)
+    area = float(_tri_area(pos).sum()) if n else 0.0
+    return {"pos": pos, "nrm": nrm, "uv": np.zeros((n, 6), np.float32), "mat": np.zeros(n, np.int32),
+            "objects": [{"start": 0, "end": n, "area": area, "materials": [0], "name": "Plain"}],
+            "materials": mats, "camera": {"pos": [0.0, 0.0, -5.0], "forward": [0.0, 0.0, 1.0], "focus": 1.0, "dof": 0.0}}
+
+
 def soup_rays(n, seed=99):
     """Config 5 rays: origin uniform on the sphere r = 250, direction towards a uniform point of [-100,100]^3
     (incoherent), normalised in float32.  [n, 6] float32."""

@@ -204,7 +204,7 @@ def run_ours(args):
     pt = ptb_b200.PathTracer(local)
     sc.upload_scene(pt, scene)
     t0 = time.perf_counter()
-    pt.build_bvh()
+    pt.build_bvh(gpu=args.builder == "gpu")
     if args.structure == "subgrid":
         pt.build_subgrid(8, 8, 50)
         mode = 2
@@ -340,7 +340,7 @@ def run_ours(args):
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["name"], "width": W, "height": H, "spp": spp, "max_depth": wl["max_depth"], "nee": 0,
-                       "structure": {"bvh": "BVH2, 64-byte two-box nodes", "subgrid": "Subgrid / 2Plane hierarchy gs 8 os 8 m 50",
+                       "structure": {"bvh": "BVH2, 64-byte two-box nodes" + (" (built on the GPU: Morton radix tree)" if args.builder == "gpu" else " (host binned SAH)"), "subgrid": "Subgrid / 2Plane hierarchy gs 8 os 8 m 50",
                                      "subbeams": "Subbeams gs 6 m 50 depth 1"}[args.structure], "triangles": int(scene["pos"].shape[0]),
                        "parallelism": "1 GPU" if world == 1 else (f"tiles32x8 round-robin over {world} GPUs, NCCL sum-reduce to rank 0 (bit-identical to 1 GPU)"
                                                                  if shard == "tiles" else
@@ -390,6 +390,8 @@ def main():
     ap.add_argument("--ref-spp", type=int, default=4, help="spp per step of the --impl reference arm")
     ap.add_argument("--structure", default="bvh", choices=["bvh", "subgrid", "subbeams"],
                     help="acceleration structure (subgrid: gs 8 / os 8 / m 50 like the published runs; subbeams: gs 6 / m 50 / depth 1)")
+    ap.add_argument("--builder", default="host", choices=["host", "gpu"],
+                    help="BVH construction: host binned SAH (default, the better tree) or ptb_build_bvh_gpu (Morton radix tree built in HBM)")
     ap.add_argument("--shard", default="auto", choices=["auto", "tiles", "samples"], help="multi-GPU partition of the frame")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--res", default="", help="override the frame size WxH (experiments only)")

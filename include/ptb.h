@@ -98,6 +98,12 @@ int ptb_set_camera_basis(ptb_ctx *ctx, const float origin[3], const float forwar
  * Builders run on the host inside the library (construction is outside the timed path in the
  * reference too, main.cpp:97 vs :116) and upload flattened device layouts. */
 int ptb_build_bvh(ptb_ctx *ctx);                                        /* constructBVH, bvh.h:33 (scene.cpp:113-120) */
+/* constructBVH on the device (bvh.cpp:116-189,222-390 is 7.2 s at 1e5 triangles and superlinear):
+ * Morton keys + radix sort + radix-tree hierarchy + bottom-up boxes, all in HBM (csrc/ptb_lbvh.cu).  Same node and
+ * triangle layouts, same closest hits (they do not depend on the tree); visit counts differ from the SAH tree. */
+int ptb_build_bvh_gpu(ptb_ctx *ctx);
+double ptb_last_build_ms(const ptb_ctx *ctx); /* last ptb_build_bvh (host wall clock) / ptb_build_bvh_gpu (device time, CUDA events) */
+int ptb_bvh_depth(const ptb_ctx *ctx);        /* inner nodes on the longest root-to-leaf chain (< PTB_STACK, the per-lane traversal stack); -1 before a build */
 int ptb_build_subgrid(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m); /* setGridSettings + constructGrid, lightFieldGrid.h:24,26 */
 int ptb_build_subbeams(ptb_ctx *ctx, uint32_t gs, uint32_t m);          /* setGridBeamsSettings + buildGridsWithSubBeams, lightFieldGridSubBeams.h:28-29 */
 /* The reference's Subbeam recursion has no depth limit (lightFieldGridSubBeams.cpp:286-324) and does not

@@ -1,6 +1,8 @@
 #!/usr/bin/env python
 """BASELINE config 5: triangle-soup sweep, incoherent rays, traversal Mrays/s and algorithmic GB/s per
-structure.  usage: config5_soup_sweep.py [max_log10_n=7] [log2_rays=24].  Writes gpurun_out/config5.json."""
+structure.  usage: config5_soup_sweep.py [max_log10_n=7] [log2_rays=24] [min_log10_n=4].  Writes gpurun_out/config5.json.
+Up to 10^7 triangles the BVH is built twice — host binned SAH and on the GPU (ptb_build_bvh_gpu) — and both trees
+must return identical hits; 10^8 is built on the GPU only and cross-checked against brute force on a ray subset."""
 import json
 import os
 import sys
@@ -15,12 +17,13 @@ import ptb_b200  # noqa: E402
 
 max_log = int(sys.argv[1]) if len(sys.argv) > 1 else 7
 nrays = 1 << (int(sys.argv[2]) if len(sys.argv) > 2 else 24)
+min_log = int(sys.argv[3]) if len(sys.argv) > 3 else 4
 sc = ptb_b200.scenes
 rays = torch.from_numpy(sc.soup_rays(nrays)).cuda()
 t_out = torch.empty(nrays, dtype=torch.float32, device="cuda")
 tri_out = torch.empty(nrays, dtype=torch.int32, device="cuda")
 res = []
-for lg in range(4, max_log + 1):
+for lg in range(min_log, max_log + 1):
     n = 10 ** lg
     t0 = time.perf_counter()
     scene = sc.triangle_soup(n)
@@ -28,14 +31,15 @@ for lg in range(4, max_log + 1):
     pt = ptb_b200.PathTracer(0)
     sc.upload_scene(pt, scene)
     del scene
-    structs = [("BVH", 1, lambda: pt.build_bvh())]
+    structs = [("BVH", 1, lambda: pt.build_bvh())] if lg <= 7 else []
     if lg <= 5:
         structs.append(("Subgrid gs6 os4 m40", 2, lambda: pt.build_subgrid(6, 4, 40)))
     if lg <= 4:
         structs.append(("Subbeams gs4 m40 depth2", 3, lambda: pt.build_subbeams(4, 40, max_depth=2)))
+    structs.append(("BVH built on the GPU", 1, lambda: pt.build_bvh(gpu=True)))  # last: it replaces the tree the Subgrid derives from
     for name, mode, build in structs:
         t0 = time.perf_counter()
-        build()
+        build_ms = build()
         bs = time.perf_counter() - t0
         pt.set_params(width=64, height=64, mode=mode, count_tests=1)
         sub = min(nrays, 1 << 20)
@@ -48,9 +52,21 @@ for lg in range(4, max_log + 1):
             ms.append(pt.trace_rays_device(rays.data_ptr(), nrays, mode, t_out.data_ptr(), tri_out.data_ptr()))
         best = min(ms[1:])
         bpr = 24 + 8 + 32 * boxes + 36 * tris
-        rec = {"n": n, "structure": name, "build_s": bs, "bytes": pt.structure_bytes(mode), "ms": best, "mrays_s": nrays / best / 1e3,
+        rec = {"n": n, "structure": name, "build_s": bs, "build_ms_reported": build_ms, "bvh_depth": pt.bvh_depth() if mode == 1 else None, "bytes": pt.structure_bytes(mode), "ms": best, "mrays_s": nrays / best / 1e3,
                "as_tests_per_ray": boxes, "tri_tests_per_ray": tris, "algorithmic_bytes_per_ray": bpr,
                "algorithmic_gb_s": bpr * nrays / best / 1e6, "hit_fraction": float((t_out < float("inf")).float().mean())}
+        if mode == 1:  # both trees (and brute force at 10^8) must agree hit for hit
+            t_h, tri_h = t_out.cpu().numpy().copy(), tri_out.cpu().numpy().copy()
+            if name == "BVH":
+                sah_hits = (t_h, tri_h)
+            elif lg <= 7:
+                rec["hits_equal_to_sah_tree"] = bool((t_h.view(np.uint32) == sah_hits[0].view(np.uint32)).all() and (tri_h == sah_hits[1]).all())
+            else:
+                sub = 128
+                pt.trace_rays_device(rays.data_ptr(), sub, 0, t_out.data_ptr(), tri_out.data_ptr())
+                rec["hits_equal_to_brute_force"] = bool((t_out[:sub].cpu().numpy().view(np.uint32) == t_h[:sub].view(np.uint32)).all()
+                                                        and (tri_out[:sub].cpu().numpy() == tri_h[:sub]).all())
+                rec["brute_force_rays"] = sub
         res.append(rec)
         print(rec, flush=True)
     pt.close()
