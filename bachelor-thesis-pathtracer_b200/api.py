@@ -22,7 +22,7 @@ SYMBOLS = (
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
     "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
-    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth",
+    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest",
 )
 
 
@@ -71,6 +71,11 @@ def load_library():
     L.ptb_bvh_depth.argtypes = [vp]
     L.ptb_build_subgrid.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_build_subbeams.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32]
+    L.ptb_build_subgrid_gpu.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
+    L.ptb_last_build_device_ms.argtypes = [vp]
+    L.ptb_last_build_device_ms.restype = ctypes.c_double
+    L.ptb_structure_digest.argtypes = [vp, ci]
+    L.ptb_structure_digest.restype = cu64
     L.ptb_set_build_limits.argtypes = [vp, ci]
     L.ptb_structure_bytes.argtypes = [vp, ci]
     L.ptb_structure_bytes.restype = cu64
@@ -170,8 +175,19 @@ class PathTracer:
     def bvh_depth(self):
         return int(self.L.ptb_bvh_depth(self.h))
 
-    def build_subgrid(self, gs=10, os_=5, m=40):
-        self._ck(self.L.ptb_build_subgrid(self.h, gs, os_, m), "ptb_build_subgrid")
+    def build_subgrid(self, gs=10, os_=5, m=40, gpu=False):
+        """constructGrid: channels filled by the host threads, or (gpu=True) one GPU thread per channel.  Returns
+        (wall ms, device ms) of the build."""
+        import time
+        t0 = time.perf_counter()
+        if gpu:
+            self._ck(self.L.ptb_build_subgrid_gpu(self.h, gs, os_, m), "ptb_build_subgrid_gpu")
+        else:
+            self._ck(self.L.ptb_build_subgrid(self.h, gs, os_, m), "ptb_build_subgrid")
+        return (time.perf_counter() - t0) * 1e3, (float(self.L.ptb_last_build_device_ms(self.h)) if gpu else 0.0)
+
+    def structure_digest(self, mode):
+        return int(self.L.ptb_structure_digest(self.h, mode))
 
     def build_subbeams(self, gs=10, m=40, max_depth=None):
         if max_depth is not None:

@@ -15,6 +15,7 @@
 #include "ptb.h"
 #include "ptb_bvh_build.h"
 #include "ptb_grid_build.h"
+#include "ptb_grid_gpu.h"
 #include "ptb_lbvh.h"
 #include "ptb_kernels.cuh"
 #include "ptb_mega.cuh"
@@ -96,8 +97,10 @@ struct ptb_ctx {
     bool bvhOnGpu = false;   // built by ptb_build_bvh_gpu: no host copy of the nodes (c->bvh holds order + bounds only)
     uint64_t bvhNodes = 0;   // inner nodes of the tree in HBM
     double lastBuildMs = 0.0; // ptb_last_build_ms
+    double lastBuildDeviceMs = 0.0; // device part of the last *_gpu build (CUDA events)
     std::vector<uint32_t> triOfId; // reference id -> leaf position
     uint64_t gridBytes = 0, beamBytes = 0;
+    uint64_t gridCounts[3] = {0, 0, 0}; // grids, LUT cells, index entries (ptb_structure_digest)
 
     // device scene
     SceneDev S{};
@@ -595,7 +598,7 @@ extern "C" int ptb_build_bvh_gpu(ptb_ctx *c) {
     c->A.vtx = c->dVtx;
     c->bvhBuilt = c->bvhOnGpu = true;
     c->bvhNodes = R.n_nodes;
-    c->lastBuildMs = R.ms;
+    c->lastBuildMs = c->lastBuildDeviceMs = R.ms;
     return PTB_OK;
 }
 
@@ -1295,9 +1298,80 @@ extern "C" int ptb_build_subgrid(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t 
     c->S.grid_lut = c->dGridLut;
     c->S.grid_idx = c->dGridIdx;
     c->gridBytes = R.hdr.size() * sizeof(GridHdr) + R.lut.size() * sizeof(GridCell) + R.idx.size() * sizeof(uint32_t);
+    c->gridCounts[0] = R.hdr.size(); c->gridCounts[1] = R.lut.size(); c->gridCounts[2] = R.idx.size();
     c->gridBuilt = true;
     return PTB_OK;
 }
+
+// constructGrid with the channel population on the device (ptb_grid_gpu.cu): the hierarchy is walked on the host
+// (microseconds per grid), every (grid, channel) pair is one GPU thread.  Produces the same pools as
+// ptb_build_subgrid, byte for byte (tests/test_gpu_builders.py compares the digests).
+extern "C" int ptb_build_subgrid_gpu(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
+    GUARD(c);
+    SETTLE(c);
+    if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (the Subgrid hierarchy derives from the BVH)");
+    if (gs < 1 || gs > 64 || os < 1 || os > 64) return fail(c, PTB_ERR_INVALID, "grid sizes must be 1..64");
+    if (int r = mirror_gpu_bvh(c)) return r;
+    const auto t0 = std::chrono::steady_clock::now();
+    SubgridTopo T;
+    subgrid_topology(c->mat.size(), c->bvh, gs, os, m, T);
+    devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
+    c->gridBuilt = false;
+    SubgridDev D;
+    std::string msg;
+    const cudaError_t e = subgrid_build_gpu(T, c->dVtx, c->dIdOfTri, c->stream, D, msg);
+    if (e != cudaSuccess) {
+        if (e != cudaErrorInvalidValue) c->poisoned = true;
+        return fail(c, e == cudaErrorInvalidValue ? PTB_ERR_INVALID : PTB_ERR_CUDA, msg);
+    }
+    c->dGridHdr = D.hdr;
+    c->dGridLut = D.lut;
+    c->dGridIdx = D.idx;
+    c->S.grid_hdr = c->dGridHdr;
+    c->S.grid_lut = c->dGridLut;
+    c->S.grid_idx = c->dGridIdx;
+    c->gridBytes = D.n_grids * sizeof(GridHdr) + D.n_cells * sizeof(GridCell) + D.n_idx * sizeof(uint32_t);
+    c->gridCounts[0] = D.n_grids; c->gridCounts[1] = D.n_cells; c->gridCounts[2] = D.n_idx;
+    c->gridBuilt = true;
+    c->lastBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->lastBuildDeviceMs = D.ms;
+    return PTB_OK;
+}
+
+// FNV-1a over the bytes of a structure's device pools, in a fixed order — lets a caller (the tests) check that two
+// builders produced the same structure without exposing the layouts.  0 if the structure is not built.
+extern "C" uint64_t ptb_structure_digest(ptb_ctx *c, int mode) {
+    if (!c || c->poisoned || cudaSetDevice(c->device) != cudaSuccess) return 0;
+    if (c->pendingRender && finish_mega(c)) return 0;
+    uint64_t h = 1469598103934665603ull;
+    std::vector<unsigned char> buf;
+    auto eat = [&](const void *dev, size_t bytes) {
+        const size_t chunk = 256u << 20;
+        for (size_t off = 0; off < bytes; off += chunk) {
+            const size_t nb = std::min(chunk, bytes - off);
+            buf.resize(nb);
+            if (cudaMemcpy(buf.data(), (const char *)dev + off, nb, cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+            for (size_t i = 0; i < nb; ++i) {
+                h ^= buf[i];
+                h *= 1099511628211ull;
+            }
+        }
+        return true;
+    };
+    const size_t n = c->mat.size();
+    if (mode == PTB_MODE_BVH && c->bvhBuilt) {
+        if (!eat(c->dNodes, c->bvhNodes * sizeof(BvhNode64)) || !eat(c->dTri, 3 * n * sizeof(float4)) || !eat(c->dNrm, 3 * n * sizeof(float4))) return 0;
+        return h;
+    }
+    if (mode == PTB_MODE_TWO_PLANE && c->gridBuilt) {
+        if (!eat(c->dGridHdr, c->gridCounts[0] * sizeof(GridHdr)) || !eat(c->dGridLut, c->gridCounts[1] * sizeof(GridCell)) ||
+            !eat(c->dGridIdx, c->gridCounts[2] * sizeof(uint32_t)))
+            return 0;
+        return h;
+    }
+    return 0;
+}
+extern "C" double ptb_last_build_device_ms(const ptb_ctx *c) { return c ? c->lastBuildDeviceMs : 0.0; }
 
 extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
     GUARD(c);

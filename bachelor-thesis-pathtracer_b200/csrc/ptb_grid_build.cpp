@@ -11,6 +11,8 @@
 // What is new: one BVH over all triangles instead of scene+object trees, channel-side projections
 // computed once per cell instead of once per candidate, grids of a level built in parallel.
 #include "ptb_grid_build.h"
+#include "ptb_grid_gpu.h"
+#include "ptb_sat.h"
 
 #include <algorithm>
 #include <atomic>
@@ -21,161 +23,6 @@
 
 namespace ptb {
 namespace {
-
-struct V3 {
-    float x, y, z;
-    float &operator[](int i) { return (&x)[i]; }
-    float operator[](int i) const { return (&x)[i]; }
-};
-inline V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
-inline float dot(V3 a, V3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
-inline V3 cross(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
-inline V3 normalized(V3 v) {
-    float z = v.x * v.x + (v.y * v.y + v.z * v.z);
-    if (z > 0.0f) {
-        float l = sqrtf(z);
-        return {v.x / l, v.y / l, v.z / l};
-    }
-    return v;
-}
-inline void axes_of(int axis, int &right, int &up) { // getGridAxes, lightFieldGrid.cpp:26-35
-    right = axis == 0 ? 1 : 0;
-    up = axis == 2 ? 1 : 2;
-}
-
-// adjustGridSize (lightFieldGrid.cpp:165-187 / lightFieldGridSubBeams.cpp:47-68)
-void enlarge(V3 &gmin, V3 &gmax, int axis) {
-    int right, up;
-    axes_of(axis, right, up);
-    const float offset = 0.1f;
-    gmin[axis] -= offset;
-    gmax[axis] += offset;
-    const float deltaF = gmax[axis] - gmin[axis];
-    gmin[up] -= offset + deltaF;
-    gmin[right] -= offset + deltaF;
-    gmax[up] += offset + deltaF;
-    gmax[right] += offset + deltaF;
-}
-
-// A channel / beam: 8 corners, 3 edge directions, 3 face normals (lightFieldGrid.cpp:509-569) plus
-// its own projection intervals on the axes that do not depend on the candidate.
-struct Channel {
-    V3 p[8], e[3], n[3];
-    float cmin[3], cmax[3];   // coordinate axes
-    float emin[3], emax[3];   // own edges
-    float nmin[3], nmax[3];   // own normals
-};
-
-inline void interval(const V3 *pts, int n, V3 ax, float &mn, float &mx) {
-    mn = INFINITY;
-    mx = -INFINITY;
-    for (int j = 0; j < n; ++j) {
-        float pr = dot(pts[j], ax);
-        if (pr < mn) mn = pr;
-        if (pr > mx) mx = pr;
-    }
-}
-
-void make_channel(V3 gmin, V3 gmax, int axis, float u0, float v0, float u1, float v1, float s0, float t0, float s1, float t1, Channel &c) {
-    int right, up;
-    axes_of(axis, right, up);
-    const float dR = gmax[right] - gmin[right], dU = gmax[up] - gmin[up];
-    auto set = [&](int i, float a, float r, float u) {
-        c.p[i][axis] = a;
-        c.p[i][right] = gmin[right] + dR * r;
-        c.p[i][up] = gmin[up] + dU * u;
-    };
-    set(0, gmin[axis], u0, v0);
-    set(1, gmin[axis], u1, v1);
-    set(2, gmax[axis], s0, t1);
-    set(3, gmax[axis], s1, t0);
-    set(4, gmin[axis], u1, v0);
-    set(5, gmin[axis], u0, v1);
-    set(6, gmax[axis], s1, t1);
-    set(7, gmax[axis], s0, t0);
-    c.e[0] = normalized(sub(c.p[6], c.p[1]));
-    c.e[1] = normalized(sub(c.p[2], c.p[6]));
-    c.e[2] = normalized(sub(c.p[6], c.p[3]));
-    c.n[0] = normalized(cross(c.e[0], c.e[1]));
-    c.n[1] = normalized(cross(c.e[0], c.e[2]));
-    c.n[2] = normalized(cross(c.e[2], c.e[1]));
-    for (int k = 0; k < 3; ++k) {
-        c.cmin[k] = INFINITY;
-        c.cmax[k] = -INFINITY;
-        for (int i = 0; i < 8; ++i) {
-            if (c.p[i][k] < c.cmin[k]) c.cmin[k] = c.p[i][k];
-            if (c.p[i][k] > c.cmax[k]) c.cmax[k] = c.p[i][k];
-        }
-        interval(c.p, 8, c.e[k], c.emin[k], c.emax[k]);
-        interval(c.p, 8, c.n[k], c.nmin[k], c.nmax[k]);
-    }
-}
-
-inline bool separated(float amin, float amax, float bmin, float bmax) { return amax < bmin || amin > bmax; }
-
-// triangle vs channel: the 3 + 19 axes of triInChannel (sat.cpp:177-257)
-bool tri_in_channel(const float *t9, const Channel &c) {
-    const V3 tv[3] = {{t9[0], t9[1], t9[2]}, {t9[3], t9[4], t9[5]}, {t9[6], t9[7], t9[8]}};
-    for (int k = 0; k < 3; ++k) {
-        float mn = std::min(tv[0][k], std::min(tv[1][k], tv[2][k])), mx = std::max(tv[0][k], std::max(tv[1][k], tv[2][k]));
-        if (separated(mn, mx, c.cmin[k], c.cmax[k])) return false;
-    }
-    const V3 te[3] = {sub(tv[1], tv[0]), sub(tv[2], tv[1]), sub(tv[0], tv[2])};
-    float a0, a1, b0, b1;
-    for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) {
-            V3 ax = cross(te[i], c.e[j]);
-            interval(tv, 3, ax, a0, a1);
-            interval(c.p, 8, ax, b0, b1);
-            if (separated(a0, a1, b0, b1)) return false;
-        }
-    for (int i = 0; i < 3; ++i) {
-        interval(tv, 3, te[i], a0, a1);
-        interval(c.p, 8, te[i], b0, b1);
-        if (separated(a0, a1, b0, b1)) return false;
-    }
-    {
-        V3 ax = normalized(cross(te[0], te[1]));
-        interval(tv, 3, ax, a0, a1);
-        interval(c.p, 8, ax, b0, b1);
-        if (separated(a0, a1, b0, b1)) return false;
-    }
-    for (int i = 0; i < 3; ++i) {
-        interval(tv, 3, c.e[i], a0, a1);
-        if (separated(a0, a1, c.emin[i], c.emax[i])) return false;
-    }
-    for (int i = 0; i < 3; ++i) {
-        interval(tv, 3, c.n[i], a0, a1);
-        if (separated(a0, a1, c.nmin[i], c.nmax[i])) return false;
-    }
-    return true;
-}
-
-// channel vs axis-aligned box: the 3 + 15 axes of cuboidInAABB (sat.cpp:8-84)
-bool box_in_channel(V3 mn, V3 mx, const Channel &c) {
-    for (int k = 0; k < 3; ++k)
-        if (separated(c.cmin[k], c.cmax[k], mn[k], mx[k])) return false;
-    const V3 bv[8] = {{mn.x, mn.y, mn.z}, {mn.x, mn.y, mx.z}, {mn.x, mx.y, mn.z}, {mn.x, mx.y, mx.z},
-                      {mx.x, mn.y, mn.z}, {mx.x, mn.y, mx.z}, {mx.x, mx.y, mn.z}, {mx.x, mx.y, mx.z}};
-    const V3 ea[3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
-    float a0, a1, b0, b1;
-    for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) {
-            V3 ax = cross(ea[i], c.e[j]);
-            interval(c.p, 8, ax, a0, a1);
-            interval(bv, 8, ax, b0, b1);
-            if (separated(a0, a1, b0, b1)) return false;
-        }
-    for (int i = 0; i < 3; ++i) {
-        interval(bv, 8, c.e[i], b0, b1);
-        if (separated(c.emin[i], c.emax[i], b0, b1)) return false;
-    }
-    for (int i = 0; i < 3; ++i) {
-        interval(bv, 8, c.n[i], b0, b1);
-        if (separated(c.nmin[i], c.nmax[i], b0, b1)) return false;
-    }
-    return true;
-}
 
 template <typename F>
 void parallel_for(size_t n, F f) {
@@ -355,6 +202,95 @@ void build_subgrid(const float *tri_leaf, uint64_t n, const BvhResult &bvh, uint
         std::vector<GridCell>().swap(g.lut);
         std::vector<uint32_t>().swap(g.idx);
     }
+}
+
+// The same hierarchy walk as step 1 of build_subgrid, written into flat arrays for the device builder
+// (ptb_grid_gpu.cu): same grid numbering, same candidate order after the reference's sort by aabb.min[axis].
+void subgrid_topology(uint64_t n, const BvhResult &bvh, uint32_t gs, uint32_t os, uint32_t m, SubgridTopo &out) {
+    out = SubgridTopo();
+    struct Pend {
+        int axis;
+        int32_t ref;
+        V3 lo, hi;
+        uint32_t first, count;
+    };
+    std::vector<Pend> G;
+    V3 slo{bvh.lo[0], bvh.lo[1], bvh.lo[2]}, shi{bvh.hi[0], bvh.hi[1], bvh.hi[2]};
+    if (n == 0) {
+        slo = {0, 0, 0};
+        shi = {0, 0, 0};
+    }
+    for (int a = 0; a < 3; ++a) G.push_back(Pend{a, bvh.root, slo, shi, 0u, (uint32_t)n});
+    out.cell_base.push_back(0);
+    for (size_t gi = 0; gi < G.size(); ++gi) { // breadth-first: children are appended in the order build_subgrid creates them
+        const Pend g = G[gi];
+        GridTopo t{};
+        V3 gmin = g.lo, gmax = g.hi;
+        enlarge(gmin, gmax, g.axis);
+        for (int k = 0; k < 3; ++k) {
+            t.lo[k] = g.lo[k];
+            t.hi[k] = g.hi[k];
+            t.gmin[k] = gmin[k];
+            t.gmax[k] = gmax[k];
+        }
+        const bool inner = g.ref >= 0 && g.count > m && n > 0;
+        uint32_t size;
+        if (inner) {
+            std::vector<Pend> cur{g}, nxt;
+            for (int lvl = 0; lvl < 4; ++lvl) {
+                nxt.clear();
+                for (auto &s : cur) {
+                    if (s.ref < 0) {
+                        nxt.push_back(s);
+                        continue;
+                    }
+                    const BvhNode64 &nd = bvh.nodes[s.ref];
+                    for (int w = 0; w < 2; ++w) {
+                        const float *l = w ? nd.lo1 : nd.lo0, *h = w ? nd.hi1 : nd.hi0;
+                        const BvhRange &r = bvh.ranges[2 * (size_t)s.ref + w];
+                        nxt.push_back(Pend{g.axis, w ? nd.c1 : nd.c0, V3{l[0], l[1], l[2]}, V3{h[0], h[1], h[2]}, r.first, r.count});
+                    }
+                }
+                cur.swap(nxt);
+            }
+            size = gs;
+            t.cand_base = (uint32_t)out.cand.size();
+            t.cand_count = (uint32_t)cur.size();
+            struct Ord {
+                uint32_t id;
+                float d;
+            };
+            std::vector<Ord> ord;
+            for (auto &s : cur) {
+                ord.push_back({(uint32_t)G.size(), s.lo[g.axis]});
+                G.push_back(s);
+            }
+            std::stable_sort(ord.begin(), ord.end(), [](const Ord &a, const Ord &b) { return a.d < b.d; });
+            for (auto &o : ord) out.cand.push_back(o.id);
+        } else {
+            size = os;
+            t.cand_base = g.first;
+            t.cand_count = g.count;
+        }
+        t.axis_size_flags = (uint32_t)g.axis | (size << 8) | (inner ? 0u : 0x80000000u);
+        out.max_cand = std::max(out.max_cand, t.cand_count);
+        out.grids.push_back(t);
+        out.cell_base.push_back(out.cell_base.back() + (uint64_t)size * size * size * size);
+    }
+}
+
+GridHdr subgrid_header(const GridTopo &g, uint64_t lut_base) {
+    GridHdr h;
+    for (int k = 0; k < 3; ++k) {
+        h.amin[k] = g.lo[k];
+        h.amax[k] = g.hi[k];
+        h.gmin[k] = g.gmin[k];
+        h.inv_delta[k] = 1.0f / (g.gmax[k] - g.gmin[k]); // lightFieldGrid.cpp:302-304
+    }
+    h.size_flags = ((g.axis_size_flags >> 8) & 0xffffu) | (g.axis_size_flags & 0x80000000u);
+    h.lut_base = (uint32_t)lut_base;
+    h.pad0 = h.pad1 = 0;
+    return h;
 }
 
 // =============================================================================================

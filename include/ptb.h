@@ -105,6 +105,14 @@ int ptb_build_bvh_gpu(ptb_ctx *ctx);
 double ptb_last_build_ms(const ptb_ctx *ctx); /* last ptb_build_bvh (host wall clock) / ptb_build_bvh_gpu (device time, CUDA events) */
 int ptb_bvh_depth(const ptb_ctx *ctx);        /* inner nodes on the longest root-to-leaf chain (< PTB_STACK, the per-lane traversal stack); -1 before a build */
 int ptb_build_subgrid(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m); /* setGridSettings + constructGrid, lightFieldGrid.h:24,26 */
+/* constructGrid with the size^4 channel loop on the device (lightFieldGrid.cpp:381-414,493-583 with
+ * the separating-axis tests of src/types/sat.cpp): one GPU thread per (grid, channel), count -> scan -> fill.  Same pools
+ * as ptb_build_subgrid byte for byte (both evaluate csrc/ptb_sat.h). */
+int ptb_build_subgrid_gpu(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m);
+double ptb_last_build_device_ms(const ptb_ctx *ctx); /* device part (CUDA events) of the last ptb_build_*_gpu call */
+/* FNV-1a over a structure's device pools (mode BVH: nodes + triangle arrays; TWO_PLANE: headers + LUT + indices); 0 if
+ * it is not built.  For checking that two builders agree without exposing the layouts. */
+uint64_t ptb_structure_digest(ptb_ctx *ctx, int mode);
 int ptb_build_subbeams(ptb_ctx *ctx, uint32_t gs, uint32_t m);          /* setGridBeamsSettings + buildGridsWithSubBeams, lightFieldGridSubBeams.h:28-29 */
 /* The reference's Subbeam recursion has no depth limit (lightFieldGridSubBeams.cpp:286-324) and does not
  * terminate on dense clusters; beams at `beam_max_depth` become leaves (default 12, 0 = unbounded). */
