@@ -22,7 +22,7 @@ SYMBOLS = (
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
     "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
-    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest",
+    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh",
 )
 
 
@@ -35,6 +35,11 @@ class Params(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "width", "height", "mode", "nee", "primary_only", "max_depth", "reference_quirks", "debug_view", "debug_scale",
         "rank", "world", "tile_w", "tile_h", "count_tests", "seed_offset")]
+
+
+# ptb_ref_bvh_node (include/ptb.h): BvhNode (bvh.h:14-24) with its box inlined, 48 bytes
+REF_BVH_NODE = np.dtype([("bmin", np.float32, 3), ("start_idx", np.int32), ("bmax", np.float32, 3), ("end_idx", np.int32),
+                         ("child_left", np.int32), ("child_right", np.int32), ("has_tris", np.int32), ("pad", np.int32)])
 
 
 class PtbError(RuntimeError):
@@ -71,6 +76,8 @@ def load_library():
     L.ptb_bvh_depth.argtypes = [vp]
     L.ptb_build_subgrid.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_build_subbeams.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32]
+    L.ptb_upload_ref_bvh.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, ctypes.c_uint32, ctypes.c_int32]
+    L.ptb_use_ref_bvh.argtypes = [vp, ci]
     L.ptb_build_subgrid_gpu.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_last_build_device_ms.argtypes = [vp]
     L.ptb_last_build_device_ms.restype = ctypes.c_double
@@ -185,6 +192,18 @@ class PathTracer:
         else:
             self._ck(self.L.ptb_build_subgrid(self.h, gs, os_, m), "ptb_build_subgrid")
         return (time.perf_counter() - t0) * 1e3, (float(self.L.ptb_last_build_device_ms(self.h)) if gpu else 0.0)
+
+    def upload_ref_bvh(self, nodes, indices, object_roots, scene_root):
+        """nodes: structured array of REF_BVH_NODE (the reference's BvhNode + its box); see ptb_upload_ref_bvh."""
+        nodes = np.ascontiguousarray(nodes, REF_BVH_NODE)
+        indices = np.ascontiguousarray(indices, np.uint32)
+        object_roots = np.ascontiguousarray(object_roots, np.int32)
+        self._ck(self.L.ptb_upload_ref_bvh(self.h, _ptr(nodes), nodes.shape[0], _ptr(indices), indices.shape[0], _ptr(object_roots),
+                                           object_roots.shape[0], int(scene_root)), "ptb_upload_ref_bvh")
+
+    def use_ref_bvh(self, on=True):
+        """Mode BVH walks the uploaded reference tree: counters and heat maps become the reference's own numbers."""
+        self._ck(self.L.ptb_use_ref_bvh(self.h, int(on)), "ptb_use_ref_bvh")
 
     def structure_digest(self, mode):
         return int(self.L.ptb_structure_digest(self.h, mode))

@@ -94,6 +94,10 @@ struct ptb_ctx {
     // structures
     BvhResult bvh;
     bool bvhBuilt = false, gridBuilt = false, beamBuilt = false;
+    bool refBvhLoaded = false, useRefBvh = false; // ptb_upload_ref_bvh / ptb_use_ref_bvh
+    float4 *dRefNode = nullptr;
+    uint32_t *dRefIdx = nullptr;
+    int *dRefObjRoot = nullptr;
     bool bvhOnGpu = false;   // built by ptb_build_bvh_gpu: no host copy of the nodes (c->bvh holds order + bounds only)
     uint64_t bvhNodes = 0;   // inner nodes of the tree in HBM
     double lastBuildMs = 0.0; // ptb_last_build_ms
@@ -338,6 +342,7 @@ extern "C" void ptb_destroy(ptb_ctx *c) {
     devFree(c->dMats); devFree(c->dLights);
     devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
     devFree(c->dBeam); devFree(c->dBeamIdx);
+    devFree(c->dRefNode); devFree(c->dRefIdx); devFree(c->dRefObjRoot);
     for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
     devFree(c->dRings); devFree(c->dCounters); devFree(c->dShScratch);
     devFree(c->dScratchF); devFree(c->dScratchI); devFree(c->dRays);
@@ -367,6 +372,7 @@ extern "C" int ptb_upload_triangles(ptb_ctx *c, const float *pos9, const float *
     c->nrm9.assign(nrm9, nrm9 + 9 * n);
     c->mat.assign(mat, mat + n);
     c->bvhBuilt = c->gridBuilt = c->beamBuilt = false;
+    c->refBvhLoaded = c->useRefBvh = false; // its indices refer to the previous triangle list
     return PTB_OK;
 }
 
@@ -537,6 +543,7 @@ extern "C" int ptb_build_bvh(ptb_ctx *c) {
     c->S.n_tris = (uint32_t)n;
     c->A.nrm = c->dNrm;
     c->A.tri_of_id = c->dTriOfId;
+    c->S.ref_tri_pos = c->dTriOfId;
     c->A.id_of_tri = c->dIdOfTri;
     c->A.vtx = c->dVtx;
     c->bvhBuilt = true;
@@ -594,6 +601,7 @@ extern "C" int ptb_build_bvh_gpu(ptb_ctx *c) {
     c->S.n_tris = (uint32_t)n;
     c->A.nrm = c->dNrm;
     c->A.tri_of_id = c->dTriOfId;
+    c->S.ref_tri_pos = c->dTriOfId;
     c->A.id_of_tri = c->dIdOfTri;
     c->A.vtx = c->dVtx;
     c->bvhBuilt = c->bvhOnGpu = true;
@@ -604,6 +612,103 @@ extern "C" int ptb_build_bvh_gpu(ptb_ctx *c) {
 
 extern "C" double ptb_last_build_ms(const ptb_ctx *c) { return c ? c->lastBuildMs : 0.0; }
 extern "C" int ptb_bvh_depth(const ptb_ctx *c) { return (c && c->bvhBuilt) ? c->bvh.max_depth : -1; }
+
+// The reference's own BVH — what constructBVH (bvh.cpp:222-390) left behind getNode / getNodeAABB / bvhGetTrisIndex
+// (bvh.h:27-29) and Object::root — for count-exact traversal (refbvh_closest).  Validated here, because the kernel
+// trusts it: every link in range, no cycles, and the worst-case stack of the reference's push order below PTB_STACK.
+extern "C" int ptb_upload_ref_bvh(ptb_ctx *c, const ptb_ref_bvh_node *nodes, uint32_t n_nodes, const uint32_t *indices, uint32_t n_indices,
+                                  const int32_t *object_roots, uint32_t n_objects, int32_t scene_root) {
+    GUARD(c);
+    SETTLE(c);
+    c->refBvhLoaded = c->useRefBvh = false;
+    const uint64_t nTris = c->mat.size();
+    if (!nodes || n_nodes == 0 || (n_indices && !indices) || (n_objects && !object_roots)) return fail(c, PTB_ERR_INVALID, "null reference-BVH arrays");
+    if (scene_root < 0 || (uint32_t)scene_root >= n_nodes) return fail(c, PTB_ERR_INVALID, "scene_root out of range");
+    for (uint32_t o = 0; o < n_objects; ++o)
+        if (object_roots[o] < 0 || (uint32_t)object_roots[o] >= n_nodes) return fail(c, PTB_ERR_INVALID, "object root out of range");
+    for (uint32_t i = 0; i < n_nodes; ++i) {
+        const ptb_ref_bvh_node &nd = nodes[i];
+        const bool leaf = nd.child_left == -1 && nd.child_right == -1;
+        if (!leaf && (nd.child_left < 0 || nd.child_right < 0 || (uint32_t)nd.child_left >= n_nodes || (uint32_t)nd.child_right >= n_nodes))
+            return fail(c, PTB_ERR_INVALID, "reference BVH: child index out of range");
+        if (leaf) {
+            if (nd.start_idx < 0 || nd.end_idx < nd.start_idx || (uint32_t)nd.end_idx > n_indices) return fail(c, PTB_ERR_INVALID, "reference BVH: leaf range outside the index array");
+            for (int32_t k = nd.start_idx; k < nd.end_idx; ++k)
+                if (indices[k] >= (nd.has_tris ? nTris : (uint64_t)n_objects)) return fail(c, PTB_ERR_INVALID, "reference BVH: leaf entry out of range");
+        }
+    }
+    // worst-case stack entries while a subtree is being walked; -1 = being visited (cycle)
+    std::vector<int> need(n_nodes, -2);
+    struct Fr { int32_t node; int phase; };
+    std::vector<Fr> st;
+    auto children = [&](const ptb_ref_bvh_node &nd, std::vector<int32_t> &out) {
+        out.clear();
+        if (!(nd.child_left == -1 && nd.child_right == -1)) {
+            out.push_back(nd.child_left);
+            out.push_back(nd.child_right);
+        } else if (!nd.has_tris)
+            for (int32_t k = nd.start_idx; k < nd.end_idx; ++k) out.push_back(object_roots[indices[k]]);
+    };
+    std::vector<int32_t> ch;
+    st.push_back({scene_root, 0});
+    while (!st.empty()) {
+        Fr &f = st.back();
+        const int32_t node = f.node;
+        if (f.phase == 0) {
+            if (need[node] == -1) return fail(c, PTB_ERR_INVALID, "reference BVH: cycle");
+            if (need[node] >= 0) {
+                st.pop_back();
+                continue;
+            }
+            need[node] = -1;
+            f.phase = 1;
+            children(nodes[node], ch);
+            for (int32_t x : ch) {
+                if (need[x] == -1) return fail(c, PTB_ERR_INVALID, "reference BVH: cycle");
+                if (need[x] == -2) st.push_back({x, 0});
+            }
+            continue;
+        }
+        children(nodes[node], ch);
+        int worst = 0;
+        for (int32_t x : ch) worst = std::max(worst, need[x]);
+        need[node] = ch.empty() ? 0 : (int)ch.size() - 1 + worst; // the siblings wait on the stack while one child is walked
+        st.pop_back();
+    }
+    if (need[scene_root] + 1 >= PTB_STACK) return fail(c, PTB_ERR_INVALID, "reference BVH deeper than the traversal stack (PTB_STACK)");
+    std::vector<float4> dev(3 * (size_t)n_nodes);
+    for (uint32_t i = 0; i < n_nodes; ++i) {
+        const ptb_ref_bvh_node &nd = nodes[i];
+        float s, e, l, r, h;
+        memcpy(&s, &nd.start_idx, 4); memcpy(&e, &nd.end_idx, 4); memcpy(&l, &nd.child_left, 4); memcpy(&r, &nd.child_right, 4);
+        const int32_t ht = nd.has_tris ? 1 : 0;
+        memcpy(&h, &ht, 4);
+        dev[3 * (size_t)i] = make_float4(nd.bmin[0], nd.bmin[1], nd.bmin[2], s);
+        dev[3 * (size_t)i + 1] = make_float4(nd.bmax[0], nd.bmax[1], nd.bmax[2], e);
+        dev[3 * (size_t)i + 2] = make_float4(l, r, h, 0.0f);
+    }
+    devFree(c->dRefNode); devFree(c->dRefIdx); devFree(c->dRefObjRoot);
+    CK(cudaMalloc(&c->dRefNode, dev.size() * sizeof(float4)));
+    CK(cudaMalloc(&c->dRefIdx, std::max<size_t>(1, n_indices) * sizeof(uint32_t)));
+    CK(cudaMalloc(&c->dRefObjRoot, std::max<size_t>(1, n_objects) * sizeof(int)));
+    CK(cudaMemcpy(c->dRefNode, dev.data(), dev.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    if (n_indices) CK(cudaMemcpy(c->dRefIdx, indices, n_indices * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    if (n_objects) CK(cudaMemcpy(c->dRefObjRoot, object_roots, n_objects * sizeof(int), cudaMemcpyHostToDevice));
+    c->S.ref_node = c->dRefNode;
+    c->S.ref_idx = c->dRefIdx;
+    c->S.ref_obj_root = c->dRefObjRoot;
+    c->S.ref_root = scene_root;
+    c->refBvhLoaded = true;
+    return PTB_OK;
+}
+
+extern "C" int ptb_use_ref_bvh(ptb_ctx *c, int on) {
+    GUARD(c);
+    SETTLE(c);
+    if (on && !c->refBvhLoaded) return fail(c, PTB_ERR_NOT_BUILT, "ptb_upload_ref_bvh first");
+    c->useRefBvh = on != 0;
+    return PTB_OK;
+}
 
 extern "C" int ptb_set_build_limits(ptb_ctx *c, int beam_max_depth) {
     GUARD(c);
@@ -889,7 +994,7 @@ int render_mega(ptb_ctx *c, int add) {
     c->targetSamples += add;
     const ParamsDev P = make_params(c);
     // no more paths in flight than owned pixels: a pixel's samples are serial, so pixels bound the parallelism
-    const bool pool = c->useMega == 2, duo = c->useMega == 3;
+    const bool pool = MODE != 4 && c->useMega == 2, duo = MODE != 4 && c->useMega == 3; // the reference tree runs in k_mega only
     const uint64_t perCta = pool ? 4ull * PTB_POOL_NP : (duo ? 2ull * kThreads : (uint64_t)kThreads); // paths a CTA keeps in flight
     const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * (pool ? c->poolCtas : (duo ? c->duoCtas : c->megaCtas)),
                                                                    ((uint64_t)c->nSlots + perCta - 1) / perCta));
@@ -918,7 +1023,10 @@ int render_mega(ptb_ctx *c, int add) {
     M.counters = c->dCounters;
     CK(cudaMemsetAsync(c->dCounters + 8, 0, sizeof(unsigned long long), c->stream));
     CK(cudaEventRecord(c->evStart, c->stream));
+    bool launched = false;
+    if constexpr (MODE != 4) {
     if (pool) {
+        launched = true;
         const bool nee = P.nee && P.n_lights > 0;
         const size_t need = nee ? (size_t)grid * 4 * PTB_POOL_NP : 0;
         if (need > c->shScratchN) {
@@ -936,9 +1044,12 @@ int render_mega(ptb_ctx *c, int add) {
         }
         k_pool<MODE, COUNT, PTB_POOL_NP><<<grid, kThreads, smem, c->stream>>>(P, c->S, c->A, c->F, M, nee ? c->dShScratch : nullptr);
     } else if (duo) {
+        launched = true;
         if (P.nee && P.n_lights > 0) k_duo<MODE, COUNT, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
         else k_duo<MODE, COUNT, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
-    } else {
+    }
+    }
+    if (!launched) {
         const bool nee = P.nee && P.n_lights > 0;
         if (MODE == 1 && M.leaf_keep > 0) { // deep tree: straggler exit in the node loop
             if (nee) k_mega<MODE, COUNT, true, MODE == 1><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
@@ -977,6 +1088,10 @@ int finish_mega(ptb_ctx *c) {
 
 template <bool COUNT>
 int render_dispatch(ptb_ctx *c, int add) {
+    if (c->useRefBvh && c->prm.mode == PTB_MODE_BVH) {
+        if (!c->useMega) return fail(c, PTB_ERR_INVALID, "the reference tree is traversed by the path kernel only (unset PTB_MEGA=0)");
+        return render_mega<4, true>(c, add); // always the counting build: the counters are why this tree is here
+    }
     if (c->useMega) switch (c->prm.mode) {
         case PTB_MODE_ALL: return render_mega<0, COUNT>(c, add);
         case PTB_MODE_BVH: return render_mega<1, COUNT>(c, add);
@@ -1083,7 +1198,10 @@ extern "C" int ptb_primary_hits(ptb_ctx *c, float *t, int32_t *tri, int32_t *mat
     CK(cudaEventRecord(c->evStart, c->stream));
     switch (c->prm.mode) {
     case PTB_MODE_ALL: k_primary<0><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
-    case PTB_MODE_BVH: k_primary<1><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
+    case PTB_MODE_BVH:
+        if (c->useRefBvh) k_primary<4><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat);
+        else k_primary<1><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat);
+        break;
     case PTB_MODE_TWO_PLANE: k_primary<2><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
     default: k_primary<3><<<g, kThreads, 0, c->stream>>>(P, c->S, c->A, dT, dTri, dMat); break;
     }
@@ -1118,6 +1236,10 @@ extern "C" int ptb_trace_rays_device(ptb_ctx *c, const float *od6, uint64_t n, i
     switch (mode) {
     case PTB_MODE_ALL: PTB_TRACE(0); break;
     case PTB_MODE_BVH: {
+        if (c->useRefBvh) { // count-exact walk of the reference's tree
+            PTB_TRACE(4);
+            break;
+        }
         unsigned long long *cur = c->dCounters + 7; // slot 7 of the counter block: work cursor of this launch (zeroed above)
         const int gp = (int)std::min<uint64_t>((uint64_t)c->sms * c->extendCtas, (n + 127) / 128);
         const int leafFrac = c->traceLeafFrac; // off by default: coherent camera rays lose 10 % to it (config 3: 1533 -> 1383 Mrays/s)

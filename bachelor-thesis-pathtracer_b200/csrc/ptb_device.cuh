@@ -94,6 +94,13 @@ struct SceneDev {
     float beam_gmin[3][3], beam_gmax[3][3], beam_amin[3], beam_amax[3];
     uint32_t beam_grid_size;
     uint32_t n_beams;
+    // the reference's own two-level BVH (ptb_upload_ref_bvh), traversed node for node like bvh.cpp:48-99 so that
+    // the two test counters and the heat maps are the reference's numbers
+    const float4 *__restrict__ ref_node;     // 3 float4 (48 B) per node: (bmin, start) (bmax, end) (left, right, hasTris, -)
+    const uint32_t *__restrict__ ref_idx;    // bvh.cpp:20 `indicies`: triangle ids (hasTris) or object ids
+    const int *__restrict__ ref_obj_root;    // Object::root per object
+    const uint32_t *__restrict__ ref_tri_pos; // reference triangle id -> leaf position in `tri`
+    int ref_root;
 };
 
 // ---- Moeller-Trumbore: src/primitives/triangle.cpp:7-52, positions only --------------------
@@ -300,6 +307,51 @@ __device__ __forceinline__ void brute_closest(const SceneDev &S, f3 o, f3 d, Hit
     for (uint32_t i = 0; i < S.n_tris; ++i) intersect_tri<COUNT>(S.tri, (int)i, o, d, h, nTri);
 }
 
+// ---- the reference's tree, the reference's order: findBVHIntesection (bvh.cpp:48-99) statement by statement.
+// Every popped node tests its own box (1 AS test), an inner node then measures both children (2 AS tests) and
+// pushes far-then-near; a scene-level leaf pushes the roots of its objects, an object-level leaf tests its
+// triangles.  Slower than bvh_closest on purpose — it exists so that nAS / nTri equal ray.interSectionAS /
+// ray.interSectionTests of the reference (tracer.cpp:127-132) for the same ray.
+template <bool COUNT>
+__device__ __forceinline__ void refbvh_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
+    if (S.n_tris == 0 || S.ref_root < 0) return;
+    const f3 inv = rcp3(d);
+    int stack[PTB_STACK];
+    int sp = 0;
+    stack[sp++] = S.ref_root;
+    while (sp > 0) {
+        const int idx = stack[--sp];
+        const float4 *n = S.ref_node + 3 * (size_t)idx;
+        const float4 a = __ldg(n), b = __ldg(n + 1);
+        const int4 c = __ldg(reinterpret_cast<const int4 *>(n + 2));
+        if (COUNT) nAS++;
+        float tn;
+        if (!slab(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), o, inv, h.t, tn)) continue;
+        if (!(c.x == -1 && c.y == -1)) {
+            if (COUNT) nAS += 2;
+            const float4 *l = S.ref_node + 3 * (size_t)c.x, *r = S.ref_node + 3 * (size_t)c.y;
+            const float4 la = __ldg(l), lb = __ldg(l + 1), ra = __ldg(r), rb = __ldg(r + 1);
+            float dL, dR;
+            if (!slab(mk3(la.x, la.y, la.z), mk3(lb.x, lb.y, lb.z), o, inv, h.t, dL)) dL = PTB_INF;
+            if (!slab(mk3(ra.x, ra.y, ra.z), mk3(rb.x, rb.y, rb.z), o, inv, h.t, dR)) dR = PTB_INF;
+            if (dR >= dL) {
+                if (dR != PTB_INF && sp < PTB_STACK) stack[sp++] = c.y;
+                if (dL != PTB_INF && sp < PTB_STACK) stack[sp++] = c.x;
+            } else {
+                if (dL != PTB_INF && sp < PTB_STACK) stack[sp++] = c.x;
+                if (dR != PTB_INF && sp < PTB_STACK) stack[sp++] = c.y;
+            }
+        } else {
+            const int first = __float_as_int(a.w), last = __float_as_int(b.w);
+            for (int i = first; i < last; ++i) {
+                const uint32_t id = __ldg(S.ref_idx + i);
+                if (c.z) intersect_tri<COUNT>(S.tri, (int)__ldg(S.ref_tri_pos + id), o, d, h, nTri);
+                else if (sp < PTB_STACK) stack[sp++] = __ldg(S.ref_obj_root + id);
+            }
+        }
+    }
+}
+
 // dominant axis: lightFieldGrid.cpp:79-95 (strict >, first wins)
 __device__ __forceinline__ int dominant_axis(f3 d) {
     int axis = 0;
@@ -419,6 +471,7 @@ __device__ __forceinline__ void closest_hit(const SceneDev &S, f3 o, f3 d, Hit &
     if (MODE == 1) bvh_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 2) subgrid_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 3) subbeam_closest<COUNT>(S, o, d, h, nTri, nAS);
+    else if (MODE == 4) refbvh_closest<COUNT>(S, o, d, h, nTri, nAS); // BVH mode over the reference's own tree
     else brute_closest<COUNT>(S, o, d, h, nTri);
 }
 

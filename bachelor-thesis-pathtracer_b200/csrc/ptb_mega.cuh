@@ -193,6 +193,10 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                                 break;
                             }
                             cRef++;
+                            if (COUNT && MODE == 4) { // the reference walks its tree again for the unchanged ray: same tests
+                                cTri += nTri;
+                                cAS += nAS;
+                            }
                         }
                         terminated = true;
                     }

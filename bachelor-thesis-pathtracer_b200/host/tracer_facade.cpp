@@ -30,6 +30,7 @@
 #include <thread>
 #include <vector>
 
+#include "accelerationStructures/bvh.h"
 #include "common.h"
 #include "primitives/object.h"
 #include "primitives/triangle.h"
@@ -56,6 +57,7 @@ size_t uploadedTris = (size_t)-1;
 unsigned gridGs = 10, gridOs = 5, gridM = 40, beamGs = 10, beamM = 40; // main.cpp:42-44 defaults
 bool gridBuilt = false, beamBuilt = false;
 int maxDepth = 0;
+bool useReferenceTree = false; // ptbFacadeUseReferenceTree
 int renderedSamples = 0;
 std::vector<float> mirror; // host copy of the frame that tracerGetPixel serves (refreshed per batch)
 uint64_t counters[PTB_CNT__N] = {0};
@@ -106,6 +108,8 @@ bool uploadObjects() {
     return ok(ptb_upload_objects(ctx, po.data(), (uint32_t)po.size()), "ptb_upload_objects");
 }
 
+bool uploadReferenceTree();
+
 // getTris() (280-byte AoS, triangle.h:7-14) -> the flat arrays of ptb_upload_triangles
 bool uploadScene() {
     auto &tris = getTris();
@@ -129,7 +133,64 @@ bool uploadScene() {
     if (!ok(ptb_build_bvh(ctx), "ptb_build_bvh")) return false; // constructBVH, scene.cpp:113-120
     gridBuilt = beamBuilt = false;
     uploadedTris = n;
+    if (useReferenceTree && n > 0) {
+        if (!uploadReferenceTree() || !ok(ptb_use_ref_bvh(ctx, 1), "ptb_use_ref_bvh")) return false;
+    }
     return true;
+}
+
+// The reference's own BVH, read through the accessors it already exports (getNode / getNodeAABB /
+// bvhGetTrisIndex, bvh.h:27-29; Object::root) after initScene built it (scene.cpp:113-120: the scene tree is
+// the first constructBVH call, so its root is node 0).  With it on the device, mode BVH reproduces
+// getIntersectionCount / getStructureIntersectionCount and the heat maps of the CPU tracer exactly.
+bool uploadReferenceTree() {
+    auto &objs = getObjects();
+    std::vector<int32_t> roots(objs.size());
+    for (size_t i = 0; i < objs.size(); ++i) roots[i] = objs[i].root;
+    std::vector<ptb_ref_bvh_node> nodes;
+    std::vector<uint32_t> idx;
+    std::vector<int32_t> todo{0};
+    std::vector<char> seen;
+    while (!todo.empty()) {
+        const int32_t i = todo.back();
+        todo.pop_back();
+        if (i < 0) continue;
+        if ((size_t)i >= nodes.size()) {
+            ptb_ref_bvh_node empty;
+            memset(&empty, 0, sizeof empty);
+            empty.child_left = empty.child_right = -1; // never reached: an empty leaf
+            empty.has_tris = 1;
+            nodes.resize((size_t)i + 1, empty);
+            seen.resize((size_t)i + 1, 0);
+        }
+        if (seen[i]) continue;
+        seen[i] = 1;
+        const BvhNode &n = getNode((u32)i);
+        const AABB &b = getNodeAABB((u32)n.AABBIdx);
+        ptb_ref_bvh_node &o = nodes[i];
+        for (int k = 0; k < 3; ++k) {
+            o.bmin[k] = b.min[k];
+            o.bmax[k] = b.max[k];
+        }
+        o.start_idx = n.startIdx;
+        o.end_idx = n.endIdx;
+        o.child_left = n.childLeft;
+        o.child_right = n.childRight;
+        o.has_tris = n.hasTris ? 1 : 0;
+        if (n.childLeft == -1 && n.childRight == -1) {
+            if (n.endIdx > (int)idx.size()) idx.resize((size_t)n.endIdx, 0u);
+            for (int k = n.startIdx; k < n.endIdx; ++k) {
+                idx[k] = bvhGetTrisIndex((u32)k);
+                if (!n.hasTris && idx[k] < roots.size()) todo.push_back(roots[idx[k]]);
+            }
+        } else {
+            todo.push_back(n.childLeft);
+            todo.push_back(n.childRight);
+        }
+    }
+    return ok(ptb_upload_ref_bvh(ctx, nodes.data(), (uint32_t)nodes.size(), idx.data(), (uint32_t)idx.size(), roots.data(),
+                                 (uint32_t)roots.size(), 0),
+              "ptb_upload_ref_bvh");
 }
 
 bool ensureStructure(int mode) {
@@ -292,6 +353,10 @@ void ptbFacadeSetGridBeamsSettings(unsigned size, unsigned count) {
     beamBuilt = false;
 }
 void ptbFacadeSetMaxDepth(int depth) { maxDepth = depth; }
+void ptbFacadeUseReferenceTree(bool on) {
+    useReferenceTree = on;
+    uploadedTris = (size_t)-1; // next trace() uploads again, with or without the tree
+}
 void ptbFacadeSetDevice(int device) { deviceIdx = device; }
 unsigned long ptbFacadeStructureBytes(int mode) { return ctx ? (unsigned long)ptb_structure_bytes(ctx, mode) : 0ul; }
 double ptbFacadeLastRenderMs() { return ctx ? ptb_last_render_ms(ctx) : 0.0; }

@@ -6,6 +6,9 @@
 void ptbFacadeSetGridSettings(unsigned size, unsigned oSize, unsigned count); // mirrors setGridSettings, lightFieldGrid.cpp:54-58
 void ptbFacadeSetGridBeamsSettings(unsigned size, unsigned count);            // mirrors setGridBeamsSettings, lightFieldGridSubBeams.cpp:179-183
 void ptbFacadeSetMaxDepth(int depth);  // 0 = unbounded (reference behaviour); BASELINE.json's "N bounces" = depth N+1
+// Mode BVH walks the reference's OWN tree (read through getNode / getNodeAABB / bvhGetTrisIndex) node for node, so that
+// getIntersectionCount / getStructureIntersectionCount and the heat maps are the CPU tracer's numbers (slower; off by default)
+void ptbFacadeUseReferenceTree(bool on);
 void ptbFacadeSetDevice(int device);   // before the first trace(); default 0
 unsigned long ptbFacadeStructureBytes(int mode); // device bytes of the structure (cf. getMemoryBVH / getMemory2Plane)
 double ptbFacadeLastRenderMs();        // device time of the last batch (CUDA events)

@@ -104,6 +104,23 @@ int ptb_build_bvh(ptb_ctx *ctx);                                        /* const
 int ptb_build_bvh_gpu(ptb_ctx *ctx);
 double ptb_last_build_ms(const ptb_ctx *ctx); /* last ptb_build_bvh (host wall clock) / ptb_build_bvh_gpu (device time, CUDA events) */
 int ptb_bvh_depth(const ptb_ctx *ctx);        /* inner nodes on the longest root-to-leaf chain (< PTB_STACK, the per-lane traversal stack); -1 before a build */
+/* The reference's own tree for count-exact traversal.  One record per BvhNode (bvh.h:14-24) with its
+ * box boxes[node.AABBIdx] (bvh.cpp:19) inlined — what getNode / getNodeAABB hand out (bvh.h:27-28); `indices` is
+ * bvhGetTrisIndex (bvh.h:29): triangle ids under has_tris leaves, object ids under scene-level leaves; object_roots
+ * is Object::root (object.h).  With ptb_use_ref_bvh(ctx, 1) mode BVH walks this tree statement by statement like
+ * findBVHIntesection (bvh.cpp:48-99): same hits and frames as ever, and PTB_CNT_TRI_TESTS / PTB_CNT_AS_TESTS and the
+ * debug_view heat maps become the reference's own numbers (tracer.cpp:127-142) — re-traced misses included. */
+typedef struct ptb_ref_bvh_node {
+    float bmin[3];
+    int32_t start_idx;
+    float bmax[3];
+    int32_t end_idx;
+    int32_t child_left, child_right; /* both -1: leaf */
+    int32_t has_tris, pad;
+} ptb_ref_bvh_node;
+int ptb_upload_ref_bvh(ptb_ctx *ctx, const ptb_ref_bvh_node *nodes, uint32_t n_nodes, const uint32_t *indices, uint32_t n_indices,
+                       const int32_t *object_roots, uint32_t n_objects, int32_t scene_root);
+int ptb_use_ref_bvh(ptb_ctx *ctx, int on);
 int ptb_build_subgrid(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m); /* setGridSettings + constructGrid, lightFieldGrid.h:24,26 */
 /* constructGrid with the size^4 channel loop on the device (lightFieldGrid.cpp:381-414,493-583 with
  * the separating-axis tests of src/types/sat.cpp): one GPU thread per (grid, channel), count -> scan -> fill.  Same pools

@@ -127,7 +127,7 @@ struct Opts {
     int mode = 1;
     unsigned gs = 10, os = 5, m = 40;
     bool grid = false, beams = false;
-    int W = 512, H = 512, spp = 1, maxDepth = 0, nee = 0, threads = 0;
+    int W = 512, H = 512, spp = 1, maxDepth = 0, nee = 0, threads = 0, refTree = 0;
     unsigned bgs = 10, bm = 40;
 };
 
@@ -419,6 +419,7 @@ static void cmdRender(const Opts &o, const char *out) {
     ptbFacadeSetMaxDepth(o.maxDepth);
     ptbFacadeSetGridSettings(o.gs, o.os, o.m);
     ptbFacadeSetGridBeamsSettings(o.bgs, o.bm);
+    ptbFacadeUseReferenceTree(o.refTree != 0);
 #endif
     setWindowSize(o.W, o.H);
     getMaxSampleCount() = o.spp;
@@ -529,6 +530,7 @@ int main(int argc, char **argv) {
         else if (a == "--spp") o.spp = atoi(next());
         else if (a == "--max-depth") o.maxDepth = atoi(next());
         else if (a == "--nee") o.nee = atoi(next());
+        else if (a == "--ref-tree") o.refTree = atoi(next());
         else if (a == "--threads") o.threads = atoi(next());
         else if (a == "--no-count") g_countRays = false;
         else pos.push_back(a);

@@ -80,6 +80,28 @@ class Oracle:
         self.L.pto_primary_hits(self.h, t, tri, mat, rays.ctypes.data if want_rays else None)
         return (t, tri, mat, rays) if want_rays else (t, tri, mat)
 
+    def primary_counts(self):
+        """(AS tests, triangle tests) of every pixel's first-sample primary ray — the debug view's input."""
+        n = self.W * self.H
+        a = np.empty(n, np.uint32)
+        t = np.empty(n, np.uint32)
+        self.L.pto_primary_counts.argtypes = [ctypes.c_void_p, _u32p, _u32p]
+        self.L.pto_primary_counts(self.h, a, t)
+        return a, t
+
+    def export_bvh(self):
+        """The oracle's (= the reference's) two-level BVH as ptb_upload_ref_bvh takes it:
+        (nodes[48-byte records], indices, object_roots, scene_root)."""
+        self.L.pto_export_bvh.argtypes = [ctypes.c_void_p] + [ctypes.c_void_p] * 5
+        sizes = np.zeros(3, np.uint64)
+        root = ctypes.c_int32(0)
+        self.L.pto_export_bvh(self.h, None, None, None, sizes.ctypes.data, ctypes.byref(root))
+        nodes = np.zeros(int(sizes[0]) * 48, np.uint8)
+        idx = np.zeros(int(sizes[1]), np.uint32)
+        roots = np.zeros(int(sizes[2]), np.int32)
+        self.L.pto_export_bvh(self.h, nodes.ctypes.data, idx.ctypes.data, roots.ctypes.data, sizes.ctypes.data, ctypes.byref(root))
+        return nodes, idx, roots, int(root.value)
+
     def trace_rays(self, od, threads=0):
         od = np.ascontiguousarray(od, np.float32).reshape(-1, 6)
         n = od.shape[0]
