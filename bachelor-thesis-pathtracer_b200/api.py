@@ -22,7 +22,7 @@ SYMBOLS = (
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
     "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
-    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh",
+    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh", "ptb_upload_textures",
 )
 
 
@@ -40,6 +40,10 @@ class Params(ctypes.Structure):
 # ptb_ref_bvh_node (include/ptb.h): BvhNode (bvh.h:14-24) with its box inlined, 48 bytes
 REF_BVH_NODE = np.dtype([("bmin", np.float32, 3), ("start_idx", np.int32), ("bmax", np.float32, 3), ("end_idx", np.int32),
                          ("child_left", np.int32), ("child_right", np.int32), ("has_tris", np.int32), ("pad", np.int32)])
+
+
+class Texture(ctypes.Structure):  # ptb_texture
+    _fields_ = [("rgba", ctypes.c_void_p), ("width", ctypes.c_int32), ("height", ctypes.c_int32)]
 
 
 class PtbError(RuntimeError):
@@ -68,6 +72,7 @@ def load_library():
     L.ptb_upload_objects.argtypes = [vp, vp, ctypes.c_uint32]
     L.ptb_upload_materials.argtypes = [vp, vp, ctypes.c_uint32]
     L.ptb_load_ptbs.argtypes = [vp, ctypes.c_char_p]
+    L.ptb_upload_textures.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32]
     L.ptb_set_camera.argtypes = [vp, ctypes.POINTER(Camera)]
     L.ptb_build_bvh.argtypes = [vp]
     L.ptb_build_bvh_gpu.argtypes = [vp]
@@ -165,6 +170,17 @@ class PathTracer:
     def upload_materials(self, materials_bytes, n):
         buf = (ctypes.c_char * len(materials_bytes)).from_buffer_copy(materials_bytes)
         self._ck(self.L.ptb_upload_materials(self.h, ctypes.cast(buf, ctypes.c_void_p), n), "ptb_upload_materials")
+
+    def upload_textures(self, textures, material_tex2):
+        """textures: list of float32 arrays (height, width, 4); material_tex2: per material (albedo texture, normal map), -1 none."""
+        keep = [np.ascontiguousarray(t, np.float32) for t in textures]
+        arr = (Texture * max(1, len(keep)))()
+        for i, t in enumerate(keep):
+            if t.ndim != 3 or t.shape[2] != 4:
+                raise ValueError("texture must be (height, width, 4)")
+            arr[i] = Texture(t.ctypes.data, t.shape[1], t.shape[0])
+        b = np.ascontiguousarray(material_tex2, np.int32).reshape(-1, 2)
+        self._ck(self.L.ptb_upload_textures(self.h, ctypes.cast(arr, ctypes.c_void_p), len(keep), _ptr(b), b.shape[0]), "ptb_upload_textures")
 
     def set_camera(self, origin, forward, focus=1.0, dof=0.0, fov_degrees=70.0):
         cam = Camera((ctypes.c_float * 3)(*origin), (ctypes.c_float * 3)(*forward), focus, dof, fov_degrees)

@@ -79,8 +79,15 @@ struct ptb_ctx {
     bool poisoned = false;
 
     // host copy of the scene (what the loader handed over)
-    std::vector<float> pos9, nrm9;
+    std::vector<float> pos9, nrm9, uv6;
     std::vector<int32_t> mat;
+    // textures (ptb_upload_textures): host copies + per-material bindings {albedo texture, normal map}
+    std::vector<std::vector<float>> texData;
+    std::vector<int32_t> texW, texH, matTex;
+    bool haveTextures = false; // some material binds a texture: renders use the TEX build of the path kernel
+    float2 *dUv = nullptr;
+    TexDev *dTexTable = nullptr;
+    float4 *dTexels = nullptr;
     std::vector<ptbs_object> objects;
     std::vector<ptbs_material> materials;
     std::vector<LightDev> lights;
@@ -343,6 +350,7 @@ extern "C" void ptb_destroy(ptb_ctx *c) {
     devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
     devFree(c->dBeam); devFree(c->dBeamIdx);
     devFree(c->dRefNode); devFree(c->dRefIdx); devFree(c->dRefObjRoot);
+    devFree(c->dUv); devFree(c->dTexTable); devFree(c->dTexels);
     for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
     devFree(c->dRings); devFree(c->dCounters); devFree(c->dShScratch);
     devFree(c->dScratchF); devFree(c->dScratchI); devFree(c->dRays);
@@ -365,9 +373,10 @@ extern "C" const char *ptb_last_error(const ptb_ctx *c) { return c ? c->err.c_st
 // =============================================================================================
 extern "C" int ptb_upload_triangles(ptb_ctx *c, const float *pos9, const float *nrm9, const float *uv6, const int32_t *mat, uint64_t n) {
     GUARD(c);
-    (void)uv6; // texture lookups are outside the hot-path scope (no textured scene ships)
     if (n && (!pos9 || !nrm9 || !mat)) return fail(c, PTB_ERR_INVALID, "null triangle arrays");
     if (n >= (1ull << 27)) return fail(c, PTB_ERR_INVALID, "more than 2^27 triangles");
+    if (uv6) c->uv6.assign(uv6, uv6 + 6 * n); // Triangle::uv, read only by textured materials
+    else c->uv6.clear();
     c->pos9.assign(pos9, pos9 + 9 * n);
     c->nrm9.assign(nrm9, nrm9 + 9 * n);
     c->mat.assign(mat, mat + n);
@@ -403,13 +412,14 @@ extern "C" int ptb_upload_objects(ptb_ctx *c, const ptbs_object *objects, uint32
     return upload_lights(c);
 }
 
-extern "C" int ptb_upload_materials(ptb_ctx *c, const ptbs_material *materials, uint32_t n) {
-    GUARD(c);
-    if (n && !materials) return fail(c, PTB_ERR_INVALID, "null materials");
-    c->materials.assign(materials, materials + n);
+// MatDev table from the host material list + the texture bindings (if any)
+static int upload_matdev(ptb_ctx *c) {
+    const uint32_t n = (uint32_t)c->materials.size();
     std::vector<MatDev> md(n);
+    const bool bound = c->matTex.size() == 2 * (size_t)n;
+    c->haveTextures = false;
     for (uint32_t i = 0; i < n; ++i) {
-        const ptbs_material &m = materials[i];
+        const ptbs_material &m = c->materials[i];
         MatDev &d = md[i];
         memset(&d, 0, sizeof d);
         for (int k = 0; k < 3; ++k) {
@@ -418,6 +428,13 @@ extern "C" int ptb_upload_materials(ptb_ctx *c, const ptbs_material *materials, 
         }
         d.ior1 = m.ior1; d.ior2 = m.ior2; d.emission = m.emission; d.roughness = m.roughness;
         d.wl = m.w_lambert; d.wr = m.w_reflection; d.wt = m.w_refraction;
+        d.tex = d.nrm = -1;
+        if (bound) { // texture t lives twice in the pool: 2t = gamma-expanded copy (albedo use), 2t+1 = raw copy (normal maps)
+            const int32_t ta = c->matTex[2 * i], tn = c->matTex[2 * i + 1];
+            if (ta >= 0) d.tex = 2 * ta;
+            if (tn >= 0) d.nrm = 2 * tn + 1;
+            if (ta >= 0 || tn >= 0) c->haveTextures = true;
+        }
     }
     devFree(c->dMats);
     if (n) {
@@ -425,7 +442,86 @@ extern "C" int ptb_upload_materials(ptb_ctx *c, const ptbs_material *materials, 
         CK(cudaMemcpy(c->dMats, md.data(), n * sizeof(MatDev), cudaMemcpyHostToDevice));
     }
     c->A.mats = c->dMats;
+    return PTB_OK;
+}
+
+extern "C" int ptb_upload_materials(ptb_ctx *c, const ptbs_material *materials, uint32_t n) {
+    GUARD(c);
+    if (n && !materials) return fail(c, PTB_ERR_INVALID, "null materials");
+    if (n != c->materials.size()) c->matTex.clear(); // another material list: the bindings no longer apply
+    c->materials.assign(materials, materials + n);
+    if (int r = upload_matdev(c)) return r;
     return upload_lights(c);
+}
+
+// Triangle::uv in leaf order, for the texture lookups (needs the BVH's order; no-op until both exist)
+static int upload_uv(ptb_ctx *c) {
+    devFree(c->dUv);
+    c->A.uv = nullptr;
+    const size_t n = c->mat.size();
+    if (!c->haveTextures || !c->bvhBuilt || n == 0) return PTB_OK;
+    std::vector<float2> uv(3 * n, make_float2(0.0f, 0.0f));
+    if (c->uv6.size() == 6 * n)
+        for (size_t k = 0; k < n; ++k) {
+            const float *q = &c->uv6[6 * (size_t)c->bvh.order[k]];
+            uv[3 * k] = make_float2(q[0], q[1]);
+            uv[3 * k + 1] = make_float2(q[2], q[3]);
+            uv[3 * k + 2] = make_float2(q[4], q[5]);
+        }
+    CK(cudaMalloc(&c->dUv, uv.size() * sizeof(float2)));
+    CK(cudaMemcpy(c->dUv, uv.data(), uv.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    c->A.uv = c->dUv;
+    return PTB_OK;
+}
+
+// Material textures: pbrProbs::texture / ::normal (shader.h:14-24), Texture = width x height float rgba
+// (texture.h:7-11, byte/255.0f as loadTexture leaves them, texture.cpp:33-50).  The albedo copy is gamma-expanded
+// here with the host libm — the reference applies powf(c, 2.2f) to every texel it reads (shader.cpp:214) — so the
+// kernel never evaluates powf; normal maps are kept raw.
+extern "C" int ptb_upload_textures(ptb_ctx *c, const ptb_texture *textures, uint32_t n_textures, const int32_t *material_tex2, uint32_t n_materials) {
+    GUARD(c);
+    SETTLE(c);
+    if (n_textures && !textures) return fail(c, PTB_ERR_INVALID, "null textures");
+    if (n_materials != c->materials.size()) return fail(c, PTB_ERR_INVALID, "ptb_upload_materials first: one {albedo, normal} binding per material");
+    if (n_materials && !material_tex2) return fail(c, PTB_ERR_INVALID, "null bindings");
+    uint64_t texels = 0;
+    for (uint32_t t = 0; t < n_textures; ++t) {
+        if (!textures[t].rgba || textures[t].width <= 0 || textures[t].height <= 0 || textures[t].width > 32768 || textures[t].height > 32768)
+            return fail(c, PTB_ERR_INVALID, "texture without data or with a bad size");
+        texels += (uint64_t)textures[t].width * textures[t].height;
+    }
+    if (2 * texels >= (1ull << 32)) return fail(c, PTB_ERR_INVALID, "more than 2^31 texels");
+    for (uint32_t i = 0; i < 2 * n_materials; ++i)
+        if (material_tex2[i] < -1 || material_tex2[i] >= (int32_t)n_textures) return fail(c, PTB_ERR_INVALID, "texture binding out of range");
+    c->texData.resize(n_textures);
+    c->texW.resize(n_textures);
+    c->texH.resize(n_textures);
+    std::vector<TexDev> table(2 * (size_t)n_textures);
+    std::vector<float4> pool(2 * texels);
+    uint32_t at = 0;
+    for (uint32_t t = 0; t < n_textures; ++t) {
+        const size_t px = (size_t)textures[t].width * textures[t].height;
+        c->texData[t].assign(textures[t].rgba, textures[t].rgba + 4 * px);
+        c->texW[t] = textures[t].width;
+        c->texH[t] = textures[t].height;
+        const float *q = c->texData[t].data();
+        table[2 * t] = TexDev{at, textures[t].width, textures[t].height, 0};
+        for (size_t i = 0; i < px; ++i) pool[at + i] = make_float4(powf(q[4 * i], 2.2f), powf(q[4 * i + 1], 2.2f), powf(q[4 * i + 2], 2.2f), q[4 * i + 3]);
+        at += (uint32_t)px;
+        table[2 * t + 1] = TexDev{at, textures[t].width, textures[t].height, 0};
+        for (size_t i = 0; i < px; ++i) pool[at + i] = make_float4(q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3]);
+        at += (uint32_t)px;
+    }
+    c->matTex.assign(material_tex2, material_tex2 + 2 * (size_t)n_materials);
+    devFree(c->dTexTable); devFree(c->dTexels);
+    CK(cudaMalloc(&c->dTexTable, std::max<size_t>(1, table.size()) * sizeof(TexDev)));
+    CK(cudaMalloc(&c->dTexels, std::max<size_t>(1, pool.size()) * sizeof(float4)));
+    if (!table.empty()) CK(cudaMemcpy(c->dTexTable, table.data(), table.size() * sizeof(TexDev), cudaMemcpyHostToDevice));
+    if (!pool.empty()) CK(cudaMemcpy(c->dTexels, pool.data(), pool.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    c->A.tex = c->dTexTable;
+    c->A.texels = c->dTexels;
+    if (int r = upload_matdev(c)) return r;
+    return upload_uv(c);
 }
 
 extern "C" int ptb_set_camera(ptb_ctx *c, const ptb_camera *cam) {
@@ -460,9 +556,9 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
     FILE *f = path ? fopen(path, "rb") : nullptr;
     if (!f) return fail(c, PTB_ERR_IO, std::string("cannot open ") + (path ? path : "(null)"));
     ptbs_header h;
-    if (fread(&h, sizeof h, 1, f) != 1 || h.magic != PTBS_MAGIC || h.version != PTBS_VERSION) {
+    if (fread(&h, sizeof h, 1, f) != 1 || h.magic != PTBS_MAGIC || (h.version != PTBS_VERSION && h.version != PTBS_VERSION_TEXTURES)) {
         fclose(f);
-        return fail(c, PTB_ERR_IO, "not a .ptbs v1 container");
+        return fail(c, PTB_ERR_IO, "not a .ptbs v1/v2 container");
     }
     size_t n = h.n_tris;
     std::vector<float> pos(n * 9), nrm(n * 9), uv(n * 6);
@@ -473,12 +569,28 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
               fread(uv.data(), 4, n * 6, f) == n * 6 && fread(mat.data(), 4, n, f) == n &&
               fread(objs.data(), sizeof(ptbs_object), objs.size(), f) == objs.size() &&
               fread(mats.data(), sizeof(ptbs_material), mats.size(), f) == mats.size();
+    std::vector<int32_t> matTex(2 * mats.size(), -1);
+    std::vector<std::vector<float>> texData;
+    std::vector<ptb_texture> tex;
+    if (ok && h.version >= PTBS_VERSION_TEXTURES && h.reserved[0] > 0) {
+        ok = fread(matTex.data(), 4, matTex.size(), f) == matTex.size();
+        for (uint32_t k = 0; ok && k < h.reserved[0]; ++k) {
+            ptbs_texture_hdr th;
+            ok = fread(&th, sizeof th, 1, f) == 1 && th.width > 0 && th.height > 0 && th.width <= 32768 && th.height <= 32768;
+            if (!ok) break;
+            texData.emplace_back((size_t)th.width * th.height * 4);
+            ok = fread(texData.back().data(), 4, texData.back().size(), f) == texData.back().size();
+            tex.push_back(ptb_texture{nullptr, th.width, th.height});
+        }
+    }
     fclose(f);
     if (!ok) return fail(c, PTB_ERR_IO, "truncated .ptbs container");
     int r;
     if ((r = ptb_upload_triangles(c, pos.data(), nrm.data(), uv.data(), mat.data(), n))) return r;
     if ((r = ptb_upload_materials(c, mats.data(), (uint32_t)mats.size()))) return r;
     if ((r = ptb_upload_objects(c, objs.data(), (uint32_t)objs.size()))) return r;
+    for (size_t k = 0; k < tex.size(); ++k) tex[k].rgba = texData[k].data();
+    if (!tex.empty() && (r = ptb_upload_textures(c, tex.data(), (uint32_t)tex.size(), matTex.data(), (uint32_t)mats.size()))) return r;
     ptb_camera cam{};
     for (int k = 0; k < 3; ++k) {
         cam.origin[k] = h.cam_pos[k];
@@ -550,7 +662,7 @@ extern "C" int ptb_build_bvh(ptb_ctx *c) {
     c->bvhOnGpu = false;
     c->bvhNodes = c->bvh.nodes.size();
     c->gridBuilt = c->beamBuilt = false;
-    return PTB_OK;
+    return upload_uv(c);
 }
 
 // constructBVH on the device (ptb_lbvh.cu): the triangles go up once in reference order, everything else —
@@ -607,7 +719,7 @@ extern "C" int ptb_build_bvh_gpu(ptb_ctx *c) {
     c->bvhBuilt = c->bvhOnGpu = true;
     c->bvhNodes = R.n_nodes;
     c->lastBuildMs = c->lastBuildDeviceMs = R.ms;
-    return PTB_OK;
+    return upload_uv(c);
 }
 
 extern "C" double ptb_last_build_ms(const ptb_ctx *c) { return c ? c->lastBuildMs : 0.0; }
@@ -1051,11 +1163,18 @@ int render_mega(ptb_ctx *c, int add) {
     }
     if (!launched) {
         const bool nee = P.nee && P.n_lights > 0;
+        const bool tex = c->haveTextures; // a material binds a texture: the build of the kernel with the texture branches
+#define PTB_MEGA_LAUNCH(NEEV, EARLYV)                                                                                  \
+    do {                                                                                                               \
+        if (tex) k_mega<MODE, COUNT, NEEV, EARLYV, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);     \
+        else k_mega<MODE, COUNT, NEEV, EARLYV, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);        \
+    } while (0)
         if (MODE == 1 && M.leaf_keep > 0) { // deep tree: straggler exit in the node loop
-            if (nee) k_mega<MODE, COUNT, true, MODE == 1><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
-            else k_mega<MODE, COUNT, false, MODE == 1><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
-        } else if (nee) k_mega<MODE, COUNT, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
-        else k_mega<MODE, COUNT, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
+            if (nee) PTB_MEGA_LAUNCH(true, MODE == 1);
+            else PTB_MEGA_LAUNCH(false, MODE == 1);
+        } else if (nee) PTB_MEGA_LAUNCH(true, false);
+        else PTB_MEGA_LAUNCH(false, false);
+#undef PTB_MEGA_LAUNCH
     }
     CK(cudaEventRecord(c->evStop, c->stream));
     c->pendingRender = true;
@@ -1088,6 +1207,8 @@ int finish_mega(ptb_ctx *c) {
 
 template <bool COUNT>
 int render_dispatch(ptb_ctx *c, int add) {
+    if (c->haveTextures && c->useMega != 1)
+        return fail(c, PTB_ERR_INVALID, "textured materials are sampled by the default path kernel only (unset PTB_MEGA)");
     if (c->useRefBvh && c->prm.mode == PTB_MODE_BVH) {
         if (!c->useMega) return fail(c, PTB_ERR_INVALID, "the reference tree is traversed by the path kernel only (unset PTB_MEGA=0)");
         return render_mega<4, true>(c, add); // always the counting build: the counters are why this tree is here

@@ -29,7 +29,14 @@ struct MatDev { // 16 floats
     float albedo[3];
     float gamma[3]; // powf(albedo, 2.2f) evaluated on the host with the same libm the reference uses (shader.cpp:39-44)
     float ior1, ior2, emission, roughness, wl, wr, wt;
-    float pad[3];
+    int tex, nrm; // pbrProbs::texture / ::normal (shader.h:14-24) as indices into AttrDev::tex, -1 = none
+    float pad;
+};
+
+struct TexDev { // Texture (texture.h:7-11): texels at AttrDev::texels + offset, row-major y*width+x
+    uint32_t offset;
+    int width, height;
+    int pad;
 };
 
 struct LightDev { // Object fields NEE reads (shader.cpp:69-113, object.cpp:176-180)
@@ -79,6 +86,10 @@ struct AttrDev {
     const uint32_t *tri_of_id; // reference triangle id -> leaf-order index
     const uint32_t *id_of_tri; // leaf-order index -> reference id
     const float *vtx;          // 9 floats per triangle by reference id (NEE light points); null unless nee
+    // textures (ptb_upload_textures); null / unused unless a material binds one
+    const float2 *uv;          // 3 float2 per triangle (uv0, uv1, uv2), leaf order
+    const TexDev *tex;
+    const float4 *texels;      // albedo textures: rgb already gamma-expanded on the host (powf(c, 2.2f), shader.cpp:39-44), a = opacity
 };
 
 __device__ __forceinline__ f3 ld3(const float *p) { return mk3(p[0], p[1], p[2]); }
@@ -163,6 +174,25 @@ __device__ __forceinline__ void hit_frame(const AttrDev &A, int tri, float u, fl
     bt = cross3(n, tg);
 }
 
+// ray.uv = u*uv1 + v*uv2 + (1-u-v)*uv0, triangle.cpp:46 (Vector2: plain component-wise floats, vector.cpp:83-115)
+__device__ __forceinline__ float2 hit_uv(const AttrDev &A, int tri, float u, float v) {
+    const float2 a = __ldg(&A.uv[3 * tri]), b = __ldg(&A.uv[3 * tri + 1]), c = __ldg(&A.uv[3 * tri + 2]);
+    const float w = 1 - u - v;
+    return make_float2((u * b.x + v * c.x) + w * a.x, (u * b.y + v * c.y) + w * a.y);
+}
+// getTextureAtUV, texture.cpp:22-32: the reference's own wrap rule and nearest texel
+__device__ __forceinline__ float4 tex_at(const AttrDev &A, int ti, float2 q) {
+    const TexDev T = A.tex[ti];
+    float u = q.x, v = q.y;
+    if (u > 1) u = (u - (float)(int)u);
+    if (v > 1) v = (v - (float)(int)v);
+    if (v < 0) v = 1 + (v - (float)(int)v);
+    if (u < 0) u = 1 + (u - (float)(int)u);
+    const int x = (int)roundf(u * (float)(T.width - 1));
+    const int y = (int)roundf(v * (float)(T.height - 1));
+    return __ldg(&A.texels[T.offset + (uint32_t)(y * T.width + x)]);
+}
+
 struct PathState {
     f3 o, d, tp, light;
     int depth;
@@ -181,7 +211,9 @@ struct ShadowOut {
 // Returns with the path's next ray in (o,d).  When NEE fires a shadow ray, `light` is left
 // BEFORE the two adds of shader.cpp:233 and :275; they are applied in order by the shadow
 // resolve (pendingEm = emission*throughput).
-template <bool NEE = true>
+// TEX compiles the texture branches in (shader.cpp:52-66 albedo texture + alpha, :251-258 normal map); the
+// untextured build keeps the exact instruction stream it had (the path kernel is instruction-cache bound).
+template <bool NEE = true, bool TEX = false>
 __device__ __forceinline__ void shade_hit(const ParamsDev &P, const SceneDev &S, const AttrDev &A, PathState &ps, float t, int tri,
                                           float u, float v, bool &terminated, ShadowOut &sh, f3 &pendingEm) {
     f3 n, tg, bt;
@@ -193,8 +225,29 @@ __device__ __forceinline__ void shade_hit(const ParamsDev &P, const SceneDev &S,
         ps.light = ld3(m.albedo);
     }
     const float xi = fast_random(ps.rng);
-    const f3 color = ld3(m.gamma);
+    f3 color = ld3(m.gamma);
     sh.emit = false;
+    if (TEX && (m.tex >= 0 || m.nrm >= 0)) {
+        const float2 q = hit_uv(A, tri, u, v);
+        if (m.nrm >= 0) { // shader.cpp:251-258: the tangent and bitangent stay those of the interpolated normal
+            const float4 nc = tex_at(A, m.nrm, q);
+            const f3 tn = mk3(2.0f * nc.x, 2.0f * nc.y, 2.0f * nc.z) - mk3(1.0f, 1.0f, 1.0f);
+            f3 nn = tn.x * tg;
+            nn = nn + tn.y * bt;
+            nn = nn + tn.z * n;
+            n = normalize3(nn);
+        }
+        if (m.tex >= 0 && xi < m.wl) { // getColorOfMaterial, shader.cpp:52-66: only the lambert lobe reads the texture
+            const float4 fg = tex_at(A, m.tex, q);
+            const float xa = fast_random(ps.rng);
+            if (xa < 1 - fg.w) { // see-through texel: step behind the surface, same direction (shader.cpp:208-212)
+                ps.o = ps.o + ps.d * (t + 0.01f);
+                pendingEm = m.emission * ps.tp;
+                return;
+            }
+            color = mk3(fg.x, fg.y, fg.z);
+        }
+    }
     // All three lobes draw ONE cosine-weighted direction and rotate it into the hit frame with the same
     // operations (shader.cpp:211-214, :127-131, :189-193); only refraction draws its Fresnel number first.
     // Hoisted out of the branches: one copy of the double-precision sin/cos in the instruction stream instead

@@ -56,7 +56,8 @@ struct MegaArgs {
 // EARLY (BVH only): BvhWalk::round leaves its node loop when fewer than leaf_keep/32 of the walking lanes still descend.
 // NEE = false compiles the shadow-ray state machine and its 19 words of per-lane state out (the reference's
 // own --testing protocol renders with NEE off, main.cpp:101).
-template <int MODE, bool COUNT, bool NEE, bool EARLY = false>
+// TEX = true compiles the texture branches of shade_hit in (scenes that bind textures; ptb_upload_textures).
+template <int MODE, bool COUNT, bool NEE, bool EARLY = false, bool TEX = false>
 __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, MegaArgs M) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -71,6 +72,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
     ShadowRec sr;
     float shadowT = 0.0f;
     int shadowTri = -1;
+    float shadowU = 0.0f, shadowV = 0.0f; // TEX only: where the shadow ray ended (a textured light is sampled there)
     BvhWalk w;
     int2 stack[PTB_STACK];
     uint32_t nTri = 0, nAS = 0;
@@ -154,6 +156,23 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                         const int lm = __float_as_int(__ldg(&A.nrm[3 * shadowTri]).w);
                         const MatDev m = A.mats[lm];
                         f3 lc = ld3(m.gamma);
+                        if (TEX && m.tex >= 0) { // getColorOfMaterial(shadowRay, lightMaterial), shader.cpp:106
+                            float su = shadowU, sv = shadowV;
+                            if (shadowTri == sr.lightTri) { // the light triangle's own hit was the ray's starting hit: (u,v) as at shader.cpp:97
+                                Hit lh{PTB_INF, -1, 0.0f, 0.0f, -1};
+                                uint32_t dummy = 0;
+                                intersect_tri<false>(S.tri, sr.lightTri, sr.o, sr.d, lh, dummy);
+                                su = lh.u;
+                                sv = lh.v;
+                            }
+                            const float4 fg = tex_at(A, m.tex, hit_uv(A, shadowTri, su, sv));
+                            uint32_t rs = 0; // the shadow ray's own stream: one draw in findIntersection, then the alpha draw
+                            fast_random(rs);
+                            const float xa = fast_random(rs);
+                            // a see-through texel returns {-1,0,0}, which gammaCorrect turns into (NaN,0,0) BEFORE the
+                            // reference tests for -1 (shader.cpp:107-109): the NaN is carried on, here too
+                            lc = (xa < 1 - fg.w) ? mk3(__int_as_float(0x7fc00000), 0.0f, 0.0f) : mk3(fg.x, fg.y, fg.z);
+                        }
                         lc = lc / 3.14f * m.emission * sr.cosSurface * inv_sq * sr.cosLight * sr.area * (float)P.n_lights;
                         ps.light = ps.light + lc * sr.tpAt;
                     }
@@ -174,7 +193,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                     if (tri >= 0) {
                         ShadowOut sh;
                         f3 pendingEm;
-                        shade_hit<NEE>(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
+                        shade_hit<NEE, TEX>(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
                     }
                     ps.depth++;
                     terminated = true;
@@ -203,7 +222,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                 } else {
                     ShadowOut sh;
                     f3 pendingEm;
-                    shade_hit<NEE>(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
+                    shade_hit<NEE, TEX>(P, S, A, ps, w.h.t, tri, w.h.u, w.h.v, terminated, sh, pendingEm);
                     if (NEE && sh.emit) {
                         sr.o = sh.o;
                         sr.d = sh.d;
@@ -287,6 +306,10 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                         if (NEE && phase == LANE_SHADOW) {
                             shadowT = w.h.t;
                             shadowTri = w.h.tri;
+                            if (TEX) {
+                                shadowU = w.h.u;
+                                shadowV = w.h.v;
+                            }
                             if (ps.flags & PTB_FLAG_DONE) phase = LANE_LOGIC; // the DONE branch of the logic pass ignores the path hit
                             else begin_main();
                         } else {

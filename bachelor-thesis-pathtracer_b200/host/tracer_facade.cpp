@@ -37,6 +37,7 @@
 #include "scene/scene.h"
 #include "shader/shader.h"
 #include "types/camera.h"
+#include "types/texture.h"
 
 #include "ptb.h"
 #include "tracer_facade.h"
@@ -58,6 +59,7 @@ unsigned gridGs = 10, gridOs = 5, gridM = 40, beamGs = 10, beamM = 40; // main.c
 bool gridBuilt = false, beamBuilt = false;
 int maxDepth = 0;
 bool useReferenceTree = false; // ptbFacadeUseReferenceTree
+bool texturesUploaded = false;
 int renderedSamples = 0;
 std::vector<float> mirror; // host copy of the frame that tracerGetPixel serves (refreshed per batch)
 uint64_t counters[PTB_CNT__N] = {0};
@@ -90,6 +92,28 @@ bool uploadMaterials() {
         strncpy(pm[i].name, m.name.c_str(), sizeof pm[i].name - 1);
     }
     return ok(ptb_upload_materials(ctx, pm.data(), (uint32_t)pm.size()), "ptb_upload_materials");
+}
+
+// Once per scene upload (the texel pools are rebuilt and gamma-expanded by the library); later material edits go
+// through ptb_upload_materials alone, which keeps the bindings.
+bool uploadTextures() {
+    auto &mats = *getMaterials();
+    // pbrProbs::texture / ::normal (shader.h:14-24): Texture::data is width*height Vector4 = 4 packed floats per texel
+    std::vector<ptb_texture> tex;
+    std::vector<int32_t> bind(2 * mats.size(), -1);
+    for (size_t i = 0; i < mats.size(); ++i) {
+        Texture *ts[2] = {&mats[i].pbr.texture, &mats[i].pbr.normal};
+        for (int k = 0; k < 2; ++k) {
+            Texture &t = *ts[k];
+            if (t.data.empty() || t.width <= 0 || t.height <= 0 || t.data.size() != (size_t)t.width * t.height) continue;
+            static_assert(sizeof(Vector4) == 4 * sizeof(float), "Vector4 must be 4 packed floats");
+            bind[2 * i + k] = (int32_t)tex.size();
+            tex.push_back(ptb_texture{&t.data[0].x, t.width, t.height});
+        }
+    }
+    if (tex.empty() && !texturesUploaded) return true;
+    texturesUploaded = !tex.empty();
+    return ok(ptb_upload_textures(ctx, tex.data(), (uint32_t)tex.size(), bind.data(), (uint32_t)mats.size()), "ptb_upload_textures");
 }
 
 bool uploadObjects() {
@@ -129,7 +153,7 @@ bool uploadScene() {
         mat[i] = t.materialIdx;
     }
     if (!ok(ptb_upload_triangles(ctx, pos.data(), nrm.data(), uv.data(), mat.data(), n), "ptb_upload_triangles")) return false;
-    if (!uploadMaterials() || !uploadObjects()) return false;
+    if (!uploadMaterials() || !uploadTextures() || !uploadObjects()) return false;
     if (!ok(ptb_build_bvh(ctx), "ptb_build_bvh")) return false; // constructBVH, scene.cpp:113-120
     gridBuilt = beamBuilt = false;
     uploadedTris = n;

@@ -29,8 +29,8 @@ def _name(b):
 def read_ptbs(path):
     b = open(path, "rb").read()
     h = _HDR.unpack_from(b, 0)
-    if h[0] != PTBS_MAGIC or h[1] != 1:
-        raise ValueError("not a .ptbs v1 container")
+    if h[0] != PTBS_MAGIC or h[1] not in (1, 2):
+        raise ValueError("not a .ptbs v1/v2 container")
     n, no, nm = h[2], h[3], h[4]
     off = _HDR.size
     pos = np.frombuffer(b, np.float32, n * 9, off).reshape(n, 9).copy(); off += n * 36
@@ -47,7 +47,16 @@ def read_ptbs(path):
         materials.append({"albedo": list(f[0:3]), "ior1": f[3], "ior2": f[4], "emission": f[5], "roughness": f[6],
                           "weights": list(f[7:10]), "name": _name(f[10])})
     cam = {"pos": list(h[8:11]), "forward": list(h[11:14]), "focus": h[14], "dof": h[15]}
-    return {"pos": pos, "nrm": nrm, "uv": uv, "mat": mat, "objects": objects, "materials": materials, "camera": cam}
+    scene = {"pos": pos, "nrm": nrm, "uv": uv, "mat": mat, "objects": objects, "materials": materials, "camera": cam}
+    if h[1] >= 2 and h[5] > 0:  # version 2: per-material {albedo texture, normal map} + the textures (ptbs_format.h)
+        b2 = np.frombuffer(b, np.int32, 2 * nm, off).reshape(nm, 2); off += 8 * nm
+        for m, (ta, tn) in zip(materials, b2):
+            m["tex"], m["nrm"] = int(ta), int(tn)
+        scene["textures"] = []
+        for _ in range(h[5]):
+            w, hh = struct.unpack_from("<ii", b, off); off += 8
+            scene["textures"].append(np.frombuffer(b, np.float32, w * hh * 4, off).reshape(hh, w, 4).copy()); off += w * hh * 16
+    return scene
 
 
 def pack_objects(objects):
@@ -67,11 +76,17 @@ def pack_materials(materials):
     return bytes(out)
 
 
+def material_bindings(scene):
+    """n_materials x {albedo texture, normal map} (-1 = none) of a scene dict."""
+    return np.array([[int(m.get("tex", -1)), int(m.get("nrm", -1))] for m in scene["materials"]], np.int32).reshape(-1, 2)
+
+
 def write_ptbs(path, scene):
     n = scene["pos"].shape[0]
     c = scene["camera"]
+    tex = scene.get("textures") or []
     with open(path, "wb") as f:
-        f.write(_HDR.pack(PTBS_MAGIC, 1, n, len(scene["objects"]), len(scene["materials"]), 0, 0, 0,
+        f.write(_HDR.pack(PTBS_MAGIC, 2 if tex else 1, n, len(scene["objects"]), len(scene["materials"]), len(tex), 0, 0,
                           *[float(x) for x in c["pos"]], *[float(x) for x in c["forward"]], float(c["focus"]), float(c["dof"])))
         f.write(np.ascontiguousarray(scene["pos"], np.float32).tobytes())
         f.write(np.ascontiguousarray(scene["nrm"], np.float32).tobytes())
@@ -79,13 +94,21 @@ def write_ptbs(path, scene):
         f.write(np.ascontiguousarray(scene["mat"], np.int32).tobytes())
         f.write(pack_objects(scene["objects"]))
         f.write(pack_materials(scene["materials"]))
+        if tex:
+            f.write(material_bindings(scene).tobytes())
+            for t in tex:
+                t = np.ascontiguousarray(t, np.float32)
+                f.write(struct.pack("<ii", t.shape[1], t.shape[0]))
+                f.write(t.tobytes())
 
 
 def upload_scene(pt, scene):
-    """The three uploads + camera of a scene dict through the C ABI."""
+    """The uploads + camera of a scene dict through the C ABI."""
     pt.upload_triangles(scene["pos"], scene["nrm"], scene["uv"], scene["mat"])
     pt.upload_materials(pack_materials(scene["materials"]), len(scene["materials"]))
     pt.upload_objects(pack_objects(scene["objects"]), len(scene["objects"]))
+    if scene.get("textures"):
+        pt.upload_textures(scene["textures"], material_bindings(scene))
     c = scene["camera"]
     pt.set_camera(c["pos"], c["forward"], c["focus"], c["dof"])
 
@@ -226,6 +249,36 @@ def triangle_soup(n, seed=None):
     return {"pos": pos, "nrm": _flat_normals(pos), "uv": np.zeros((n, 6), np.float32), "mat": np.zeros(n, np.int32),
             "objects": [{"start": 0, "end": n, "area": float(_tri_area(pos).sum()), "materials": [0], "name": "Soup"}],
             "materials": mats, "camera": {"pos": [0.0, 0.0, -400.0], "forward": [0.0, 0.0, 1.0], "focus": 1.0, "dof": 0.0}}
+
+
+def _texture_bytes(w, h, salt, alpha):
+    """Deterministic RGBA bytes -> Texture::data exactly as loadTexture leaves it (byte / 255.0f, texture.cpp:41-44).
+    alpha: "opaque", or "holes" = a pattern of fully transparent, half transparent and opaque texels."""
+    y, x = np.mgrid[0:h, 0:w].astype(np.int64)
+    px = np.empty((h, w, 4), np.int64)
+    for c in range(3):
+        px[..., c] = (x * 37 + y * 91 + c * 53 + salt * 17 + ((x // 2 + y // 2) % 2) * 128) % 256
+    if alpha == "opaque":
+        px[..., 3] = 255
+    else:
+        px[..., 3] = np.choose((x + 2 * y) % 4, [255, 0, 128, 255])
+    return (px.astype(np.float32) / np.float32(255.0)).astype(np.float32)
+
+
+def textured_cornell(room, light_texture=True):
+    """The Cornell box with textures on it — no textured scene ships with the reference, so this exercises the texture
+    branches of the shader (shader.cpp:52-66,251-258) on its own scene: an albedo texture with see-through and
+    half-transparent texels on two walls, a normal map on the floor and on the glass sphere, an opaque texture on the
+    emissive cube (sampled by NEE), and uv stretched to [-1, 2] so that every branch of getTextureAtUV's wrap rule runs."""
+    s = {k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in room.items()}
+    s["materials"] = [dict(m) for m in room["materials"]]
+    s["uv"] = (room["uv"].astype(np.float32) * np.float32(3.0) - np.float32(1.0)).astype(np.float32)
+    s["textures"] = [_texture_bytes(16, 16, 1, "holes"), _texture_bytes(8, 5, 2, "opaque"), _texture_bytes(4, 4, 3, "opaque")]
+    for mi, (ta, tn) in {1: (0, -1), 6: (0, 1), 5: (-1, 1), 4: (-1, 1), 7: (0, -1)}.items():
+        s["materials"][mi]["tex"], s["materials"][mi]["nrm"] = ta, tn
+    if light_texture:
+        s["materials"][3]["tex"] = 2
+    return s
 
 
 def scene_from_triangles(pos):

@@ -88,7 +88,18 @@ const char *ptb_last_error(const ptb_ctx *ctx); /* never NULL; ctx may be NULL (
 int ptb_upload_triangles(ptb_ctx *ctx, const float *pos9, const float *nrm9, const float *uv6, const int32_t *mat, uint64_t n);
 int ptb_upload_objects(ptb_ctx *ctx, const ptbs_object *objects, uint32_t n);       /* also derives the light list, scene.cpp:138-148 */
 int ptb_upload_materials(ptb_ctx *ctx, const ptbs_material *materials, uint32_t n); /* may be called again (UI edits + reset) */
-int ptb_load_ptbs(ptb_ctx *ctx, const char *path); /* the three uploads + camera from one .ptbs container */
+/* Material textures: pbrProbs::texture / ::normal (src/shader/shader.h:14-24) as getColorOfMaterial (shader.cpp:52-66:
+ * nearest texel at the hit's uv, opacity = alpha with one RNG draw, see-through texels step behind the surface) and the
+ * normal-map branch of shade (shader.cpp:251-258) read them.  rgba = Texture::data (src/types/texture.h:7-11), row-major
+ * y*width+x, channel = byte/255.0f as loadTexture leaves it (texture.cpp:33-50).  material_tex2 = n_materials x
+ * {albedo texture, normal map} indices into `textures`, -1 = none; call after ptb_upload_materials (a later
+ * ptb_upload_materials with the same material count keeps the bindings: the UI edit + reset flow). */
+typedef struct ptb_texture {
+    const float *rgba;
+    int32_t width, height;
+} ptb_texture;
+int ptb_upload_textures(ptb_ctx *ctx, const ptb_texture *textures, uint32_t n_textures, const int32_t *material_tex2, uint32_t n_materials);
+int ptb_load_ptbs(ptb_ctx *ctx, const char *path); /* the uploads + camera from one .ptbs container (v1, or v2 with textures) */
 int ptb_set_camera(ptb_ctx *ctx, const ptb_camera *cam); /* cameraSetForward + origin/dof/focus, scene.cpp:127-130 */
 /* the Camera struct verbatim (camera.h:5-18) after the UI rotated it (camera.cpp:70-135): no re-orthonormalisation */
 int ptb_set_camera_basis(ptb_ctx *ctx, const float origin[3], const float forward[3], const float right[3], const float up[3],

@@ -16,6 +16,11 @@
  *   int32_t  mat[n_tris]                                       (Triangle::materialIdx)
  *   ptbs_object   objects[n_objects]
  *   ptbs_material materials[n_materials]
+ * version 2 only (n_textures = header.reserved[0] > 0; a version-1 file simply ends here):
+ *   int32_t  mat_tex[n_materials][2]   albedo texture, normal map of each material (-1 = none)
+ *                                      (pbrProbs::texture / ::normal, src/shader/shader.h:14-24)
+ *   n_textures x { ptbs_texture_hdr; float rgba[height][width][4] }   Texture::data as loadTexture leaves it
+ *                                      (byte / 255.0f per channel, src/types/texture.cpp:33-50)
  */
 #ifndef PTBS_FORMAT_H
 #define PTBS_FORMAT_H
@@ -27,6 +32,7 @@ extern "C" {
 
 #define PTBS_MAGIC 0x53425450u /* "PTBS" */
 #define PTBS_VERSION 1u
+#define PTBS_VERSION_TEXTURES 2u
 #define PTBS_MAX_OBJECT_MATERIALS 28
 
 typedef struct ptbs_header {
@@ -35,7 +41,7 @@ typedef struct ptbs_header {
     uint32_t n_tris;
     uint32_t n_objects;
     uint32_t n_materials;
-    uint32_t reserved[3];
+    uint32_t reserved[3]; /* [0] = n_textures (version 2) */
     /* camera: src/scene/SceneFile.h:26-31, applied at src/scene/scene.cpp:127-130 */
     float cam_pos[3];
     float cam_forward[3]; /* as written in the scene file (not yet normalised) */
@@ -65,6 +71,12 @@ typedef struct ptbs_material {
     float w_refraction;
     char name[64];
 } ptbs_material;
+
+/* src/types/texture.h:7-11 */
+typedef struct ptbs_texture_hdr {
+    int32_t width;
+    int32_t height;
+} ptbs_texture_hdr;
 
 #ifdef __cplusplus
 }

@@ -167,9 +167,26 @@ static void loadFromPtbs(const Opts &o, ptbs_header &hdr) {
               fread(uv.data(), 4, n * 6, f) == n * 6 && fread(mat.data(), 4, n, f) == n &&
               fread(objs.data(), sizeof(ptbs_object), objs.size(), f) == objs.size() &&
               fread(mats.data(), sizeof(ptbs_material), mats.size(), f) == mats.size();
+    // version 2: textures exactly as loadTexture (src/types/texture.cpp:33-50) would have left them in Texture::data
+    std::vector<int32_t> matTex(2 * mats.size(), -1);
+    std::vector<Texture> textures;
+    if (ok && hdr.version >= PTBS_VERSION_TEXTURES && hdr.reserved[0] > 0) {
+        ok = fread(matTex.data(), 4, matTex.size(), f) == matTex.size();
+        for (uint32_t k = 0; ok && k < hdr.reserved[0]; ++k) {
+            ptbs_texture_hdr th;
+            ok = fread(&th, sizeof th, 1, f) == 1 && th.width > 0 && th.height > 0;
+            if (!ok) break;
+            Texture t = createTexture(th.width, th.height);
+            std::vector<float> px((size_t)th.width * th.height * 4);
+            ok = fread(px.data(), 4, px.size(), f) == px.size();
+            for (size_t i = 0; ok && i < t.data.size(); ++i) t.data[i] = {px[4 * i], px[4 * i + 1], px[4 * i + 2], px[4 * i + 3]};
+            textures.push_back(t);
+        }
+    }
     fclose(f);
     if (!ok) die("short ptbs");
-    for (auto &m : mats) {
+    for (size_t mi = 0; mi < mats.size(); ++mi) {
+        auto &m = mats[mi];
         Material mm{.pbr = {.albedo = {m.albedo[0], m.albedo[1], m.albedo[2]},
                             .refractiveIdx1 = m.ior1,
                             .refractiveIdx2 = m.ior2,
@@ -177,6 +194,8 @@ static void loadFromPtbs(const Opts &o, ptbs_header &hdr) {
                             .roughness = m.roughness},
                     .weights = {.lambert = m.w_lambert, .reflection = m.w_reflection, .refraction = m.w_refraction},
                     .name = std::string(m.name)};
+        if (matTex[2 * mi] >= 0 && (size_t)matTex[2 * mi] < textures.size()) mm.pbr.texture = textures[matTex[2 * mi]];
+        if (matTex[2 * mi + 1] >= 0 && (size_t)matTex[2 * mi + 1] < textures.size()) mm.pbr.normal = textures[matTex[2 * mi + 1]];
         addMaterial(mm);
     }
     auto &tris = getTris();

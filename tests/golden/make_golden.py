@@ -18,7 +18,12 @@ build container (the reference sources do not travel); the outputs do:
         t_sha256                      digest of the hit distances (bit pattern)
         two_plane_equal               1 if the reference's TWO_PLANE run gave identical t and ids
 
-    python tests/golden/make_golden.py [--lucy [--lucy-two-plane]]
+  tests/golden/cornel_textured_ref_48.npz   (--textured) the reference's texture branches (shader.cpp:52-66,251-258,
+                                      texture.cpp:22-32) on scenes.textured_cornell: 64x48, 3 spp, BVH and TWO_PLANE
+        img_m{mode}_nee{0,1}_d{0,4}_l{0,1}   fp32 image (l = the emissive cube carries a texture too)
+        scene_sha256_l{0,1}           digest of the generated textures + uv (the generator is bit-reproducible)
+
+    python tests/golden/make_golden.py [--lucy [--lucy-two-plane]] [--textured]
 """
 import os
 import sys
@@ -58,9 +63,40 @@ def lucy():
     print("wrote lucy_standin_ref_1080p.npz", {k: v for k, v in out.items() if k != "tri"})
 
 
+def textured_scene_digest(scene):
+    import hashlib
+    h = hashlib.sha256(scene["uv"].tobytes())
+    for t in scene["textures"]:
+        h.update(np.ascontiguousarray(t, np.float32).tobytes())
+    return h.hexdigest()
+
+
+def textured():
+    import tempfile
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    import ptb_b200
+    sc = ptb_b200.scenes
+    room = sc.read_ptbs(os.path.join(HERE, "cornel.ptbs"))
+    out = {}
+    with tempfile.TemporaryDirectory() as d:
+        for lt in (0, 1):
+            scene = sc.textured_cornell(room, light_texture=bool(lt))
+            ptbs = os.path.join(d, f"tex{lt}.ptbs")
+            sc.write_ptbs(ptbs, scene)
+            out[f"scene_sha256_l{lt}"] = textured_scene_digest(scene)
+            for mode in (1, 2):
+                for nee, depth in ((0, 0), (1, 0), (1, 4)):
+                    img, rec, _ = ptref_render(ptbs, 64, 48, mode, 3, depth, nee)
+                    out[f"img_m{mode}_nee{nee}_d{depth}_l{lt}"] = img
+    np.savez_compressed(os.path.join(HERE, "cornel_textured_ref_48.npz"), **out)
+    print("wrote cornel_textured_ref_48.npz", len(out), "entries")
+
+
 def main():
     if "--lucy" in sys.argv:
         return lucy()
+    if "--textured" in sys.argv:
+        return textured()
     if not os.path.isfile(PTREF):
         raise SystemExit("oracle/_ref/ptref missing: make -C oracle ref (needs /root/reference)")
     ptbs = os.path.join(HERE, "cornel.ptbs")

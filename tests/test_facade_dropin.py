@@ -26,3 +26,17 @@ def test_reference_host_code_renders_through_the_facade(cornel_ptbs, ptb, mode, 
     assert rec["paths"] == W * H * spp
     if nee == 0:  # with NEE the GPU count also holds the shadow rays, which the path-ray statistic of the oracle does not
         assert rec["rays_unique"] == st["rays_unique"], "GPU traversal count != the reference's unique-ray count"
+
+
+@pytest.mark.skipif(not have_facade(), reason="oracle/_ref/ptfacade not built (needs the reference sources at build time)")
+def test_facade_forwards_the_references_textures(cornel_ptbs, ptb, tmp_path):
+    """The reference-side loader fills Material::pbr.texture / .normal (here from the v2 container); the facade hands
+    Texture::data to ptb_upload_textures, and the frame equals the reference's own golden image of the textured scene."""
+    import os
+    sc = ptb.scenes
+    path = str(tmp_path / "tex.ptbs")
+    sc.write_ptbs(path, sc.textured_cornell(sc.read_ptbs(cornel_ptbs), light_texture=True))
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cornel_textured_ref_48.npz"))
+    img, rec = ptfacade_render(path, 64, 48, MODE_BVH, 3, 4, 1)
+    n = int((img.view(np.uint32) != gold["img_m1_nee1_d4_l1"].view(np.uint32)).any(axis=-1).sum())
+    assert n <= 1, f"{n} pixels differ from the reference's textured frame"

@@ -92,3 +92,58 @@ def test_live_against_compiled_reference(oracle, cornel_ptbs, mode):
     rimg, rec, _ = ptref_render(cornel_ptbs, W, H, mode, 3, 5, 1)
     assert (_bits(img) == _bits(rimg)).all()
     assert st["tri_tests"] == rec["tri_tests"] and st["as_tests"] == rec["as_tests"]
+
+
+# ---- texture branches (shader.cpp:52-66 albedo texture + alpha, :251-258 normal map; texture.cpp:22-32) ------------
+TEX_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cornel_textured_ref_48.npz")
+
+
+@pytest.fixture(scope="module")
+def textured_scenes(cornel_ptbs, tmp_path_factory):
+    """scenes.textured_cornell with and without a texture on the emissive cube, as .ptbs v2 files; the generator must
+    reproduce the bytes the golden images were rendered from."""
+    import hashlib
+    import ptb_b200
+    sc = ptb_b200.scenes
+    gold = np.load(TEX_GOLD)
+    d = tmp_path_factory.mktemp("textured")
+    paths = {}
+    for lt in (0, 1):
+        scene = sc.textured_cornell(sc.read_ptbs(cornel_ptbs), light_texture=bool(lt))
+        h = hashlib.sha256(scene["uv"].tobytes())
+        for t in scene["textures"]:
+            h.update(np.ascontiguousarray(t, np.float32).tobytes())
+        assert h.hexdigest() == str(gold[f"scene_sha256_l{lt}"]), "textured scene generator is not bit-reproducible here"
+        paths[lt] = str(d / f"tex{lt}.ptbs")
+        sc.write_ptbs(paths[lt], scene)
+        back = sc.read_ptbs(paths[lt])
+        assert all((a == b).all() for a, b in zip(back["textures"], scene["textures"]))
+        assert [(m.get("tex", -1), m.get("nrm", -1)) for m in back["materials"]] == [(m.get("tex", -1), m.get("nrm", -1)) for m in scene["materials"]]
+    return paths, gold
+
+
+@pytest.mark.parametrize("lt", [0, 1])
+@pytest.mark.parametrize("mode", [MODE_BVH, MODE_TWO_PLANE])
+def test_textured_images_match_reference_golden(textured_scenes, mode, lt):
+    paths, gold = textured_scenes
+    o = Oracle(paths[lt])
+    o.build(grid=True)
+    for nee, depth in ((0, 0), (1, 0), (1, 4)):
+        o.configure(64, 48, mode, nee=nee, max_depth=depth)
+        img, _, _, _ = o.render(3)
+        assert (_bits(img) == _bits(gold[f"img_m{mode}_nee{nee}_d{depth}_l{lt}"])).all(), f"mode {mode} nee {nee} depth {depth} light texture {lt}"
+    o.close()
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref/ptref not built (needs the reference sources)")
+def test_textured_live_against_compiled_reference(textured_scenes):
+    paths, _ = textured_scenes
+    W, H = 80, 56
+    o = Oracle(paths[1])
+    o.build()
+    o.configure(W, H, MODE_BVH, nee=1, max_depth=6)
+    img, _, _, st = o.render(2)
+    o.close()
+    rimg, rec, _ = ptref_render(paths[1], W, H, MODE_BVH, 2, 6, 1)
+    assert (_bits(img) == _bits(rimg)).all()
+    assert st["tri_tests"] == rec["tri_tests"] and st["as_tests"] == rec["as_tests"]
