@@ -23,6 +23,9 @@ SYMBOLS = (
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
     "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
     "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh", "ptb_upload_textures",
+    "ptb_group_create", "ptb_group_destroy", "ptb_group_size", "ptb_group_ctx", "ptb_group_last_error", "ptb_group_peer_direct",
+    "ptb_group_set_params", "ptb_group_reset", "ptb_group_clear", "ptb_group_render", "ptb_group_read_image", "ptb_group_read_counters",
+    "ptb_group_last_render_ms",
 )
 
 
@@ -73,6 +76,23 @@ def load_library():
     L.ptb_upload_materials.argtypes = [vp, vp, ctypes.c_uint32]
     L.ptb_load_ptbs.argtypes = [vp, ctypes.c_char_p]
     L.ptb_upload_textures.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32]
+    L.ptb_group_create.argtypes = [vp, ci, ctypes.POINTER(vp)]
+    L.ptb_group_destroy.argtypes = [vp]
+    L.ptb_group_destroy.restype = None
+    L.ptb_group_size.argtypes = [vp]
+    L.ptb_group_ctx.argtypes = [vp, ci]
+    L.ptb_group_ctx.restype = vp
+    L.ptb_group_last_error.argtypes = [vp]
+    L.ptb_group_last_error.restype = ctypes.c_char_p
+    L.ptb_group_peer_direct.argtypes = [vp, ci]
+    L.ptb_group_set_params.argtypes = [vp, ctypes.POINTER(Params)]
+    for f in ("ptb_group_reset", "ptb_group_clear"):
+        getattr(L, f).argtypes = [vp]
+    L.ptb_group_render.argtypes = [vp, ci]
+    L.ptb_group_read_image.argtypes = [vp, vp]
+    L.ptb_group_read_counters.argtypes = [vp, vp]
+    L.ptb_group_last_render_ms.argtypes = [vp]
+    L.ptb_group_last_render_ms.restype = ctypes.c_double
     L.ptb_set_camera.argtypes = [vp, ctypes.POINTER(Camera)]
     L.ptb_build_bvh.argtypes = [vp]
     L.ptb_build_bvh_gpu.argtypes = [vp]
@@ -126,12 +146,16 @@ class PathTracer:
     """One context on one GPU.  Mirrors the reference's call sequence (src/main.cpp:91-125):
     settings -> load scene -> build structures -> initTracer -> trace."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, _borrowed=None):
         self.L = load_library()
-        h = ctypes.c_void_p()
-        rc = self.L.ptb_create(device, ctypes.byref(h))
-        if rc != 0:
-            raise PtbError(f"ptb_create: {self.L.ptb_last_error(None).decode()} (rc {rc})")
+        self._owned = _borrowed is None
+        if _borrowed is not None:  # a member of a PathTracerGroup: the group owns the context
+            h = ctypes.c_void_p(_borrowed)
+        else:
+            h = ctypes.c_void_p()
+            rc = self.L.ptb_create(device, ctypes.byref(h))
+            if rc != 0:
+                raise PtbError(f"ptb_create: {self.L.ptb_last_error(None).decode()} (rc {rc})")
         self.h = h
         self.device = device
         self.params = Params(reference_quirks=1, world=1, tile_w=32, tile_h=8, mode=MODE_BVH)
@@ -142,7 +166,8 @@ class PathTracer:
 
     def close(self):
         if getattr(self, "h", None):
-            self.L.ptb_destroy(self.h)
+            if self._owned:
+                self.L.ptb_destroy(self.h)
             self.h = None
 
     def __del__(self):
@@ -329,3 +354,73 @@ class PathTracer:
 
     def image_device_ptr(self):
         return int(self.L.ptb_image_device_ptr(self.h) or 0)
+
+
+class PathTracerGroup:
+    """ptb_group_*: one context per listed device behind one host thread; the frame is tile-sharded over the members
+    and gathered on member 0 (bit-identical to the 1-GPU frame).  `members[i]` is a PathTracer view of member i for
+    the per-member calls (uploads, structure builds); `each(fn)` applies one to all."""
+
+    def __init__(self, devices):
+        self.L = load_library()
+        devs = (ctypes.c_int * len(devices))(*devices)
+        g = ctypes.c_void_p()
+        rc = self.L.ptb_group_create(ctypes.cast(devs, ctypes.c_void_p), len(devices), ctypes.byref(g))
+        if rc != 0:
+            raise PtbError(f"ptb_group_create: {self.L.ptb_group_last_error(None).decode()} (rc {rc})")
+        self.g = g
+        self.members = [PathTracer(d, _borrowed=self.L.ptb_group_ctx(g, i)) for i, d in enumerate(devices)]
+        self.params = Params(reference_quirks=1, world=len(devices), tile_w=32, tile_h=8, mode=MODE_BVH)
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise PtbError(f"{what}: {self.L.ptb_group_last_error(self.g).decode()} (rc {rc})")
+
+    def close(self):
+        if getattr(self, "g", None):
+            for m in self.members:
+                m.h = None
+            self.L.ptb_group_destroy(self.g)
+            self.g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def each(self, fn):
+        return [fn(m) for m in self.members]
+
+    def peer_direct(self):
+        return [bool(self.L.ptb_group_peer_direct(self.g, i)) for i in range(len(self.members))]
+
+    def set_params(self, **kw):
+        for k, v in kw.items():
+            if not hasattr(self.params, k):
+                raise AttributeError(k)
+            setattr(self.params, k, int(v))
+        self._ck(self.L.ptb_group_set_params(self.g, ctypes.byref(self.params)), "ptb_group_set_params")
+        for i, m in enumerate(self.members):  # keep the member views' idea of the frame size in step
+            ctypes.memmove(ctypes.byref(m.params), ctypes.byref(self.params), ctypes.sizeof(Params))
+            m.params.rank, m.params.world = i, len(self.members)
+
+    def reset(self):
+        self._ck(self.L.ptb_group_reset(self.g), "ptb_group_reset")
+
+    def clear(self):
+        self._ck(self.L.ptb_group_clear(self.g), "ptb_group_clear")
+
+    def render(self, add_samples):
+        self._ck(self.L.ptb_group_render(self.g, add_samples), "ptb_group_render")
+        return float(self.L.ptb_group_last_render_ms(self.g))
+
+    def read_image(self):
+        img = np.empty((self.params.height, self.params.width, 4), np.float32)
+        self._ck(self.L.ptb_group_read_image(self.g, _ptr(img)), "ptb_group_read_image")
+        return img
+
+    def counters(self):
+        c = np.zeros(8, np.uint64)
+        self._ck(self.L.ptb_group_read_counters(self.g, _ptr(c)), "ptb_group_read_counters")
+        return dict(zip(COUNTER_NAMES, (int(v) for v in c)))

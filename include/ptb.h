@@ -179,6 +179,28 @@ void *ptb_stream(ptb_ctx *ctx); /* the cudaStream_t every launch and copy of thi
 int ptb_set_profiling(ptb_ctx *ctx, int on);
 int ptb_read_stage_ms(ptb_ctx *ctx, double ms[2], uint64_t launches[2]);
 
+/* ---- the GPUs of one box behind one host thread -------------------------------------------------
+ * The reference spreads the frame over 16 std::threads with a 4x4 pixel interleave (tracer.cpp:228-231); a group
+ * spreads it over n devices with the tile rule of ptb_params (tile (tx,ty) -> member (ty*tiles_x + tx) % n), scene and
+ * structures replicated per device.  Scene uploads and structure builds are per member (ptb_group_ctx); the calls
+ * below act on all members.  ptb_group_render enqueues the render on every device before it waits, so the devices run
+ * concurrently; ptb_group_read_image gathers each pixel from its owner's HBM on member 0 (peer loads over NVLink where
+ * the devices can map each other, a staged peer copy otherwise) — the frame is bit-identical to the 1-GPU frame. */
+typedef struct ptb_group ptb_group;
+int ptb_group_create(const int *devices, int n_devices, ptb_group **out); /* a device may be listed twice (tests on one GPU) */
+void ptb_group_destroy(ptb_group *g);
+int ptb_group_size(const ptb_group *g);
+ptb_ctx *ptb_group_ctx(ptb_group *g, int rank);     /* owned by the group */
+const char *ptb_group_last_error(const ptb_group *g);
+int ptb_group_peer_direct(const ptb_group *g, int rank); /* 1: member 0 reads this member's frame in place */
+int ptb_group_set_params(ptb_group *g, const ptb_params *p); /* rank / world filled in per member; tile 32x8 if p leaves it 0 */
+int ptb_group_reset(ptb_group *g);                  /* initTracer on every member */
+int ptb_group_clear(ptb_group *g);                  /* reset() on every member */
+int ptb_group_render(ptb_group *g, int add_samples); /* trace(true): all members concurrently */
+int ptb_group_read_image(ptb_group *g, float *rgba); /* the whole frame, row-major y*W+x */
+int ptb_group_read_counters(ptb_group *g, uint64_t out[PTB_CNT__N]); /* summed over the members */
+double ptb_group_last_render_ms(const ptb_group *g); /* max over the members (device time) */
+
 #ifdef __cplusplus
 }
 #endif
