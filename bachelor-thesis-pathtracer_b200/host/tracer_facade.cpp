@@ -52,8 +52,9 @@ std::mutex mtx; // guards reinitTracer like tracer.cpp:162-173
 bool reinitTracer = true;
 bool clearPending = false, reseedPending = true;
 
-ptb_ctx *ctx = nullptr;
-int deviceIdx = 0;
+ptb_group *grp = nullptr;  // one context per device (ptbFacadeSetDevices), tile-sharded; a single device by default
+ptb_ctx *ctx = nullptr;    // member 0 (error text, structure sizes)
+std::vector<int> deviceList{0};
 size_t uploadedTris = (size_t)-1;
 unsigned gridGs = 10, gridOs = 5, gridM = 40, beamGs = 10, beamM = 40; // main.cpp:42-44 defaults
 bool gridBuilt = false, beamBuilt = false;
@@ -69,10 +70,29 @@ bool ok(int rc, const char *what) {
     fprintf(stderr, "ptb facade: %s failed: %s\n", what, ptb_last_error(ctx)); // the reference prints and carries on
     return false;
 }
+bool gok(int rc, const char *what) { // calls on the whole group
+    if (rc == 0) return true;
+    fprintf(stderr, "ptb facade: %s failed: %s\n", what, ptb_group_last_error(grp));
+    return false;
+}
+// the same per-context call on every member (scene and structures are replicated in each GPU's HBM)
+template <typename F>
+bool all(F f, const char *what) {
+    ptb_ctx *first = ctx;
+    bool good = true;
+    for (int i = 0; good && i < ptb_group_size(grp); ++i) {
+        ctx = ptb_group_ctx(grp, i); // ok() reports this member's error text
+        good = ok(f(ctx), what);
+    }
+    ctx = first;
+    return good;
+}
 
 bool ensureContext() {
-    if (ctx) return true;
-    return ok(ptb_create(deviceIdx, &ctx), "ptb_create");
+    if (grp) return true;
+    if (!gok(ptb_group_create(deviceList.data(), (int)deviceList.size(), &grp), "ptb_group_create")) return false;
+    ctx = ptb_group_ctx(grp, 0);
+    return true;
 }
 
 bool uploadMaterials() {
@@ -91,7 +111,7 @@ bool uploadMaterials() {
         pm[i].w_refraction = m.weights.refraction;
         strncpy(pm[i].name, m.name.c_str(), sizeof pm[i].name - 1);
     }
-    return ok(ptb_upload_materials(ctx, pm.data(), (uint32_t)pm.size()), "ptb_upload_materials");
+    return all([&](ptb_ctx *c) { return ptb_upload_materials(c, pm.data(), (uint32_t)pm.size()); }, "ptb_upload_materials");
 }
 
 // Once per scene upload (the texel pools are rebuilt and gamma-expanded by the library); later material edits go
@@ -113,7 +133,7 @@ bool uploadTextures() {
     }
     if (tex.empty() && !texturesUploaded) return true;
     texturesUploaded = !tex.empty();
-    return ok(ptb_upload_textures(ctx, tex.data(), (uint32_t)tex.size(), bind.data(), (uint32_t)mats.size()), "ptb_upload_textures");
+    return all([&](ptb_ctx *c) { return ptb_upload_textures(c, tex.data(), (uint32_t)tex.size(), bind.data(), (uint32_t)mats.size()); }, "ptb_upload_textures");
 }
 
 bool uploadObjects() {
@@ -129,7 +149,7 @@ bool uploadObjects() {
         for (uint32_t k = 0; k < po[i].n_materials; ++k) po[i].materials[k] = o.materials[k];
         strncpy(po[i].name, o.name.c_str(), sizeof po[i].name - 1);
     }
-    return ok(ptb_upload_objects(ctx, po.data(), (uint32_t)po.size()), "ptb_upload_objects");
+    return all([&](ptb_ctx *c) { return ptb_upload_objects(c, po.data(), (uint32_t)po.size()); }, "ptb_upload_objects");
 }
 
 bool uploadReferenceTree();
@@ -152,13 +172,13 @@ bool uploadScene() {
         }
         mat[i] = t.materialIdx;
     }
-    if (!ok(ptb_upload_triangles(ctx, pos.data(), nrm.data(), uv.data(), mat.data(), n), "ptb_upload_triangles")) return false;
+    if (!all([&](ptb_ctx *c) { return ptb_upload_triangles(c, pos.data(), nrm.data(), uv.data(), mat.data(), n); }, "ptb_upload_triangles")) return false;
     if (!uploadMaterials() || !uploadTextures() || !uploadObjects()) return false;
-    if (!ok(ptb_build_bvh(ctx), "ptb_build_bvh")) return false; // constructBVH, scene.cpp:113-120
+    if (!all([&](ptb_ctx *c) { return ptb_build_bvh(c); }, "ptb_build_bvh")) return false; // constructBVH, scene.cpp:113-120
     gridBuilt = beamBuilt = false;
     uploadedTris = n;
     if (useReferenceTree && n > 0) {
-        if (!uploadReferenceTree() || !ok(ptb_use_ref_bvh(ctx, 1), "ptb_use_ref_bvh")) return false;
+        if (!uploadReferenceTree() || !all([&](ptb_ctx *c) { return ptb_use_ref_bvh(c, 1); }, "ptb_use_ref_bvh")) return false;
     }
     return true;
 }
@@ -212,18 +232,19 @@ bool uploadReferenceTree() {
             todo.push_back(n.childRight);
         }
     }
-    return ok(ptb_upload_ref_bvh(ctx, nodes.data(), (uint32_t)nodes.size(), idx.data(), (uint32_t)idx.size(), roots.data(),
-                                 (uint32_t)roots.size(), 0),
-              "ptb_upload_ref_bvh");
+    return all([&](ptb_ctx *c) {
+        return ptb_upload_ref_bvh(c, nodes.data(), (uint32_t)nodes.size(), idx.data(), (uint32_t)idx.size(), roots.data(), (uint32_t)roots.size(), 0);
+    }, "ptb_upload_ref_bvh");
 }
 
 bool ensureStructure(int mode) {
     if (mode == TWO_PLANE && !gridBuilt) { // constructGrid, scene.cpp:123
-        if (!ok(ptb_build_subgrid(ctx, gridGs, gridOs, gridM), "ptb_build_subgrid")) return false;
+        // channels filled on each GPU (ptb_build_subgrid_gpu: same pools as the host builder, 58x faster on the Lucy stand-in)
+        if (!all([&](ptb_ctx *c) { return ptb_build_subgrid_gpu(c, gridGs, gridOs, gridM); }, "ptb_build_subgrid_gpu")) return false;
         gridBuilt = true;
     }
     if (mode == SUB_BEAMS && !beamBuilt) { // buildGridsWithSubBeams (commented out at scene.cpp:125)
-        if (!ok(ptb_build_subbeams(ctx, beamGs, beamM), "ptb_build_subbeams")) return false;
+        if (!all([&](ptb_ctx *c) { return ptb_build_subbeams(c, beamGs, beamM); }, "ptb_build_subbeams")) return false;
         beamBuilt = true;
     }
     return true;
@@ -233,7 +254,7 @@ bool pushSettings() {
     const Camera *cam = getCamera();
     const float o[3] = {cam->origin[0], cam->origin[1], cam->origin[2]}, f[3] = {cam->forward[0], cam->forward[1], cam->forward[2]};
     const float r[3] = {cam->right[0], cam->right[1], cam->right[2]}, u[3] = {cam->up[0], cam->up[1], cam->up[2]};
-    if (!ok(ptb_set_camera_basis(ctx, o, f, r, u, cam->focus, cam->dof, cam->fovScale), "ptb_set_camera_basis")) return false;
+    if (!all([&](ptb_ctx *c) { return ptb_set_camera_basis(c, o, f, r, u, cam->focus, cam->dof, cam->fovScale); }, "ptb_set_camera_basis")) return false;
     if (!uploadMaterials() || !uploadObjects()) return false; // the UI edits materials in place (window.cpp:96-190); lights follow
     ptb_params p;
     memset(&p, 0, sizeof p);
@@ -250,13 +271,13 @@ bool pushSettings() {
     p.tile_w = 32;
     p.tile_h = 8;
     p.count_tests = 1; // getIntersectionCount / getStructureIntersectionCount are part of tracer.h
-    return ok(ptb_set_params(ctx, &p), "ptb_set_params");
+    return gok(ptb_group_set_params(grp, &p), "ptb_group_set_params"); // rank / world per member
 }
 
 void refreshMirror() {
     mirror.resize((size_t)WIDTH * HEIGHT * 4);
-    ok(ptb_read_image(ctx, mirror.data()), "ptb_read_image");
-    ptb_read_counters(ctx, counters);
+    gok(ptb_group_read_image(grp, mirror.data()), "ptb_group_read_image"); // gathered from the owners on member 0
+    ptb_group_read_counters(grp, counters);
 }
 } // namespace
 
@@ -339,9 +360,9 @@ void trace(bool testing) {
         if (uploadedTris != getTris().size() && !uploadScene()) break;
         if (!ensureStructure((int)getIntersectMode()) || !pushSettings()) break;
         if (reseed) {
-            if (!ok(ptb_reset(ctx), "ptb_reset")) break;
+            if (!gok(ptb_group_reset(grp), "ptb_group_reset")) break;
         } else if (clear) {
-            if (!ok(ptb_clear(ctx), "ptb_clear")) break;
+            if (!gok(ptb_group_clear(grp), "ptb_group_clear")) break;
         }
         // progressive batches so the window sees the image converge and a reset() is honoured quickly
         int batch = testing ? MAX_SAMPLE_COUNT : 1;
@@ -351,7 +372,7 @@ void trace(bool testing) {
                 if (reinitTracer) break; // reset() arrived: restart with the new settings
             }
             const int todo = std::min(batch, MAX_SAMPLE_COUNT - renderedSamples);
-            if (!ok(ptb_render(ctx, todo), "ptb_render")) {
+            if (!gok(ptb_group_render(grp, todo), "ptb_group_render")) { // every GPU renders its tiles concurrently
                 running = false;
                 break;
             }
@@ -381,7 +402,10 @@ void ptbFacadeUseReferenceTree(bool on) {
     useReferenceTree = on;
     uploadedTris = (size_t)-1; // next trace() uploads again, with or without the tree
 }
-void ptbFacadeSetDevice(int device) { deviceIdx = device; }
+void ptbFacadeSetDevice(int device) { deviceList.assign(1, device); }
+void ptbFacadeSetDevices(const int *devices, int n) { // before the first trace(): the frame is tile-sharded over them
+    if (devices && n > 0) deviceList.assign(devices, devices + n);
+}
 unsigned long ptbFacadeStructureBytes(int mode) { return ctx ? (unsigned long)ptb_structure_bytes(ctx, mode) : 0ul; }
-double ptbFacadeLastRenderMs() { return ctx ? ptb_last_render_ms(ctx) : 0.0; }
+double ptbFacadeLastRenderMs() { return grp ? ptb_group_last_render_ms(grp) : 0.0; }
 unsigned long ptbFacadeRaysTraced() { return (unsigned long)counters[PTB_CNT_RAYS]; }

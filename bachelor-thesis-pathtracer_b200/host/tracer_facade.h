@@ -10,6 +10,8 @@ void ptbFacadeSetMaxDepth(int depth);  // 0 = unbounded (reference behaviour); B
 // getIntersectionCount / getStructureIntersectionCount and the heat maps are the CPU tracer's numbers (slower; off by default)
 void ptbFacadeUseReferenceTree(bool on);
 void ptbFacadeSetDevice(int device);   // before the first trace(); default 0
+// several GPUs of the box behind the one trace() thread: scene replicated, frame tile-sharded (ptb_group_*), same pixels
+void ptbFacadeSetDevices(const int *devices, int n);
 unsigned long ptbFacadeStructureBytes(int mode); // device bytes of the structure (cf. getMemoryBVH / getMemory2Plane)
 double ptbFacadeLastRenderMs();        // device time of the last batch (CUDA events)
 unsigned long ptbFacadeRaysTraced();   // traversals executed on the GPU since initTracer/reset

@@ -127,7 +127,7 @@ struct Opts {
     int mode = 1;
     unsigned gs = 10, os = 5, m = 40;
     bool grid = false, beams = false;
-    int W = 512, H = 512, spp = 1, maxDepth = 0, nee = 0, threads = 0, refTree = 0;
+    int W = 512, H = 512, spp = 1, maxDepth = 0, nee = 0, threads = 0, refTree = 0, gpus = 1, sameDevice = 0;
     unsigned bgs = 10, bm = 40;
 };
 
@@ -439,6 +439,11 @@ static void cmdRender(const Opts &o, const char *out) {
     ptbFacadeSetGridSettings(o.gs, o.os, o.m);
     ptbFacadeSetGridBeamsSettings(o.bgs, o.bm);
     ptbFacadeUseReferenceTree(o.refTree != 0);
+    if (o.gpus > 1) {
+        std::vector<int> devs(o.gpus);
+        for (int i = 0; i < o.gpus; ++i) devs[i] = o.sameDevice ? 0 : i;
+        ptbFacadeSetDevices(devs.data(), o.gpus);
+    }
 #endif
     setWindowSize(o.W, o.H);
     getMaxSampleCount() = o.spp;
@@ -550,6 +555,8 @@ int main(int argc, char **argv) {
         else if (a == "--max-depth") o.maxDepth = atoi(next());
         else if (a == "--nee") o.nee = atoi(next());
         else if (a == "--ref-tree") o.refTree = atoi(next());
+        else if (a == "--gpus") o.gpus = atoi(next());               // facade flavour: tile-shard the frame over N devices
+        else if (a == "--same-device") o.sameDevice = atoi(next());  // ... all N members on device 0 (single-GPU boxes)
         else if (a == "--threads") o.threads = atoi(next());
         else if (a == "--no-count") g_countRays = false;
         else pos.push_back(a);

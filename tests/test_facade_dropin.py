@@ -40,3 +40,18 @@ def test_facade_forwards_the_references_textures(cornel_ptbs, ptb, tmp_path):
     img, rec = ptfacade_render(path, 64, 48, MODE_BVH, 3, 4, 1)
     n = int((img.view(np.uint32) != gold["img_m1_nee1_d4_l1"].view(np.uint32)).any(axis=-1).sum())
     assert n <= 1, f"{n} pixels differ from the reference's textured frame"
+
+
+@pytest.mark.skipif(not have_facade(), reason="oracle/_ref/ptfacade not built (needs the reference sources at build time)")
+@pytest.mark.parametrize("mode", [MODE_BVH, MODE_TWO_PLANE])
+def test_facade_over_several_devices_renders_the_same_frame(cornel_ptbs, ptb, mode):
+    """ptbFacadeSetDevices: the one trace() thread of the reference drives a ptb_group; the frame it serves through
+    tracerGetPixel is the single-device frame bit for bit.  With one GPU on the box the members share device 0."""
+    import torch
+    W, H, spp = 96, 64, 3
+    one, rec1 = ptfacade_render(cornel_ptbs, W, H, mode, spp, 5, 1)
+    n = torch.cuda.device_count()
+    extra = ("--gpus", n) if n > 1 else ("--gpus", 3, "--same-device", 1)
+    many, recn = ptfacade_render(cornel_ptbs, W, H, mode, spp, 5, 1, extra=extra)
+    assert (one.view(np.uint32) == many.view(np.uint32)).all()
+    assert recn["paths"] == rec1["paths"] == W * H * spp and recn["rays_unique"] == rec1["rays_unique"]
