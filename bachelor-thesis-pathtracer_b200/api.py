@@ -25,7 +25,7 @@ SYMBOLS = (
     "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh", "ptb_upload_textures",
     "ptb_group_create", "ptb_group_destroy", "ptb_group_size", "ptb_group_ctx", "ptb_group_last_error", "ptb_group_peer_direct",
     "ptb_group_set_params", "ptb_group_reset", "ptb_group_clear", "ptb_group_render", "ptb_group_read_image", "ptb_group_read_counters",
-    "ptb_group_last_render_ms",
+    "ptb_group_last_render_ms", "ptb_group_set_sharding",
 )
 
 
@@ -86,6 +86,7 @@ def load_library():
     L.ptb_group_last_error.restype = ctypes.c_char_p
     L.ptb_group_peer_direct.argtypes = [vp, ci]
     L.ptb_group_set_params.argtypes = [vp, ctypes.POINTER(Params)]
+    L.ptb_group_set_sharding.argtypes = [vp, ci]
     for f in ("ptb_group_reset", "ptb_group_clear"):
         getattr(L, f).argtypes = [vp]
     L.ptb_group_render.argtypes = [vp, ci]
@@ -391,6 +392,10 @@ class PathTracerGroup:
 
     def each(self, fn):
         return [fn(m) for m in self.members]
+
+    def set_sharding(self, samples):
+        """False: tiles (bit-identical to one GPU).  True: sample ranges from per-member seeds (statistical parity)."""
+        self._ck(self.L.ptb_group_set_sharding(self.g, 1 if samples else 0), "ptb_group_set_sharding")
 
     def peer_direct(self):
         return [bool(self.L.ptb_group_peer_direct(self.g, i)) for i in range(len(self.members))]

@@ -28,9 +28,12 @@ struct ptb_group {
     size_t stagePixels = 0;
     float4 *dGather = nullptr;     // device 0: the assembled frame
     const float4 **dPtrs = nullptr; // device 0: where to read each member's pixels from
+    float *dWeights = nullptr;     // device 0: n_i + 1 per member (PTB_SHARD_SAMPLES)
     size_t gatherPixels = 0;
     ptb_params prm{};
     bool haveParams = false;
+    int shard = PTB_SHARD_TILES;
+    std::vector<int> samples;      // PTB_SHARD_SAMPLES: samples each member has accumulated since the last reset / clear
     double lastMs = 0.0;
     std::string err;
 };
@@ -57,6 +60,23 @@ __global__ void __launch_bounds__(256) k_group_gather(const float4 *const *__res
     }
 }
 
+// PTB_SHARD_SAMPLES: member i holds the reference's running mean over its n_i samples, sum(L)/(n_i+1)
+// (tracer.cpp:147-154).  Rebuild the sums, add them, apply the same law over all samples: sum(L)/(n_total+1).
+__global__ void __launch_bounds__(256) k_group_combine(const float4 *const *__restrict__ src, const float *__restrict__ weight, int n,
+                                                        float denom /* n_total + 1 */, size_t total, float4 *__restrict__ out) {
+    for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (size_t)gridDim.x * blockDim.x) {
+        float4 acc = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+        for (int i = 0; i < n; ++i) {
+            const float4 v = src[i][p];
+            const float w = weight[i];
+            acc.x += v.x * w;
+            acc.y += v.y * w;
+            acc.z += v.z * w;
+        }
+        out[p] = make_float4(acc.x / denom, acc.y / denom, acc.z / denom, 1.0f);
+    }
+}
+
 #define GCK(call)                                                                          \
     do {                                                                                   \
         const cudaError_t e_ = (call);                                                     \
@@ -77,6 +97,8 @@ void free_gather(ptb_group *g) {
     cudaSetDevice(g->dev[0]);
     cudaFree(g->dGather);
     cudaFree((void *)g->dPtrs);
+    cudaFree(g->dWeights);
+    g->dWeights = nullptr;
     for (auto *s : g->stage) cudaFree(s);
     g->dGather = nullptr;
     g->dPtrs = nullptr;
@@ -94,6 +116,7 @@ extern "C" int ptb_group_create(const int *devices, int n_devices, ptb_group **o
     g->dev.assign(devices, devices + n_devices);
     g->direct.assign(n_devices, 0);
     g->stage.assign(n_devices, nullptr);
+    g->samples.assign(n_devices, 0);
     for (int i = 0; i < n_devices; ++i) {
         ptb_ctx *c = nullptr;
         const int r = ptb_create(devices[i], &c);
@@ -136,18 +159,37 @@ extern "C" const char *ptb_group_last_error(const ptb_group *g) { return g ? g->
 extern "C" int ptb_group_peer_direct(const ptb_group *g, int rank) { return (g && rank >= 0 && rank < (int)g->ctx.size()) ? g->direct[rank] : 0; }
 extern "C" double ptb_group_last_render_ms(const ptb_group *g) { return g ? g->lastMs : 0.0; }
 
+// How the frame is split.  TILES (default): bit-identical to the 1-GPU frame.  SAMPLES (opt-in): every member renders all
+// pixels with its share of the samples from its own seeds (ptb_params.seed_offset = rank; member 0 keeps the reference's) —
+// the same estimator with other random numbers, statistical parity only; it keeps every GPU full when 1/n of the frame
+// has fewer pixels than a GPU has lanes.  Takes effect at the next ptb_group_set_params.
+extern "C" int ptb_group_set_sharding(ptb_group *g, int shard) {
+    if (!g || (shard != PTB_SHARD_TILES && shard != PTB_SHARD_SAMPLES)) return PTB_ERR_INVALID;
+    g->shard = shard;
+    g->haveParams = false;
+    return PTB_OK;
+}
+
 extern "C" int ptb_group_set_params(ptb_group *g, const ptb_params *p) {
     if (!g || !p) return PTB_ERR_INVALID;
     ptb_params q = *p;
-    q.world = (int32_t)g->ctx.size();
+    const int n = (int)g->ctx.size();
     if (q.tile_w <= 0) q.tile_w = 32;
     if (q.tile_h <= 0) q.tile_h = 8;
-    for (size_t i = 0; i < g->ctx.size(); ++i) {
-        q.rank = (int32_t)i;
+    for (int i = 0; i < n; ++i) {
+        if (g->shard == PTB_SHARD_SAMPLES) {
+            q.world = 1;
+            q.rank = 0;
+            q.seed_offset = i;
+        } else {
+            q.world = n;
+            q.rank = i;
+        }
         const int r = ptb_set_params(g->ctx[i], &q);
         if (r) return gfail(g, r, std::string("ptb_set_params on member ") + std::to_string(i) + ": " + ptb_last_error(g->ctx[i]));
     }
     q.rank = 0;
+    q.world = n;
     g->prm = q;
     g->haveParams = true;
     return PTB_OK;
@@ -156,12 +198,14 @@ extern "C" int ptb_group_set_params(ptb_group *g, const ptb_params *p) {
 extern "C" int ptb_group_reset(ptb_group *g) {
     if (!g) return PTB_ERR_INVALID;
     GEACH(ptb_reset(c), "ptb_reset");
+    std::fill(g->samples.begin(), g->samples.end(), 0);
     return PTB_OK;
 }
 
 extern "C" int ptb_group_clear(ptb_group *g) {
     if (!g) return PTB_ERR_INVALID;
     GEACH(ptb_clear(c), "ptb_clear");
+    std::fill(g->samples.begin(), g->samples.end(), 0);
     return PTB_OK;
 }
 
@@ -169,7 +213,16 @@ extern "C" int ptb_group_clear(ptb_group *g) {
 extern "C" int ptb_group_render(ptb_group *g, int add_samples) {
     if (!g) return PTB_ERR_INVALID;
     if (!g->haveParams) return gfail(g, PTB_ERR_INVALID, "ptb_group_set_params first");
-    GEACH(ptb_render_async(c, add_samples), "ptb_render_async");
+    if (add_samples <= 0) return gfail(g, PTB_ERR_INVALID, "add_samples must be positive");
+    const int n = (int)g->ctx.size();
+    for (int i = 0; i < n; ++i) {
+        // SAMPLES: member i takes add/n samples, the first add % n members one more
+        const int mine = g->shard == PTB_SHARD_SAMPLES ? add_samples / n + (i < add_samples % n ? 1 : 0) : add_samples;
+        if (mine <= 0) continue;
+        const int r = ptb_render_async(g->ctx[i], mine);
+        if (r) return gfail(g, r, std::string("ptb_render_async on member ") + std::to_string(i) + ": " + ptb_last_error(g->ctx[i]));
+        g->samples[i] += mine;
+    }
     GEACH(ptb_sync(c), "ptb_sync");
     g->lastMs = 0.0;
     for (auto *c : g->ctx) g->lastMs = std::max(g->lastMs, ptb_last_render_ms(c));
@@ -229,7 +282,19 @@ extern "C" int ptb_group_read_image(ptb_group *g, float *rgba) {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, g->dev[0]);
     const int blocks = (int)std::min<size_t>((px + 255) / 256, (size_t)sms * 8);
-    k_group_gather<<<blocks, 256, 0, s0>>>(g->dPtrs, n, g->prm.width, g->prm.height, g->prm.tile_w, g->prm.tile_h, g->dGather);
+    if (g->shard == PTB_SHARD_SAMPLES) {
+        std::vector<float> w(n);
+        int total = 0;
+        for (int i = 0; i < n; ++i) {
+            w[i] = g->samples[i] > 0 ? (float)(g->samples[i] + 1) : 0.0f; // a member without samples holds zeros
+            total += g->samples[i];
+        }
+        if (!g->dWeights) GCK(cudaMalloc(&g->dWeights, 64 * sizeof(float)));
+        GCK(cudaMemcpyAsync(g->dWeights, w.data(), n * sizeof(float), cudaMemcpyHostToDevice, s0));
+        k_group_combine<<<blocks, 256, 0, s0>>>(g->dPtrs, g->dWeights, n, (float)(total + 1), px, g->dGather);
+    } else {
+        k_group_gather<<<blocks, 256, 0, s0>>>(g->dPtrs, n, g->prm.width, g->prm.height, g->prm.tile_w, g->prm.tile_h, g->dGather);
+    }
     GCK(cudaGetLastError());
     GCK(cudaMemcpyAsync(rgba, g->dGather, px * sizeof(float4), cudaMemcpyDeviceToHost, s0));
     GCK(cudaStreamSynchronize(s0));

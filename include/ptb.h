@@ -193,6 +193,11 @@ int ptb_group_size(const ptb_group *g);
 ptb_ctx *ptb_group_ctx(ptb_group *g, int rank);     /* owned by the group */
 const char *ptb_group_last_error(const ptb_group *g);
 int ptb_group_peer_direct(const ptb_group *g, int rank); /* 1: member 0 reads this member's frame in place */
+enum { PTB_SHARD_TILES = 0, PTB_SHARD_SAMPLES = 1 };
+/* TILES (default): bit-identical to one GPU.  SAMPLES: every member renders all pixels with its share of the samples from its
+ * own seeds (seed_offset = rank) and ptb_group_read_image re-applies the reference's sum(L)/(N+1) law (tracer.cpp:147-154)
+ * over all of them — statistical parity only; for frames with fewer pixels per GPU than a GPU has lanes. */
+int ptb_group_set_sharding(ptb_group *g, int shard);
 int ptb_group_set_params(ptb_group *g, const ptb_params *p); /* rank / world filled in per member; tile 32x8 if p leaves it 0 */
 int ptb_group_reset(ptb_group *g);                  /* initTracer on every member */
 int ptb_group_clear(ptb_group *g);                  /* reset() on every member */

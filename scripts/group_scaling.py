@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """ptb_group_* scaling inside ONE process: the Lucy stand-in at 1920x1080, 8 bounces, tile-sharded over the first
 n GPUs of the box (n = 1, 2, 4, 8 as available), gathered on member 0; every n-GPU frame must equal the 1-GPU frame
-bit for bit.  usage: group_scaling.py [spp=64].  Writes gpurun_out/group_scaling.json."""
+bit for bit; then the same with sample-range sharding (every member all pixels, spp/n samples from its own seeds:
+statistical parity, RMSE against the tile frame reported).  usage: group_scaling.py [spp=64].  Writes
+gpurun_out/group_scaling.json."""
 import json
 import os
 import sys
@@ -20,10 +22,11 @@ scene = sc.lucy_standin(sc.read_ptbs(os.path.join(ROOT, "tests", "golden", "corn
 W, H = 1920, 1080
 avail = torch.cuda.device_count()
 res, ref = [], None
-for n in (1, 2, 4, 8):
+for samples_mode, n in [(False, k) for k in (1, 2, 4, 8)] + [(True, k) for k in (2, 4, 8)]:
     if n > avail:
-        break
+        continue
     g = ptb_b200.PathTracerGroup(list(range(n)))
+    g.set_sharding(samples_mode)
 
     def prep(m):
         sc.upload_scene(m, scene)
@@ -45,7 +48,8 @@ for n in (1, 2, 4, 8):
     c = g.counters()
     if ref is None:
         ref = img
-    rec = {"gpus": n, "spp": spp, "device_ms_max": min(ms), "wall_ms": min(wall), "gather_and_d2h_ms": min(gather), "rays": c["rays"],
+    rmse = float(np.sqrt(np.mean((np.minimum(img[..., :3], 4.0) - np.minimum(ref[..., :3], 4.0)) ** 2)))
+    rec = {"gpus": n, "sharding": "samples" if samples_mode else "tiles", "rmse_vs_1gpu_frame_clamped4": rmse, "spp": spp, "device_ms_max": min(ms), "wall_ms": min(wall), "gather_and_d2h_ms": min(gather), "rays": c["rays"],
            "mrays_s_device": c["rays"] / min(ms) / 1e3, "mrays_s_wall": c["rays"] / min(wall) / 1e3, "peer_direct": g.peer_direct(),
            "identical_to_1gpu": bool((img.view(np.uint32) == ref.view(np.uint32)).all())}
     res.append(rec)

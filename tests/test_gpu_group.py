@@ -104,3 +104,31 @@ def test_group_over_real_peers(ptb, cornel_ptbs):
     print(f"{n} GPUs in one process: {t1:.2f} ms -> {tn:.2f} ms per {spp}-spp 1080p frame ({t1 / tn:.2f}x), peers read in place: {g.peer_direct()}")
     g.close()
     assert (_bits(img) == _bits(ref)).all()
+
+
+def test_group_sample_sharding_is_the_documented_combination(ptb, cornel_ptbs):
+    """PTB_SHARD_SAMPLES: member i renders all pixels with its share of the samples from seeds offset by i; the combined
+    frame is sum_i(mean_i * (n_i + 1)) / (n + 1) — checked against the same arithmetic on frames of single contexts."""
+    W, H, spp = 96, 64, 7
+    g = _group(ptb, [0, 0, 0], cornel_ptbs)
+    g.set_sharding(True)
+    g.set_params(width=W, height=H, mode=MODE_BVH, nee=1, max_depth=5)
+    g.reset()
+    g.render(4)
+    g.render(spp - 4)  # shares per call: 4 -> (2,1,1), 3 -> (1,1,1)
+    img = g.read_image()
+    assert g.counters()["paths"] == W * H * spp
+    g.close()
+    acc = np.zeros((H, W, 3), np.float32)
+    for i, n_i in enumerate((3, 2, 2)):
+        pt = ptb.PathTracer(0)
+        pt.load_ptbs(cornel_ptbs)
+        pt.build_bvh()
+        pt.set_params(width=W, height=H, mode=MODE_BVH, nee=1, max_depth=5, seed_offset=i)
+        pt.reset()
+        pt.render(n_i)
+        acc = acc + pt.read_image()[..., :3] * np.float32(n_i + 1)
+        pt.close()
+    want = acc / np.float32(spp + 1)
+    assert (_bits(img[..., :3]) == _bits(want.astype(np.float32))).all()
+    assert (img[..., 3] == 1.0).all()
