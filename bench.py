@@ -163,7 +163,7 @@ def run_reference(args):
         secs += s
     v = rays / secs / 1e6
     sample = f"{wl['W']}x{wl['H']} frame at {spp} spp per step (of {wl['spp']}), max_depth {wl['max_depth']}, NEE off"
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -372,11 +372,33 @@ def run_ours(args):
             "sample": f"same {W}x{H} frame at {args.cpu_spp} spp (of {spp}), max_depth {wl['max_depth']}, NEE off, "
                       f"{'reference trace(true), 16 std::threads' if kind == 'reference' else 'oracle port'}"}
     if rank == 0:
-        print(json.dumps(result))
+        emit(json.dumps(result))
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    """stdout carries ONE JSON line.  Libraries write there too (NCCL prints its version banner to stdout when the box
+    exports NCCL_DEBUG=VERSION), so file descriptor 1 is pointed at stderr for the run and the result line goes to the
+    original stdout through emit()."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    if _RESULT_FD is None:
+        print(line, flush=True)
+    else:
+        os.write(_RESULT_FD, (line + "\n").encode())
 
 
 def main():
@@ -406,9 +428,11 @@ def main():
                                         name=WORKLOADS[args.workload]["name"] + f" [frame overridden to {rw}x{rh}]")
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not (args.impl == "ours" and args.gpus > 1 and world == 1):  # (the re-launching parent passes the children's stdout through)
+        _claim_stdout()
     if args.impl == "reference":
         return run_reference(args)
-    world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus > 1 and world == 1:
         # convenience: re-launch under torchrun like the driver does
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
