@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """bench.py — the hot path of the thesis path tracer on N B200s, one JSON line.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cornell|lucy]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cornell|lucy|lucy256]
+                    [--structure bvh|subgrid|subbeams] [--builder host|gpu] [--shard auto|tiles|samples]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus N --steps K --warmup W
 
@@ -18,9 +19,10 @@ sum-reduced to rank 0 over NCCL inside the timed region.
   e2e        same metric through the C ABI with host buffers: every step uploads the material table
              and camera (what the reference's UI does before reset()), renders, and reads the fp32
              frame back to host memory; wall clock around synchronous calls, max over ranks
-  roofline   dominant kernel k_extend<BVH>: algorithmic bytes (48 B ray+hit,
-             32 B per box test, 36 B per triangle test, from the instrumented counters) / its
-             CUDA-event time inside the timed region, against MEASURED_PEAKS.json hbm_gbs
+  roofline   dominant kernel k_mega<BVH> (one fused launch per render: traversal + shade + accumulate;
+             k_extend_bvh with PTB_MEGA=0): algorithmic bytes (48 B ray+hit, 32 B per box
+             test, 36 B per triangle test, from the instrumented counters) / its CUDA-event time inside
+             the timed region, against MEASURED_PEAKS.json hbm_gbs
   cpu_baseline / --impl reference
              the UNMODIFIED reference compiled into oracle/_ref/ptref (trace(true), its 16
              std::threads) on the host cores, bounded sample = same frame at fewer spp
