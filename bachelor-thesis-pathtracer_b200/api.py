@@ -22,7 +22,7 @@ SYMBOLS = (
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
     "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
-    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh", "ptb_upload_textures",
+    "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_build_subbeams_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh", "ptb_upload_textures",
     "ptb_group_create", "ptb_group_destroy", "ptb_group_size", "ptb_group_ctx", "ptb_group_last_error", "ptb_group_peer_direct",
     "ptb_group_set_params", "ptb_group_reset", "ptb_group_clear", "ptb_group_render", "ptb_group_read_image", "ptb_group_read_counters",
     "ptb_group_last_render_ms", "ptb_group_set_sharding",
@@ -102,6 +102,7 @@ def load_library():
     L.ptb_bvh_depth.argtypes = [vp]
     L.ptb_build_subgrid.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_build_subbeams.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32]
+    L.ptb_build_subbeams_gpu.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32]
     L.ptb_upload_ref_bvh.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, ctypes.c_uint32, ctypes.c_int32]
     L.ptb_use_ref_bvh.argtypes = [vp, ci]
     L.ptb_build_subgrid_gpu.argtypes = [vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
@@ -250,9 +251,13 @@ class PathTracer:
     def structure_digest(self, mode):
         return int(self.L.ptb_structure_digest(self.h, mode))
 
-    def build_subbeams(self, gs=10, m=40, max_depth=None):
+    def build_subbeams(self, gs=10, m=40, max_depth=None, gpu=False):
+        """gpu=True: the level-synchronous builder on the device (ptb_build_subbeams_gpu), returns (wall ms, device ms)"""
         if max_depth is not None:
             self._ck(self.L.ptb_set_build_limits(self.h, max_depth), "ptb_set_build_limits")
+        if gpu:
+            self._ck(self.L.ptb_build_subbeams_gpu(self.h, gs, m), "ptb_build_subbeams_gpu")
+            return float(self.L.ptb_last_build_ms(self.h)), float(self.L.ptb_last_build_device_ms(self.h))
         self._ck(self.L.ptb_build_subbeams(self.h, gs, m), "ptb_build_subbeams")
 
     def structure_bytes(self, mode):

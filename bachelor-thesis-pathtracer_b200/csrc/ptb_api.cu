@@ -15,6 +15,7 @@
 #include "ptb.h"
 #include "ptb_bvh_build.h"
 #include "ptb_grid_build.h"
+#include "ptb_beam_gpu.h"
 #include "ptb_grid_gpu.h"
 #include "ptb_lbvh.h"
 #include "ptb_kernels.cuh"
@@ -111,6 +112,7 @@ struct ptb_ctx {
     double lastBuildDeviceMs = 0.0; // device part of the last *_gpu build (CUDA events)
     std::vector<uint32_t> triOfId; // reference id -> leaf position
     uint64_t gridBytes = 0, beamBytes = 0;
+    uint64_t beamCounts[3] = {0, 0, 0}; // beams, leaf entries, root-table entries per axis (ptb_structure_digest)
     uint64_t gridCounts[3] = {0, 0, 0}; // grids, LUT cells, index entries (ptb_structure_digest)
 
     // device scene
@@ -1612,6 +1614,17 @@ extern "C" uint64_t ptb_structure_digest(ptb_ctx *c, int mode) {
             return 0;
         return h;
     }
+    if (mode == PTB_MODE_SUB_BEAMS && c->beamBuilt) {
+        if (!eat(c->dBeam, c->beamCounts[0] * sizeof(BeamRec)) || !eat(c->dBeamIdx, c->beamCounts[1] * sizeof(uint32_t))) return 0;
+        for (int k = 0; k < 3; ++k)
+            if (!eat(c->dBeamRoot[k], c->beamCounts[2] * sizeof(uint32_t))) return 0;
+        for (const void *host : {(const void *)c->S.beam_gmin, (const void *)c->S.beam_gmax}) // the planes the records refer to
+            for (size_t i = 0; i < sizeof c->S.beam_gmin; ++i) {
+                h ^= ((const unsigned char *)host)[i];
+                h *= 1099511628211ull;
+            }
+        return h;
+    }
     return 0;
 }
 extern "C" double ptb_last_build_device_ms(const ptb_ctx *c) { return c ? c->lastBuildDeviceMs : 0.0; }
@@ -1649,6 +1662,54 @@ extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
     c->S.beam_idx = c->dBeamIdx;
     c->S.beam_grid_size = R.grid_size;
     c->S.n_beams = (uint32_t)R.beams.size();
+    c->beamCounts[0] = R.beams.size(); c->beamCounts[1] = R.idx.size(); c->beamCounts[2] = R.root[0].size();
     c->beamBuilt = true;
+    return PTB_OK;
+}
+
+// buildGridsWithSubBeams on the device (ptb_beam_gpu.cu): one data-parallel step per tree depth instead of the host's
+// depth-first recursion; same pools, byte for byte (ptb_structure_digest, tests/test_gpu_subbeam_build.py).
+extern "C" int ptb_build_subbeams_gpu(ptb_ctx *c, uint32_t gs, uint32_t m) {
+    GUARD(c);
+    SETTLE(c);
+    if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (it lays out the triangles)");
+    if (gs < 1 || gs > 64) return fail(c, PTB_ERR_INVALID, "grid size must be 1..64");
+    const auto t0 = std::chrono::steady_clock::now();
+    devFree(c->dBeam); devFree(c->dBeamIdx);
+    for (int k = 0; k < 3; ++k) devFree(c->dBeamRoot[k]);
+    c->beamBuilt = false;
+    SubbeamDev D;
+    std::string msg;
+    const cudaError_t e = subbeams_build_gpu(c->dVtx, c->dIdOfTri, c->mat.size(), c->bvh.lo, c->bvh.hi, gs, m, c->beamMaxDepth, c->stream, D, msg);
+    if (e != cudaSuccess) {
+        if (e != cudaErrorInvalidValue) c->poisoned = true;
+        return fail(c, e == cudaErrorInvalidValue ? PTB_ERR_INVALID : PTB_ERR_CUDA,
+                    e == cudaErrorInvalidValue ? msg + ": lower beam_max_depth (ptb_set_build_limits) or the grid size" : msg);
+    }
+    c->dBeam = D.beams;
+    c->dBeamIdx = D.idx;
+    const size_t cells = (size_t)gs * gs * gs * gs;
+    std::vector<uint32_t> ids(cells);
+    c->beamBytes = D.n_beams * sizeof(BeamRec) + D.n_idx * sizeof(uint32_t) + 3 * cells * sizeof(uint32_t);
+    for (int k = 0; k < 3; ++k) {
+        for (size_t i = 0; i < cells; ++i) ids[i] = (uint32_t)(k * cells + i); // root beams live at [axis * cells + cell]
+        CK(cudaMalloc(&c->dBeamRoot[k], cells * sizeof(uint32_t)));
+        CK(cudaMemcpy(c->dBeamRoot[k], ids.data(), cells * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        c->S.beam_root[k] = c->dBeamRoot[k];
+        for (int j = 0; j < 3; ++j) {
+            c->S.beam_gmin[k][j] = D.gmin[k][j];
+            c->S.beam_gmax[k][j] = D.gmax[k][j];
+        }
+        c->S.beam_amin[k] = D.amin[k];
+        c->S.beam_amax[k] = D.amax[k];
+    }
+    c->S.beam = reinterpret_cast<const float4 *>(c->dBeam);
+    c->S.beam_idx = c->dBeamIdx;
+    c->S.beam_grid_size = gs;
+    c->S.n_beams = (uint32_t)D.n_beams;
+    c->beamCounts[0] = D.n_beams; c->beamCounts[1] = D.n_idx; c->beamCounts[2] = cells;
+    c->beamBuilt = true;
+    c->lastBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->lastBuildDeviceMs = D.ms;
     return PTB_OK;
 }

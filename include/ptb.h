@@ -138,10 +138,16 @@ int ptb_build_subgrid(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m); /* se
  * as ptb_build_subgrid byte for byte (both evaluate csrc/ptb_sat.h). */
 int ptb_build_subgrid_gpu(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m);
 double ptb_last_build_device_ms(const ptb_ctx *ctx); /* device part (CUDA events) of the last ptb_build_*_gpu call */
-/* FNV-1a over a structure's device pools (mode BVH: nodes + triangle arrays; TWO_PLANE: headers + LUT + indices); 0 if
+/* FNV-1a over a structure's device pools (mode BVH: nodes + triangle arrays; TWO_PLANE: headers + LUT + indices;
+ * SUB_BEAMS: beam records + leaf slices + root tables + planes); 0 if
  * it is not built.  For checking that two builders agree without exposing the layouts. */
 uint64_t ptb_structure_digest(ptb_ctx *ctx, int mode);
 int ptb_build_subbeams(ptb_ctx *ctx, uint32_t gs, uint32_t m);          /* setGridBeamsSettings + buildGridsWithSubBeams, lightFieldGridSubBeams.h:28-29 */
+/* buildGridsWithSubBeams on the device (lightFieldGridSubBeams.cpp:185-374): all beams of one tree depth
+ * are one data-parallel step (test against the parent's list -> scan -> fill -> split into 2^4), the depth-first numbering
+ * the host builder produces is recovered from subtree sizes.  Same pools as ptb_build_subbeams byte for byte
+ * (ptb_structure_digest with mode SUB_BEAMS); the depth guard of ptb_set_build_limits applies. */
+int ptb_build_subbeams_gpu(ptb_ctx *ctx, uint32_t gs, uint32_t m);
 /* The reference's Subbeam recursion has no depth limit (lightFieldGridSubBeams.cpp:286-324) and does not
  * terminate on dense clusters; beams at `beam_max_depth` become leaves (default 12, 0 = unbounded). */
 int ptb_set_build_limits(ptb_ctx *ctx, int beam_max_depth);
