@@ -7,6 +7,7 @@
 // fires) and otherwise splits into 2^4 children.  Every beam of one depth is independent of the others, so here a whole
 // depth is one data-parallel step —
 //   count   one worker per beam: SAT tests of its channel against the parent's list      (BeamCount<false>)
+//           (depth 0, where every root tests every triangle: one worker per root and 1024 triangles, BeamRootChunks)
 //   scan    exclusive sum = the beam's slice of this level's pool
 //   fill    the accepted triangle ids, ascending like the host's lists                     (BeamCount<true>)
 //   split   leaf / inner, inner beams ranked by a scan, 16 children each                   (BeamClassify, BeamChildren)
@@ -102,6 +103,55 @@ struct BeamCount { // SAT tests of beam b's channel against its candidates (dept
             }
         }
         if (!FILL) L.cnt[b] = c;
+    }
+};
+
+template <bool FILL>
+struct BeamRootChunks { // depth 0 only: every root tests every triangle, so beam b's loop is cut into `nChunks` workers
+    BeamLevelDev L;     // of `chunk` consecutive triangles each; slot b * nChunks + c keeps the ascending order under one scan.
+    BeamGeom G;         // Worker i -> (b = i % L.n, c = i / L.n): neighbouring workers share their triangles (broadcast loads)
+    uint32_t nTris, nChunks, chunk;
+    const float *tri9;
+    const uint32_t *remap;
+    uint32_t *slotCnt;          // [L.n * nChunks + 1], the last one stays 0
+    const uint32_t *slotStart;  // its exclusive scan (FILL)
+    PTB_HD void operator()(uint32_t i) const {
+        const uint32_t b = i % L.n, c = i / L.n;
+        const int axis = (int)(L.tree[b] / G.cells);
+        float mn[4], mx[4];
+        for (int k = 0; k < 4; ++k) {
+            mn[k] = L.mn[4 * (size_t)b + k] * G.inv;
+            mx[k] = L.mx[4 * (size_t)b + k] * G.inv;
+        }
+        Channel ch;
+        make_channel(V3{G.gmin[axis][0], G.gmin[axis][1], G.gmin[axis][2]}, V3{G.gmax[axis][0], G.gmax[axis][1], G.gmax[axis][2]}, axis,
+                     mn[0], mn[1], mx[0], mx[1], mn[2], mn[3], mx[2], mx[3], ch);
+        const size_t slot = (size_t)b * nChunks + c;
+        const uint32_t k0 = c * chunk, k1 = (nTris - k0 < chunk) ? nTris : k0 + chunk;
+        uint32_t *out = FILL ? L.pool + slotStart[slot] : nullptr;
+        uint32_t n = 0;
+        for (uint32_t ti = k0; ti < k1; ++ti) {
+            const float *q = tri9 + 9 * (size_t)(remap ? remap[ti] : ti);
+            float t9[9];
+            PTB_UNROLL
+            for (int j = 0; j < 9; ++j) t9[j] = q[j];
+            if (tri_in_channel(t9, ch)) {
+                if (FILL) out[n] = ti;
+                n++;
+            }
+        }
+        if (!FILL) slotCnt[slot] = n;
+    }
+};
+
+struct BeamRootGather { // a root's list = its chunks' slots, contiguous after the scan
+    BeamLevelDev L;
+    uint32_t nChunks;
+    const uint32_t *slotStart;
+    PTB_HD void operator()(uint32_t b) const {
+        const uint32_t s = slotStart[(size_t)b * nChunks];
+        L.start[b] = s;
+        L.cnt[b] = slotStart[(size_t)(b + 1) * nChunks] - s;
     }
 };
 
@@ -227,6 +277,8 @@ struct BeamEmit { // the 48-byte record (BeamRec: mn[4], mx[4], start, end, has_
     }
 };
 
+constexpr uint32_t kBeamRootChunk = 1024; // triangles per depth-0 worker
+
 struct BeamLevelsResult {
     float *beams = nullptr;  // executor memory, 48 bytes per beam; owned by the caller (X::release)
     uint32_t *idx = nullptr;
@@ -266,13 +318,30 @@ const char *build_beam_levels(X &x, const BeamGeom &G, uint32_t nTris, const flo
         if (x.fail()) return "device error while building the beam levels";
         BeamLevelDev &L = lv[d];
         const BeamLevelDev P = d > 0 ? lv[d - 1] : BeamLevelDev();
-        x.run(L.n, BeamCount<false>{L, P, G, d, nTris, tri9, remap});
-        L.poolSize = x.sum64(L.cnt, L.n);
-        totalPool += L.poolSize; // bounds every u32 sum below (leaf entries are a subset of the level pools)
-        if (totalPool >= (1ull << 32)) return "Subbeam pools exceed 2^32 entries: lower beam_max_depth (ptb_set_build_limits) or the grid size";
-        x.scan(L.cnt, L.start, L.n);
-        L.pool = x.template alloc<uint32_t>((size_t)L.poolSize);
-        x.run(L.n, BeamCount<true>{L, P, G, d, nTris, tri9, remap});
+        // depth 0 with more than one chunk of triangles: (root, chunk) workers, see BeamRootChunks
+        uint32_t chunk = kBeamRootChunk;
+        while (d == 0 && (uint64_t)roots * ((nTris + chunk - 1) / chunk) > (1ull << 28)) chunk *= 2;
+        const uint32_t nChunks = d == 0 ? (nTris + chunk - 1) / chunk : 1;
+        if (nChunks > 1) {
+            const uint32_t slots = roots * nChunks;
+            uint32_t *slotCnt = x.template alloc<uint32_t>((size_t)slots + 1), *slotStart = x.template alloc<uint32_t>((size_t)slots + 1);
+            x.run(slots, BeamRootChunks<false>{L, G, nTris, nChunks, chunk, tri9, remap, slotCnt, slotStart});
+            L.poolSize = x.sum64(slotCnt, slots);
+            if (L.poolSize >= (1ull << 32)) return "Subbeam pools exceed 2^32 entries: lower beam_max_depth (ptb_set_build_limits) or the grid size";
+            x.scan(slotCnt, slotStart, slots + 1);
+            L.pool = x.template alloc<uint32_t>((size_t)L.poolSize);
+            x.run(slots, BeamRootChunks<true>{L, G, nTris, nChunks, chunk, tri9, remap, slotCnt, slotStart});
+            x.run(roots, BeamRootGather{L, nChunks, slotStart});
+            totalPool += L.poolSize;
+        } else {
+            x.run(L.n, BeamCount<false>{L, P, G, d, nTris, tri9, remap});
+            L.poolSize = x.sum64(L.cnt, L.n);
+            totalPool += L.poolSize; // bounds every u32 sum below (leaf entries are a subset of the level pools)
+            if (totalPool >= (1ull << 32)) return "Subbeam pools exceed 2^32 entries: lower beam_max_depth (ptb_set_build_limits) or the grid size";
+            x.scan(L.cnt, L.start, L.n);
+            L.pool = x.template alloc<uint32_t>((size_t)L.poolSize);
+            x.run(L.n, BeamCount<true>{L, P, G, d, nTris, tri9, remap});
+        }
         x.run(L.n, BeamClassify{L, maxTris, d, maxDepth});
         const uint64_t nInner = x.sum64(L.inner, L.n);
         if (nInner == 0) break;

@@ -244,7 +244,8 @@ bool ensureStructure(int mode) {
         gridBuilt = true;
     }
     if (mode == SUB_BEAMS && !beamBuilt) { // buildGridsWithSubBeams (commented out at scene.cpp:125)
-        if (!all([&](ptb_ctx *c) { return ptb_build_subbeams(c, beamGs, beamM); }, "ptb_build_subbeams")) return false;
+        // beam trees built level by level on each GPU (ptb_build_subbeams_gpu: same pools as the host's recursion)
+        if (!all([&](ptb_ctx *c) { return ptb_build_subbeams_gpu(c, beamGs, beamM); }, "ptb_build_subbeams_gpu")) return false;
         beamBuilt = true;
     }
     return true;

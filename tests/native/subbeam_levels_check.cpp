@@ -26,7 +26,7 @@ struct HostExec {
 int main() {
     int bad = 0;
     struct Case { int n; uint32_t gs, m; int depth; float spread; };
-    const Case cases[] = {{0, 3, 4, 2, 6}, {1, 2, 1, 3, 6}, {40, 2, 4, 3, 20}, {300, 3, 12, 2, 6}, {2000, 3, 40, 2, 3}, {500, 2, 8, 3, 2}};
+    const Case cases[] = {{0, 3, 4, 2, 6}, {1, 2, 1, 3, 6}, {40, 2, 4, 3, 20}, {300, 3, 12, 2, 6}, {2000, 3, 40, 2, 3}, {5000, 2, 60, 2, 2}, {500, 2, 8, 3, 2}};
     for (const Case &cs : cases) {
         const int n = cs.n;
         std::mt19937 r(n + 7); std::uniform_real_distribution<float> U(-100, 100), S(-cs.spread, cs.spread);

@@ -34,4 +34,4 @@ def test_level_synchronous_subbeam_builder_reproduces_the_host_builder(tmp_path)
     plain loops: beam records, leaf slices and their numbering equal build_subbeams' depth-first output byte for byte."""
     out = _build_and_run(tmp_path, "subbeam_levels_check")
     lines = [l for l in out.stdout.splitlines() if l.startswith("n=")]
-    assert out.returncode == 0 and len(lines) == 6 and all(l.endswith("IDENTICAL") for l in lines), out.stdout
+    assert out.returncode == 0 and len(lines) == 7 and all(l.endswith("IDENTICAL") for l in lines), out.stdout
