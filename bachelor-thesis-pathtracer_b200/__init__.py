@@ -10,4 +10,4 @@ from .api import (  # noqa: F401
     load_library,
 )
 from .build import build_native  # noqa: F401
-from . import multigpu, scenes  # noqa: F401,E402
+from . import multigpu, scenes, testing_protocol  # noqa: F401,E402
