@@ -30,10 +30,12 @@ def test_png_round_trip_and_names(tmp_path):
 def test_protocol_output_counters_and_files(ptb, cornel_ptbs, tmp_path):
     W, H, S = 160, 90, 3
     o = Oracle(cornel_ptbs)
-    o.build()
+    o.build(grid=True, gs=10, os_=5, m=40)
     nodes, idx, roots, root = o.export_bvh()
+    o.configure(W, H, MODE_TWO_PLANE, nee=0, max_depth=0)
+    grid_img, _, _, _ = o.render(S)
     o.configure(W, H, MODE_BVH, nee=0, max_depth=0)
-    _, _, _, st = o.render(S)
+    bvh_img, _, _, st = o.render(S)
     a_cnt, t_cnt = o.primary_counts()
     o.close()
     pt = ptb.PathTracer(0)
@@ -56,8 +58,17 @@ def test_protocol_output_counters_and_files(ptb, cornel_ptbs, tmp_path):
     tp = ptb.testing_protocol
     imgs = [tp.read_png(f) for r in recs for f in r["files"]]
     assert all(i.shape == (H, W, 4) and (i[..., 3] == 255).all() for i in imgs)
-    # the two structures find the same closest hits: the tone-mapped renders agree (up to the rare equal-t tie)
-    assert int((imgs[0] != imgs[3]).any(axis=-1).sum()) <= W * H // 500
+    # the renders are the CPU tracer's frames through window.cpp:511-521 (c/(1+c), gamma, clamp, *255).  The two structures'
+    # frames differ from each other in the reference as well (1524 of these pixels: the path streams diverge once a ray
+    # leaves the grid's planes differently), so each is compared with its own oracle frame; a few bytes may flip where
+    # powf rounds differently on the two sides
+    def display(img):
+        v = img[..., :3].astype(np.float32)
+        v = v / (np.float32(1) + v)
+        v = np.power(v, np.float32(0.4545))
+        return (np.minimum(v, np.float32(1)) * np.float32(255)).astype(np.uint8).reshape(H, W, 3)
+    for png, ref in ((imgs[0], bvh_img), (imgs[3], grid_img)):
+        assert int((png[..., :3] != display(ref)).any(axis=-1).sum()) <= W * H // 100
     # BVH heat maps are the reference's: grey = count / 10 below the scale, red above (tracer.cpp:136-142), then
     # the display transform without tone mapping (window.cpp:507-531)
     for img, cnt in ((imgs[1], a_cnt), (imgs[2], t_cnt)):
