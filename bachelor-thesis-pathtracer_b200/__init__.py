@@ -7,7 +7,7 @@ or through the repo-root shim `ptb_b200.py`.
 """
 from .api import (  # noqa: F401
     LIB_PATH, REF_BVH_NODE, MODE_ALL, MODE_BVH, MODE_NAMES, MODE_SUB_BEAMS, MODE_TWO_PLANE, SYMBOLS, Camera, Params, PathTracer, PathTracerGroup, PtbError,
-    load_library,
+    convert_scene_file, load_library,
 )
 from .build import build_native  # noqa: F401
 from . import multigpu, scenes, testing_protocol  # noqa: F401,E402

@@ -18,7 +18,7 @@ COUNTER_NAMES = ("rays", "paths", "tri_tests", "as_tests", "shadow_rays", "itera
 # every symbol include/ptb.h declares
 SYMBOLS = (
     "ptb_create", "ptb_destroy", "ptb_last_error", "ptb_upload_triangles", "ptb_upload_objects", "ptb_upload_materials",
-    "ptb_load_ptbs", "ptb_set_camera", "ptb_build_bvh", "ptb_build_subgrid", "ptb_build_subbeams", "ptb_structure_bytes",
+    "ptb_load_ptbs", "ptb_load_scene_file", "ptb_convert_scene_file", "ptb_set_camera", "ptb_build_bvh", "ptb_build_subgrid", "ptb_build_subbeams", "ptb_structure_bytes",
     "ptb_set_params", "ptb_reset", "ptb_render", "ptb_render_async", "ptb_sync", "ptb_primary_hits", "ptb_trace_rays",
     "ptb_trace_rays_device", "ptb_read_image", "ptb_read_state", "ptb_write_state", "ptb_read_rgba8", "ptb_read_counters",
     "ptb_image_device_ptr", "ptb_last_render_ms", "ptb_set_profiling", "ptb_read_stage_ms", "ptb_stream", "ptb_set_camera_basis", "ptb_clear", "ptb_set_build_limits",
@@ -53,6 +53,14 @@ class PtbError(RuntimeError):
     pass
 
 
+def convert_scene_file(scene_file, out_ptbs, base_dir="", ignore_textures=False):
+    """The reference's scene text (.scene + OBJ + MTL) -> .ptbs, on the host (ptb_convert_scene_file)."""
+    L = load_library()
+    err = ctypes.create_string_buffer(1024)
+    if L.ptb_convert_scene_file(os.fsencode(scene_file), os.fsencode(base_dir), os.fsencode(out_ptbs), int(bool(ignore_textures)), err, 1024):
+        raise PtbError("ptb_convert_scene_file: " + err.value.decode(errors="replace"))
+
+
 _lib = None
 
 
@@ -75,6 +83,8 @@ def load_library():
     L.ptb_upload_objects.argtypes = [vp, vp, ctypes.c_uint32]
     L.ptb_upload_materials.argtypes = [vp, vp, ctypes.c_uint32]
     L.ptb_load_ptbs.argtypes = [vp, ctypes.c_char_p]
+    L.ptb_load_scene_file.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ci]
+    L.ptb_convert_scene_file.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ci, ctypes.c_char_p, cu64]
     L.ptb_upload_textures.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32]
     L.ptb_group_create.argtypes = [vp, ci, ctypes.POINTER(vp)]
     L.ptb_group_destroy.argtypes = [vp]
@@ -181,6 +191,11 @@ class PathTracer:
     # ---- scene -------------------------------------------------------------------------------
     def load_ptbs(self, path):
         self._ck(self.L.ptb_load_ptbs(self.h, os.fsencode(path)), "ptb_load_ptbs")
+
+    def load_scene_file(self, scene_file, base_dir="", ignore_textures=False):
+        """.scene / OBJ / MTL text like the reference's loadScene + initScene + loadObject (ptb_load_scene_file)"""
+        self._ck(self.L.ptb_load_scene_file(self.h, os.fsencode(scene_file), os.fsencode(base_dir), int(bool(ignore_textures))),
+                 "ptb_load_scene_file")
 
     def upload_triangles(self, pos9, nrm9, uv6, mat):
         pos9 = np.ascontiguousarray(pos9, np.float32).reshape(-1, 9)

@@ -13,7 +13,7 @@ INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 OUT = os.path.join(_HERE, "libptb.so")
 OBJDIR = os.path.join(CSRC, "build")
 
-SOURCES = ["ptb_api.cu", "ptb_lbvh.cu", "ptb_grid_gpu.cu", "ptb_beam_gpu.cu", "ptb_group.cu", "ptb_bvh_build.cpp", "ptb_grid_build.cpp"]
+SOURCES = ["ptb_api.cu", "ptb_lbvh.cu", "ptb_grid_gpu.cu", "ptb_beam_gpu.cu", "ptb_group.cu", "ptb_bvh_build.cpp", "ptb_grid_build.cpp", "ptb_scene_loader.cpp"]
 
 # -fmad=false / -prec-div / -prec-sqrt / -ftz=false: the arithmetic contract of ptb_device.cuh
 NVCC_FLAGS = [

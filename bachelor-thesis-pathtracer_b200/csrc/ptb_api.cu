@@ -17,6 +17,7 @@
 #include "ptb_grid_build.h"
 #include "ptb_beam_gpu.h"
 #include "ptb_grid_gpu.h"
+#include "ptb_scene_loader.h"
 #include "ptb_lbvh.h"
 #include "ptb_kernels.cuh"
 #include "ptb_mega.cuh"
@@ -602,6 +603,42 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
     cam.dof = h.cam_dof;
     cam.fov_degrees = 70.0f;
     return ptb_set_camera(c, &cam);
+}
+
+// .scene / OBJ / MTL text -> the same uploads (csrc/ptb_scene_loader.cpp)
+extern "C" int ptb_load_scene_file(ptb_ctx *c, const char *scene_file, const char *base_dir, int flags) {
+    GUARD(c);
+    if (!scene_file) return fail(c, PTB_ERR_INVALID, "null scene file");
+    LoadedScene s;
+    std::string err;
+    if (!load_scene_file(scene_file, base_dir ? base_dir : "", s, err, flags)) return fail(c, PTB_ERR_IO, err);
+    int r;
+    if ((r = ptb_upload_triangles(c, s.pos9.data(), s.nrm9.data(), s.uv6.data(), s.mat.data(), s.triangles()))) return r;
+    if ((r = ptb_upload_materials(c, s.materials.data(), (uint32_t)s.materials.size()))) return r;
+    if ((r = ptb_upload_objects(c, s.objects.data(), (uint32_t)s.objects.size()))) return r;
+    ptb_camera cam{};
+    for (int k = 0; k < 3; ++k) {
+        cam.origin[k] = s.cam_pos[k];
+        cam.forward[k] = s.cam_forward[k];
+    }
+    cam.focus = s.cam_focus;
+    cam.dof = s.cam_dof;
+    cam.fov_degrees = 70.0f;
+    return ptb_set_camera(c, &cam);
+}
+
+extern "C" int ptb_convert_scene_file(const char *scene_file, const char *base_dir, const char *out_ptbs, int flags, char *err, uint64_t err_len) {
+    LoadedScene s;
+    std::string why;
+    bool ok = scene_file && out_ptbs;
+    if (!ok) why = "null path";
+    ok = ok && load_scene_file(scene_file, base_dir ? base_dir : "", s, why, flags) && write_ptbs(out_ptbs, s, why);
+    if (err && err_len) {
+        const size_t n = std::min<size_t>(why.size(), (size_t)err_len - 1);
+        memcpy(err, why.data(), n);
+        err[n] = 0;
+    }
+    return ok ? PTB_OK : PTB_ERR_IO;
 }
 
 // =============================================================================================

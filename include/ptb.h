@@ -100,6 +100,17 @@ typedef struct ptb_texture {
 } ptb_texture;
 int ptb_upload_textures(ptb_ctx *ctx, const ptb_texture *textures, uint32_t n_textures, const int32_t *material_tex2, uint32_t n_materials);
 int ptb_load_ptbs(ptb_ctx *ctx, const char *path); /* the uploads + camera from one .ptbs container (v1, or v2 with textures) */
+/* loadScene + the model / material part of initScene + loadObject (SceneFile.cpp:21-110, scene.cpp:97-110,
+ * object.cpp:35-174) without the 280-byte Triangle AoS in between: .scene / OBJ / MTL text straight into
+ * the arrays of ptb_upload_*, and the scene-file camera.  OBJ/MTL are read the way tinyobjloader 2.0.0 reads them (its
+ * number parser included), so the arrays are the reference's bit for bit; triangles and quads only.  Model paths are
+ * relative to base_dir (NULL or "": the working directory, like the reference).  flags: PTB_SCENE_IGNORE_TEXTURES drops
+ * map_Kd / bump files instead of failing on them (no image decoder here; hand texels to ptb_upload_textures). */
+#define PTB_SCENE_IGNORE_TEXTURES 1
+int ptb_load_scene_file(ptb_ctx *ctx, const char *scene_file, const char *base_dir, int flags);
+/* The same loader without a context or a GPU: writes the .ptbs container.  Returns PTB_OK or PTB_ERR_IO with the reason in
+ * err (NUL-terminated, at most err_len bytes). */
+int ptb_convert_scene_file(const char *scene_file, const char *base_dir, const char *out_ptbs, int flags, char *err, uint64_t err_len);
 int ptb_set_camera(ptb_ctx *ctx, const ptb_camera *cam); /* cameraSetForward + origin/dof/focus, scene.cpp:127-130 */
 /* the Camera struct verbatim (camera.h:5-18) after the UI rotated it (camera.cpp:70-135): no re-orthonormalisation */
 int ptb_set_camera_basis(ptb_ctx *ctx, const float origin[3], const float forward[3], const float right[3], const float up[3],
