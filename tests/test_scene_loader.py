@@ -1,0 +1,198 @@
+"""The .scene / OBJ / MTL loader (csrc/ptb_scene_loader.cpp, ptb_convert_scene_file / ptb_load_scene_file)
+against the reference's own loader: loadScene + loadObject (tinyobjloader 2.0.0 underneath) as compiled into
+oracle/_ref/ptref, whose `dump-scene` writes what getTris() / getObjects() / getMaterials() hold.  The bar is byte equality
+of the .ptbs container — vertex transforms, normals, flipped v coordinates, material ids, object ranges, Heron surface
+areas, emission normalisation, scene-file overrides, names.  tests/golden/cornel.ptbs is such a dump (committed), the
+other comparisons run where the reference is compiled (this container), on OBJ text written by the test itself."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import have_ref, run_ptref
+
+REF_SHOWCASE = "/root/reference/showcase"
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cornel.ptbs")
+
+
+def _convert(ptb, scene, out, base="", **kw):
+    ptb.convert_scene_file(scene, out, base_dir=base, **kw)
+    with open(out, "rb") as f:
+        return f.read()
+
+
+@pytest.fixture(scope="module")
+def ptb():
+    import ptb_b200
+    return ptb_b200
+
+
+@pytest.mark.skipif(not os.path.isfile(os.path.join(REF_SHOWCASE, "scenes", "cornel.scene")), reason="the reference's showcase/ assets are not on this machine")
+def test_cornell_scene_equals_the_reference_loaders_dump(ptb, tmp_path):
+    mine = _convert(ptb, os.path.join(REF_SHOWCASE, "scenes", "cornel.scene"), str(tmp_path / "c.ptbs"), REF_SHOWCASE)
+    with open(GOLDEN, "rb") as f:
+        assert mine == f.read()
+
+
+OBJ = """# written by tests/test_scene_loader.py
+mtllib m.mtl
+o first object
+v 0 0 0
+v 1.5 0 0
+v 1.5 2.25 0
+v 0 2.25 1e-1
+v -.5 -0.25 3
+v 2.5E+0 -1.75e-2 3.125
+v 0.333333343 0.1 0.7
+v 12345.678 -0.000012 7
+vn 0 0 1
+vn 0 1 0
+vn 0.577350 0.577350 -0.577350
+vt 0 0
+vt 1 0
+vt 1 1
+vt 0.25 0.75
+usemtl red
+f 1/1/1 2/2/1 3/3/1
+f 1/1/1 2/2/1 3/3/1 4/4/2
+usemtl lamp
+f -4/1/3 -3/2/3 -2/3/3
+g second group of faces
+usemtl red
+f 5/4/2 6/3/2 7/2/2 8/1/2
+f 8/1/1 7/2/2 6/3/3
+o third
+f 2/2/1 4/4/1 6/1/1\r
+usemtl nowhere
+f 1/1/1 3/3/1 5/2/2
+"""
+
+MTL = """newmtl red
+Ns 250.000000
+Kd 0.800204 0.000000 0.458439
+Ke 0 0 0
+Ni 1.5
+
+newmtl lamp
+Kd 0.1 0.2 0.3
+Ke 4.5 9.9 0.99
+illum 2
+newmtl dim
+Ke 0.25 0.5 0.125
+"""
+
+SCENE = """[Models]
+file: objs/a.obj
+pos:  0.5,-250,3
+scale: 300,2.5,-1
+file: objs/a.obj
+scale: 1,1,1
+
+[Materials]
+name: red
+color: 1.0,0.25,0.8
+roughness: 0.1
+weights: 0.25,0.25,0.5
+name: dim
+emission: 3
+
+[Camera]
+pos: 1,2,-500
+forward: 0.1,0.0,1
+focus: 1.5
+dof: 0.25
+"""
+
+
+def _write_tree(d):
+    os.makedirs(os.path.join(d, "objs"))
+    with open(os.path.join(d, "objs", "a.obj"), "w", newline="") as f:
+        f.write(OBJ)
+    with open(os.path.join(d, "objs", "m.mtl"), "w") as f:
+        f.write(MTL)
+    with open(os.path.join(d, "s.scene"), "w") as f:
+        f.write(SCENE)
+    return os.path.join(d, "s.scene")
+
+
+def test_synthetic_scene_arrays(ptb, tmp_path):
+    """What the text above must turn into, worked out by hand for the parts that need no reference: triangle count (two
+    quads -> four triangles), the shorter-diagonal rule, relative indices, per-face material ids with the fallback for an
+    unknown usemtl, shapes split at o / g, two instances of the model with their own fallback material each."""
+    scene = _write_tree(str(tmp_path))
+    _convert(ptb, scene, str(tmp_path / "s.ptbs"), str(tmp_path))
+    s = ptb.scenes.read_ptbs(str(tmp_path / "s.ptbs"))
+    assert s["pos"].shape == (18, 9) and len(s["objects"]) == 6 and len(s["materials"]) == 8
+    names = [m["name"] for m in s["materials"]]
+    assert names == ["None", "red", "lamp", "dim", "None", "red", "lamp", "dim"]
+    assert [o["name"] for o in s["objects"]] == ["first object", "second group of faces", "third"] * 2
+    assert [(o["start"], o["end"]) for o in s["objects"]] == [(0, 4), (4, 7), (7, 9), (9, 13), (13, 16), (16, 18)]
+    # first model: materials 1.. ; unknown usemtl -> the shape's first material id is >= 0, so the face takes the shape's
+    assert s["mat"].tolist() == [1, 1, 1, 2, 1, 1, 1, 1, 1] + [5, 5, 5, 6, 5, 5, 5, 5, 5]
+    assert [o["materials"] for o in s["objects"]] == [[1, 2], [1], [1], [5, 6], [5], [5]]
+    # transform of the first instance: v * scale + pos in fp32, two roundings
+    v = np.array([1.5, 2.25, 0], np.float32) * np.array([300, 2.5, -1], np.float32) + np.array([0.5, -250, 3], np.float32)
+    assert (s["pos"][0, 6:9].view(np.uint32) == v.view(np.uint32)).all()
+    # quad 1-2-3-4: |v3-v1|^2 = 7.3125 < |v4-v2|^2 = 7.3225 -> triangles (1,2,3) (1,3,4)
+    second = s["pos"][9:]  # the second instance: scale 1, and the position carried over from the first model
+    v3 = np.array([1.5 + 0.5, 2.25 - 250, 0 + 3], np.float32)
+    assert (second[1, 6:9] == v3).all() and (second[2, 3:6] == v3).all()
+    # flipped v, emission normalised by its largest component, override by name on both instances
+    assert s["uv"][0].tolist() == [0, 1, 1, 1, 1, 0]
+    lamp, red, dim = s["materials"][2], s["materials"][5], s["materials"][7]
+    assert lamp["emission"] == np.float32(9.9) and np.allclose(lamp["albedo"], [4.5 / 9.9, 1, 0.99 / 9.9])
+    assert red["albedo"] == [1.0, 0.25, np.float32(0.8)] and red["weights"] == [0.25, 0.25, 0.5] and red["roughness"] == np.float32(0.1)
+    assert dim["emission"] == 3.0 and dim["roughness"] == np.float32(0.1) and dim["weights"] == [0.25, 0.25, 0.5]  # fields carry over
+    assert s["camera"] == {"pos": [1.0, 2.0, -500.0], "forward": [np.float32(0.1), 0.0, 1.0], "focus": 1.5, "dof": 0.25}
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref/ptref not built (needs the reference sources)")
+def test_synthetic_scene_equals_the_compiled_reference(ptb, tmp_path):
+    scene = _write_tree(str(tmp_path))
+    mine = _convert(ptb, scene, str(tmp_path / "mine.ptbs"), str(tmp_path))
+    run_ptref(["--scene-file", scene, "--base", str(tmp_path), "dump-scene", str(tmp_path / "ref.ptbs")])
+    with open(tmp_path / "ref.ptbs", "rb") as f:
+        ref = f.read()
+    assert mine == ref
+
+
+@pytest.mark.skipif(not (have_ref() and os.path.isfile(os.path.join(REF_SHOWCASE, "objects", "test.obj"))), reason="needs ptref and the reference's showcase/objects/test.obj")
+def test_blender_export_equals_the_compiled_reference(ptb, tmp_path):
+    """showcase/objects/test.obj: 1,932 triangles of a Blender export with its own .mtl (naming a texture file that is
+    not shipped: both loaders go on without it), moved and scaled anisotropically"""
+    scene = str(tmp_path / "t.scene")
+    with open(scene, "w") as f:
+        f.write("[Models]\nfile: objects/test.obj\npos: 3.25,-17,0.001\nscale: 30,31.5,-29\n\n[Camera]\npos: 0,0,-500\nforward: 0,0,1\nfocus: 1\n")
+    mine = _convert(ptb, scene, str(tmp_path / "mine.ptbs"), REF_SHOWCASE)
+    run_ptref(["--scene-file", scene, "--base", REF_SHOWCASE, "dump-scene", str(tmp_path / "ref.ptbs")])
+    with open(tmp_path / "ref.ptbs", "rb") as f:
+        assert mine == f.read()
+
+
+def test_refusals(ptb, tmp_path):
+    d = str(tmp_path)
+    os.makedirs(os.path.join(d, "objs"))
+    with open(os.path.join(d, "objs", "m.mtl"), "w") as f:
+        f.write("newmtl t\nKd 1 1 1\nmap_Kd -bm 0.5 wall tex.png\n")
+    with open(os.path.join(d, "objs", "a.obj"), "w") as f:
+        f.write("mtllib m.mtl\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv -1 0.5 0\nvn 0 0 1\nvt 0 0\nusemtl t\nf 1/1/1 2/1/1 3/1/1\n")
+    with open(os.path.join(d, "s.scene"), "w") as f:
+        f.write("[Models]\nfile: objs/a.obj\n")
+    # a texture file that is not there: "could not load", untextured material, like loadTexture (texture.cpp:36-39)
+    ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d)
+    with open(os.path.join(d, "objs", "wall tex.png"), "wb") as f:
+        f.write(b"\x89PNG")
+    with pytest.raises(ptb.PtbError, match="wall tex.png"):  # the file name keeps its blank; options are skipped
+        ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d)
+    ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d, ignore_textures=True)
+    assert ptb.scenes.read_ptbs(os.path.join(d, "o.ptbs"))["pos"].shape == (1, 9)
+    with open(os.path.join(d, "objs", "a.obj"), "a") as f:
+        f.write("f 1/1/1 2/1/1 3/1/1 4/1/1 5/1/1\n")
+    with pytest.raises(ptb.PtbError, match="polygon with 5 vertices"):
+        ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d, ignore_textures=True)
+    with pytest.raises(ptb.PtbError, match="cannot open"):
+        ptb.convert_scene_file(os.path.join(d, "missing.scene"), os.path.join(d, "o.ptbs"))
+    with open(os.path.join(d, "s2.scene"), "w") as f:
+        f.write("[Models]\nfile: objs/none.obj\n")
+    with pytest.raises(ptb.PtbError, match="Cannot open file"):
+        ptb.convert_scene_file(os.path.join(d, "s2.scene"), os.path.join(d, "o.ptbs"), base_dir=d)
