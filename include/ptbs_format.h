@@ -5,8 +5,9 @@
  * (reference: src/scene/scene.cpp:97-131 `initScene`, src/primitives/object.cpp:35-174
  * `loadObject`): the triangle buffer (`getTris()`), the object table (`getObjects()`),
  * the material table (`getMaterials()`) and the camera from the scene file
- * (src/scene/SceneFile.h:26-31).  The OBJ / .scene text parsers themselves are host-side
- * I/O and stay outside the hot path.
+ * (src/scene/SceneFile.h:26-31).  ptb_convert_scene_file (csrc/ptb_scene_loader.cpp) writes it
+ * from .scene / OBJ / MTL text; oracle/ref/ref_driver.cpp's dump-scene writes it from the
+ * reference's own loader, and the two agree byte for byte (tests/test_scene_loader.py).
  *
  * Layout (little endian, all blocks tightly packed, in this order):
  *   ptbs_header
