@@ -6,7 +6,7 @@
 // tinyobjloader 2.0.0 (vendored header, includes/singleHeaderLibs/tiny_obj_loader.h; default options: triangulate,
 // real_t = float); the pieces of its published behaviour the arrays depend on are restated in the .cpp, each with the
 // line range it follows.  The result is what the reference holds in getTris() / getObjects() / getMaterials() after
-// initScene — field for field what oracle/ref/ref_driver.cpp's dump-scene writes (tests/golden/cornel.ptbs), which is how
+// initScene — field for field what the compiled reference's scene dump holds (tests/golden/cornel.ptbs), which is how
 // tests/test_scene_loader.py checks it: byte equality of the .ptbs.
 #pragma once
 #include <array>
