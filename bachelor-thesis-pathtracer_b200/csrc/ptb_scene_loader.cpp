@@ -11,6 +11,7 @@
 #include <map>
 #include <set>
 #include <sstream>
+#include <thread>
 
 namespace ptb {
 namespace {
@@ -247,144 +248,313 @@ bool parse_corner(const char *&t, int nv, int nvn, int nvt, Corner &c) {
     return true;
 }
 
-// exportGroupsToShape (:1481-1960), faces only: triangles as they are, quads cut along the shorter diagonal (ties: 1-3),
-// larger polygons are refused — tinyobj ear-clips them, which is not restated here.
-bool flush_faces(Shape &shape, const std::vector<std::vector<Corner>> &faces, int material, const std::string &name,
-                 const std::vector<float> &v, std::string &log, std::string &err) {
-    if (faces.empty()) return false;
-    shape.name = name;
-    for (const auto &f : faces) {
-        if (f.size() < 3) {
-            log += "Degenerated face found\n";
-            continue;
-        }
-        if (f.size() == 3) {
-            shape.corners.insert(shape.corners.end(), f.begin(), f.end());
-            shape.material_ids.push_back(material);
-        } else if (f.size() == 4) {
-            bool bad = false;
-            for (const Corner &c : f) bad |= 3 * (size_t)c.v + 2 >= v.size();
-            if (bad) {
-                log += "Face with invalid vertex index found.\n";
-                continue;
-            }
-            const float *p0 = &v[3 * (size_t)f[0].v], *p1 = &v[3 * (size_t)f[1].v], *p2 = &v[3 * (size_t)f[2].v], *p3 = &v[3 * (size_t)f[3].v];
-            const float ax = p2[0] - p0[0], ay = p2[1] - p0[1], az = p2[2] - p0[2];
-            const float bx = p3[0] - p1[0], by = p3[1] - p1[1], bz = p3[2] - p1[2];
-            const float d02 = ax * ax + ay * ay + az * az, d13 = bx * bx + by * by + bz * bz;
-            const int cut[2][6] = {{0, 1, 2, 0, 2, 3}, {0, 1, 3, 1, 2, 3}};
-            for (int k : cut[d02 < d13 ? 0 : 1]) shape.corners.push_back(f[k]);
-            shape.material_ids.push_back(material);
-            shape.material_ids.push_back(material);
-        } else {
-            err = "polygon with " + std::to_string(f.size()) + " vertices: triangulate the mesh (only triangles and quads are loaded)";
-            return false;
-        }
+// ---- the file in memory, cut into chunks of whole lines that are scanned and parsed by one thread each ------------------
+// v / vn / vt / f statements only depend on how many v / vn / vt came before them (relative indices), so they are counted
+// per chunk, prefix-summed, and parsed in parallel into their final places; the statements that carry state from line to
+// line (usemtl, mtllib, g, o) are collected with their position among the faces and replayed in file order afterwards.
+enum Statement { S_OTHER, S_V, S_VN, S_VT, S_F, S_USEMTL, S_MTLLIB, S_G, S_O };
+
+Statement classify(const char *t) { // the order of tests of LoadObj's if-chain (tiny_obj_loader.h:2640-3000)
+    if (t[0] == 'v' && is_space(t[1])) return S_V;
+    if (t[0] == 'v' && t[1] == 'n' && is_space(t[2])) return S_VN;
+    if (t[0] == 'v' && t[1] == 't' && is_space(t[2])) return S_VT;
+    if (t[0] == 'f' && is_space(t[1])) return S_F;
+    if (strncmp(t, "usemtl", 6) == 0) return S_USEMTL;
+    if (starts(t, "mtllib")) return S_MTLLIB;
+    if (t[0] == 'g' && is_space(t[1])) return S_G;
+    if (t[0] == 'o' && is_space(t[1])) return S_O;
+    return S_OTHER;
+}
+
+struct Control {
+    Statement kind;
+    std::string text;  // the statement's line, leading blanks removed
+    uint32_t face;     // faces of its chunk that precede it
+    size_t nv_local;   // "v" statements of its chunk that precede it
+};
+struct Chunk {
+    const char *b = nullptr, *e = nullptr;
+    size_t nv = 0, nvn = 0, nvt = 0, lines = 0, nfaces = 0, ncorners = 0; // counted by scan()
+    size_t v0 = 0, vn0 = 0, vt0 = 0, line0 = 0;                           // prefix sums
+    std::vector<Control> ctl;
+    std::vector<Corner> corners; // faces of the chunk, CSR
+    std::vector<uint32_t> start;
+    std::string err;
+};
+
+// calls f(text, line_number_in_chunk) for every non-empty, non-comment line; lines end at \n, \r\n or \r (safeGetline)
+template <class F> void for_lines(const char *b, const char *e, std::string &line, F f) {
+    size_t no = 0;
+    while (b < e) {
+        const char *p = b;
+        while (p < e && *p != '\n' && *p != '\r') ++p;
+        line.assign(b, p);
+        b = p;
+        if (b < e) b += (*b == '\r' && b + 1 < e && b[1] == '\n') ? 2 : 1;
+        ++no;
+        const char *t = line.c_str();
+        t += strspn(t, " \t");
+        if (*t == '\0' || *t == '#') continue;
+        f(t, no);
     }
+}
+
+void scan_chunk(Chunk &c) {
+    std::string line;
+    for_lines(c.b, c.e, line, [&](const char *t, size_t no) {
+        (void)no;
+        switch (classify(t)) {
+        case S_V: c.nv++; break;
+        case S_VN: c.nvn++; break;
+        case S_VT: c.nvt++; break;
+        case S_F: {
+            c.nfaces++;
+            const char *p = t + 2;
+            p += strspn(p, " \t");
+            while (!is_eol(*p)) { // one corner per blank-separated word
+                c.ncorners++;
+                p += strcspn(p, " \t\r");
+                p += strspn(p, " \t\r");
+            }
+            break;
+        }
+        case S_USEMTL: case S_MTLLIB: case S_G: case S_O:
+            c.ctl.push_back(Control{classify(t), std::string(t), (uint32_t)c.nfaces, c.nv});
+            break;
+        default: break;
+        }
+    });
+    // lines: for_lines numbers every line, c.lines holds the last statement's; count the rest for the prefix sum
+    size_t total = 0;
+    for (const char *p = c.b; p < c.e; ++p)
+        if (*p == '\n' || (*p == '\r' && !(p + 1 < c.e && p[1] == '\n'))) ++total;
+    if (c.e > c.b && c.e[-1] != '\n' && c.e[-1] != '\r') ++total;
+    c.lines = total;
+}
+
+void parse_chunk(Chunk &c, ObjFile &out) {
+    std::string line;
+    size_t iv = c.v0, ivn = c.vn0, ivt = c.vt0;
+    c.corners.reserve(c.ncorners);
+    c.start.reserve(c.nfaces + 1);
+    c.start.push_back(0);
+    for_lines(c.b, c.e, line, [&](const char *t, size_t no) {
+        if (!c.err.empty()) return;
+        switch (classify(t)) {
+        case S_V: {
+            Cursor k{t + 2};
+            for (int j = 0; j < 3; ++j) out.v[3 * iv + j] = k.real_or(0.0);
+            ++iv;
+            break;
+        }
+        case S_VN: {
+            Cursor k{t + 3};
+            for (int j = 0; j < 3; ++j) out.vn[3 * ivn + j] = k.real_or(0.0);
+            ++ivn;
+            break;
+        }
+        case S_VT: {
+            Cursor k{t + 3};
+            for (int j = 0; j < 2; ++j) out.vt[2 * ivt + j] = k.real_or(0.0);
+            ++ivt;
+            break;
+        }
+        case S_F: {
+            const char *p = t + 2;
+            p += strspn(p, " \t");
+            while (!is_eol(*p)) {
+                Corner k;
+                if (!parse_corner(p, (int)iv, (int)ivn, (int)ivt, k)) {
+                    c.err = "Failed to parse `f' line (e.g. a zero value for vertex index or invalid relative vertex index). Line " +
+                            std::to_string(c.line0 + no);
+                    return;
+                }
+                c.corners.push_back(k);
+                p += strspn(p, " \t\r");
+            }
+            c.start.push_back((uint32_t)c.corners.size());
+            break;
+        }
+        default: break;
+        }
+    });
+}
+
+template <class F> void run_parallel(size_t n, F f) {
+    if (n <= 1) {
+        for (size_t i = 0; i < n; ++i) f(i);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (size_t i = 0; i < n; ++i) th.emplace_back([&f, i]() { f(i); });
+    for (auto &t : th) t.join();
+}
+
+struct FaceRange { const Chunk *c; uint32_t b, e; };
+
+// exportGroupsToShape (:1481-1960), faces only: triangles as they are, quads cut along the shorter diagonal (ties: 1-3),
+// larger polygons are refused — tinyobj ear-clips them, which is not restated here.  `nv`: vertices read so far (a quad
+// that names a later one is dropped like the reference drops it).
+bool flush_faces(Shape &shape, const std::vector<FaceRange> &pending, int material, const std::string &name, const std::vector<float> &v,
+                 size_t nv, std::string &log, std::string &err) {
+    size_t total = 0;
+    for (const FaceRange &r : pending) total += r.e - r.b;
+    if (total == 0) return false;
+    shape.name = name;
+    for (const FaceRange &r : pending)
+        for (uint32_t fi = r.b; fi < r.e; ++fi) {
+            const Corner *f = &r.c->corners[r.c->start[fi]];
+            const size_t n = r.c->start[fi + 1] - r.c->start[fi];
+            if (n < 3) {
+                log += "Degenerated face found\n";
+            } else if (n == 3) {
+                shape.corners.insert(shape.corners.end(), f, f + 3);
+                shape.material_ids.push_back(material);
+            } else if (n == 4) {
+                bool bad = false;
+                for (int k = 0; k < 4; ++k) bad |= (size_t)f[k].v >= nv;
+                if (bad) {
+                    log += "Face with invalid vertex index found.\n";
+                    continue;
+                }
+                const float *p0 = &v[3 * (size_t)f[0].v], *p1 = &v[3 * (size_t)f[1].v], *p2 = &v[3 * (size_t)f[2].v], *p3 = &v[3 * (size_t)f[3].v];
+                const float ax = p2[0] - p0[0], ay = p2[1] - p0[1], az = p2[2] - p0[2];
+                const float bx = p3[0] - p1[0], by = p3[1] - p1[1], bz = p3[2] - p1[2];
+                const float d02 = ax * ax + ay * ay + az * az, d13 = bx * bx + by * by + bz * bz;
+                const int cut[2][6] = {{0, 1, 2, 0, 2, 3}, {0, 1, 3, 1, 2, 3}};
+                for (int k : cut[d02 < d13 ? 0 : 1]) shape.corners.push_back(f[k]);
+                shape.material_ids.push_back(material);
+                shape.material_ids.push_back(material);
+            } else {
+                err = "polygon with " + std::to_string(n) + " vertices: triangulate the mesh (only triangles and quads are loaded)";
+                return false;
+            }
+        }
     return true;
 }
 
 // LoadObj (tiny_obj_loader.h:2584-3146) for the statements that reach the triangle buffer: v vn vt f usemtl mtllib g o
 bool read_obj(const std::string &file, const std::string &mtl_dir, ObjFile &out, std::string &log, std::string &err) {
-    std::ifstream is(file, std::ios::binary);
-    if (!is) {
-        err = "Cannot open file [" + file + "]";
-        return false;
+    std::string buf;
+    {
+        std::ifstream is(file, std::ios::binary);
+        if (!is) {
+            err = "Cannot open file [" + file + "]";
+            return false;
+        }
+        is.seekg(0, std::ios::end);
+        const std::streamoff size = is.tellg();
+        is.seekg(0);
+        buf.resize(size > 0 ? (size_t)size : 0);
+        if (!buf.empty() && !is.read(&buf[0], (std::streamsize)buf.size())) {
+            err = "Cannot read file [" + file + "]";
+            return false;
+        }
     }
+    // chunks of at least 1 MB, cut after a '\n' (PTB_LOADER_THREADS=n forces n chunks whatever the size: tests)
+    size_t want = std::max<size_t>(1, std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), buf.size() >> 20));
+    if (const char *forced = getenv("PTB_LOADER_THREADS"))
+        if (atoi(forced) > 0) want = (size_t)std::min(atoi(forced), 256);
+    std::vector<Chunk> chunks;
+    const char *base = buf.data(), *end = base + buf.size();
+    for (size_t i = 0; i < want; ++i) {
+        const char *b = chunks.empty() ? base : chunks.back().e;
+        const char *e = i + 1 == want ? end : base + buf.size() * (i + 1) / want;
+        if (e < b) e = b;
+        while (e < end && e > base && e[-1] != '\n') ++e;
+        Chunk c;
+        c.b = b;
+        c.e = e;
+        chunks.push_back(std::move(c));
+    }
+    run_parallel(chunks.size(), [&](size_t i) { scan_chunk(chunks[i]); });
+    size_t nv = 0, nvn = 0, nvt = 0, lines = 0;
+    for (Chunk &c : chunks) {
+        c.v0 = nv; c.vn0 = nvn; c.vt0 = nvt; c.line0 = lines;
+        nv += c.nv; nvn += c.nvn; nvt += c.nvt; lines += c.lines;
+    }
+    out.v.resize(3 * nv);
+    out.vn.resize(3 * nvn);
+    out.vt.resize(2 * nvt);
+    run_parallel(chunks.size(), [&](size_t i) { parse_chunk(chunks[i], out); });
+    for (const Chunk &c : chunks)
+        if (!c.err.empty()) {
+            err = c.err;
+            return false;
+        }
+
+    // the stateful statements, replayed in file order
     std::map<std::string, int> by_name;
     std::set<std::string> mtl_seen;
-    std::vector<std::vector<Corner>> faces;
+    std::vector<FaceRange> pending;
     Shape shape;
-    std::string name, line;
+    std::string name;
     int material = -1;
-    size_t line_no = 0;
-    auto flush = [&]() { return flush_faces(shape, faces, material, name, out.v, log, err); };
-    while (next_line(is, line)) {
-        ++line_no;
-        if (line.empty()) continue;
-        const char *t = line.c_str();
-        t += strspn(t, " \t");
-        if (*t == '\0' || *t == '#') continue;
-        if (t[0] == 'v' && is_space(t[1])) {
-            Cursor c{t + 2};
-            for (int k = 0; k < 3; ++k) out.v.push_back(c.real_or(0.0));
-        } else if (t[0] == 'v' && t[1] == 'n' && is_space(t[2])) {
-            Cursor c{t + 3};
-            for (int k = 0; k < 3; ++k) out.vn.push_back(c.real_or(0.0));
-        } else if (t[0] == 'v' && t[1] == 't' && is_space(t[2])) {
-            Cursor c{t + 3};
-            for (int k = 0; k < 2; ++k) out.vt.push_back(c.real_or(0.0));
-        } else if (t[0] == 'f' && is_space(t[1])) {
-            t += 2;
-            t += strspn(t, " \t");
-            std::vector<Corner> f;
-            while (!is_eol(*t)) {
-                Corner c;
-                if (!parse_corner(t, (int)(out.v.size() / 3), (int)(out.vn.size() / 3), (int)(out.vt.size() / 2), c)) {
-                    err = "Failed to parse `f' line (e.g. a zero value for vertex index or invalid relative vertex index). Line " +
-                          std::to_string(line_no);
-                    return false;
+    auto flush = [&](size_t nv_now) { return flush_faces(shape, pending, material, name, out.v, nv_now, log, err); };
+    for (const Chunk &c : chunks) {
+        uint32_t cursor = 0;
+        for (const Control &k : c.ctl) {
+            if (k.face > cursor) pending.push_back(FaceRange{&c, cursor, k.face});
+            cursor = k.face;
+            const size_t nv_now = c.v0 + k.nv_local;
+            const char *t = k.text.c_str();
+            if (k.kind == S_USEMTL) {
+                Cursor w{t + 6};
+                const std::string m = w.word();
+                const auto it = by_name.find(m);
+                const int id = it != by_name.end() ? it->second : -1;
+                if (it == by_name.end()) log += "material [ '" + m + "' ] not found in .mtl\n";
+                if (id != material) { // faces so far keep the old material; the shape goes on (:2839-2847)
+                    flush(nv_now);
+                    if (!err.empty()) return false;
+                    pending.clear();
+                    material = id;
                 }
-                f.push_back(c);
-                t += strspn(t, " \t\r");
-            }
-            faces.push_back(std::move(f));
-        } else if (strncmp(t, "usemtl", 6) == 0) {
-            Cursor c{t + 6};
-            const std::string m = c.word();
-            const auto it = by_name.find(m);
-            const int id = it != by_name.end() ? it->second : -1;
-            if (it == by_name.end()) log += "material [ '" + m + "' ] not found in .mtl\n";
-            if (id != material) { // faces so far keep the old material; the shape goes on (:2839-2847)
-                flush();
-                if (!err.empty()) return false;
-                faces.clear();
-                material = id;
-            }
-        } else if (starts(t, "mtllib")) {
-            std::istringstream names(t + 7);
-            std::string fn;
-            bool found = false;
-            while (!found && names >> fn) {
-                if (mtl_seen.count(fn)) {
+            } else if (k.kind == S_MTLLIB) {
+                std::istringstream names(t + 7);
+                std::string fn;
+                bool found = false;
+                while (!found && names >> fn) {
+                    if (mtl_seen.count(fn)) {
+                        found = true;
+                        break;
+                    }
+                    std::ifstream ms(mtl_dir + fn, std::ios::binary);
+                    if (!ms) {
+                        log += "Material file [ " + fn + " ] not found in a path : " + mtl_dir + "\n";
+                        continue;
+                    }
+                    read_mtl(ms, out.materials, by_name);
+                    mtl_seen.insert(fn);
                     found = true;
-                    break;
                 }
-                std::ifstream ms(mtl_dir + fn, std::ios::binary);
-                if (!ms) {
-                    log += "Material file [ " + fn + " ] not found in a path : " + mtl_dir + "\n";
-                    continue;
+                if (!found) log += "Failed to load material file(s). Use default material.\n";
+            } else { // g, o: the shape so far is complete
+                flush(nv_now);
+                if (!err.empty()) return false;
+                if (!shape.corners.empty()) out.shapes.push_back(std::move(shape));
+                shape = Shape();
+                pending.clear();
+                if (k.kind == S_O) {
+                    name = std::string(t + 2); // the rest of the line, spaces included (:2989-2992)
+                } else {
+                    // the statement letter itself is the first "name" the reference collects, the group name starts at the second
+                    Cursor w{t};
+                    std::vector<std::string> words;
+                    while (!is_eol(*w.p)) {
+                        words.push_back(w.word());
+                        w.p += strspn(w.p, " \t\r");
+                    }
+                    name.clear();
+                    for (size_t i = 1; i < words.size(); ++i) name += (i > 1 ? " " : "") + words[i];
                 }
-                read_mtl(ms, out.materials, by_name);
-                mtl_seen.insert(fn);
-                found = true;
-            }
-            if (!found) log += "Failed to load material file(s). Use default material.\n";
-        } else if ((t[0] == 'g' || t[0] == 'o') && is_space(t[1])) {
-            flush();
-            if (!err.empty()) return false;
-            if (!shape.corners.empty()) out.shapes.push_back(shape);
-            shape = Shape();
-            faces.clear();
-            if (t[0] == 'o') {
-                name = std::string(t + 2); // the rest of the line, spaces included (:2989-2992)
-            } else {
-                // the statement letter itself is the first "name" the reference collects, the group name starts at the second
-                Cursor c{t};
-                std::vector<std::string> words;
-                while (!is_eol(*c.p)) {
-                    words.push_back(c.word());
-                    c.p += strspn(c.p, " \t\r");
-                }
-                name.clear();
-                for (size_t i = 1; i < words.size(); ++i) name += (i > 1 ? " " : "") + words[i];
             }
         }
-        // everything else (s, l, p, t, vw, ...) does not reach the triangle buffer
+        if (c.nfaces > cursor) pending.push_back(FaceRange{&c, cursor, (uint32_t)c.nfaces});
     }
-    const bool some = flush();
+    const bool some = flush(nv);
     if (!err.empty()) return false;
-    if (some || !shape.corners.empty()) out.shapes.push_back(shape);
+    if (some || !shape.corners.empty()) out.shapes.push_back(std::move(shape));
     return true;
 }
 
@@ -470,55 +640,67 @@ bool load_obj(const std::string &file, const float position[3], const float size
         const int start = (int)sc.triangles();
         int shape_mat = sh.material_ids[0];
         shape_mat = shape_mat >= 0 ? shape_mat + first_mat : default_mat;
-        std::vector<uint32_t> used;
+        std::vector<uint32_t> used; // the shape's materials in order of first use (:125-131)
         std::vector<bool> seen(obj.materials.size(), false);
-        float area = 0.0f;
-        for (size_t i = 0; i < sh.corners.size(); i += 3) {
-            float p[9], n[9], uv[6];
-            bool have_normals = true;
-            for (int j = 0; j < 3; ++j) {
-                const Corner &c = sh.corners[i + j];
-                if (c.v < 0 || (size_t)c.v >= nv) {
-                    err = "shape " + sh.name + ": vertex index out of bounds";
-                    return false;
-                }
-                for (int k = 0; k < 3; ++k) p[3 * j + k] = obj.v[3 * (size_t)c.v + k] * size[k] + position[k];
-                // a corner without vn / vt makes the reference read before the start of its arrays; here: the
-                // geometric normal (createTriangle's 4-argument flavour, triangle.cpp:54-65) and uv (0, 0)
-                if (c.vn >= 0 && (size_t)c.vn < nn)
-                    for (int k = 0; k < 3; ++k) n[3 * j + k] = obj.vn[3 * (size_t)c.vn + k];
-                else
-                    have_normals = false;
-                if (c.vt >= 0 && (size_t)c.vt < nt) {
-                    uv[2 * j] = obj.vt[2 * (size_t)c.vt];
-                    uv[2 * j + 1] = 1.0f - obj.vt[2 * (size_t)c.vt + 1];
-                } else {
-                    uv[2 * j] = uv[2 * j + 1] = 0.0f;
-                }
+        const size_t ntri = sh.corners.size() / 3;
+        for (size_t i = 0; i < ntri; ++i) {
+            const int m = sh.material_ids[i];
+            if (m >= 0 && !seen[m]) {
+                seen[m] = true;
+                used.push_back((uint32_t)(m + first_mat));
             }
-            if (!have_normals) {
-                const float e1[3] = {p[3] - p[0], p[4] - p[1], p[5] - p[2]}, e2[3] = {p[6] - p[0], p[7] - p[1], p[8] - p[2]};
-                float g[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
-                const float l = length3(g[0], g[1], g[2]);
-                for (int j = 0; j < 3; ++j)
-                    for (int k = 0; k < 3; ++k) n[3 * j + k] = l > 0 ? g[k] / l : 0.0f;
-            }
-            int m = sh.material_ids[i / 3];
-            if (m >= 0) {
-                if (!seen[m]) {
-                    seen[m] = true;
-                    used.push_back((uint32_t)(m + first_mat));
-                }
-                m += first_mat;
-            } else {
-                m = shape_mat;
-            }
-            sc.pos9.insert(sc.pos9.end(), p, p + 9);
-            sc.nrm9.insert(sc.nrm9.end(), n, n + 9);
-            sc.uv6.insert(sc.uv6.end(), uv, uv + 6);
-            sc.mat.push_back(m);
-            area += surface_area(p); // summed in triangle order (:151-154)
         }
+        const size_t base = sc.triangles();
+        sc.pos9.resize(9 * (base + ntri));
+        sc.nrm9.resize(9 * (base + ntri));
+        sc.uv6.resize(6 * (base + ntri));
+        sc.mat.resize(base + ntri);
+        std::vector<float> areas(ntri);
+        const size_t workers = std::max<size_t>(1, std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), ntri >> 14));
+        std::vector<int> bad(workers, 0);
+        run_parallel(workers, [&](size_t w) {
+            for (size_t i = ntri * w / workers; i < ntri * (w + 1) / workers; ++i) {
+                float *p = &sc.pos9[9 * (base + i)], *n = &sc.nrm9[9 * (base + i)], *uv = &sc.uv6[6 * (base + i)];
+                bool have_normals = true;
+                for (int j = 0; j < 3; ++j) {
+                    const Corner &c = sh.corners[3 * i + j];
+                    if (c.v < 0 || (size_t)c.v >= nv) {
+                        bad[w] = 1;
+                        return;
+                    }
+                    for (int k = 0; k < 3; ++k) p[3 * j + k] = obj.v[3 * (size_t)c.v + k] * size[k] + position[k];
+                    // a corner without vn / vt makes the reference read before the start of its arrays; here: the
+                    // geometric normal (createTriangle's 4-argument flavour, triangle.cpp:54-65) and uv (0, 0)
+                    if (c.vn >= 0 && (size_t)c.vn < nn)
+                        for (int k = 0; k < 3; ++k) n[3 * j + k] = obj.vn[3 * (size_t)c.vn + k];
+                    else
+                        have_normals = false;
+                    if (c.vt >= 0 && (size_t)c.vt < nt) {
+                        uv[2 * j] = obj.vt[2 * (size_t)c.vt];
+                        uv[2 * j + 1] = 1.0f - obj.vt[2 * (size_t)c.vt + 1];
+                    } else {
+                        uv[2 * j] = uv[2 * j + 1] = 0.0f;
+                    }
+                }
+                if (!have_normals) {
+                    const float e1[3] = {p[3] - p[0], p[4] - p[1], p[5] - p[2]}, e2[3] = {p[6] - p[0], p[7] - p[1], p[8] - p[2]};
+                    float g[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+                    const float l = length3(g[0], g[1], g[2]);
+                    for (int j = 0; j < 3; ++j)
+                        for (int k = 0; k < 3; ++k) n[3 * j + k] = l > 0 ? g[k] / l : 0.0f;
+                }
+                const int m = sh.material_ids[i];
+                sc.mat[base + i] = m >= 0 ? m + first_mat : shape_mat;
+                areas[i] = surface_area(p);
+            }
+        });
+        for (int b : bad)
+            if (b) {
+                err = "shape " + sh.name + ": vertex index out of bounds";
+                return false;
+            }
+        float area = 0.0f;
+        for (size_t i = 0; i < ntri; ++i) area += areas[i]; // summed in triangle order like the reference (:151-154)
         ptbs_object o{};
         o.start_idx = start;
         o.end_idx = (int)sc.triangles();

@@ -596,8 +596,8 @@ int main(int argc, char **argv) {
     if (cmd == "dump-scene") {
         if (pos.size() < 2) die("dump-scene <out.ptbs>");
         dumpScene(pos[1].c_str());
-        printf("PTREF_JSON {\"cmd\":\"dump-scene\",\"tris\":%zu,\"objects\":%zu,\"materials\":%zu}\n", getTris().size(),
-               getObjects().size(), getMaterials()->size());
+        printf("PTREF_JSON {\"cmd\":\"dump-scene\",\"tris\":%zu,\"objects\":%zu,\"materials\":%zu,\"load_ms\":%.1f}\n", getTris().size(),
+               getObjects().size(), getMaterials()->size(), loadMs);
         return 0;
     }
     buildStructures(o, cp, cf, cam.focus, cam.dof);

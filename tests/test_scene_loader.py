@@ -156,6 +156,18 @@ def test_synthetic_scene_equals_the_compiled_reference(ptb, tmp_path):
     assert mine == ref
 
 
+@pytest.mark.parametrize("chunks", [2, 3, 7, 64])
+def test_chunked_parse_equals_the_single_chunk_parse(ptb, tmp_path, monkeypatch, chunks):
+    """Large files are cut into chunks of whole lines parsed by one thread each (relative indices resolved from prefix
+    counts, usemtl / g / o replayed in file order); forcing that path on the small scene puts the cuts anywhere."""
+    scene = _write_tree(str(tmp_path))
+    monkeypatch.setenv("PTB_LOADER_THREADS", "1")
+    one = _convert(ptb, scene, str(tmp_path / "one.ptbs"), str(tmp_path))
+    monkeypatch.setenv("PTB_LOADER_THREADS", str(chunks))
+    many = _convert(ptb, scene, str(tmp_path / "many.ptbs"), str(tmp_path))
+    assert one == many
+
+
 @pytest.mark.skipif(not (have_ref() and os.path.isfile(os.path.join(REF_SHOWCASE, "objects", "test.obj"))), reason="needs ptref and the reference's showcase/objects/test.obj")
 def test_blender_export_equals_the_compiled_reference(ptb, tmp_path):
     """showcase/objects/test.obj: 1,932 triangles of a Blender export with its own .mtl (naming a texture file that is
@@ -164,9 +176,15 @@ def test_blender_export_equals_the_compiled_reference(ptb, tmp_path):
     with open(scene, "w") as f:
         f.write("[Models]\nfile: objects/test.obj\npos: 3.25,-17,0.001\nscale: 30,31.5,-29\n\n[Camera]\npos: 0,0,-500\nforward: 0,0,1\nfocus: 1\n")
     mine = _convert(ptb, scene, str(tmp_path / "mine.ptbs"), REF_SHOWCASE)
+    os.environ["PTB_LOADER_THREADS"] = "5"
+    try:
+        chunked = _convert(ptb, scene, str(tmp_path / "mine5.ptbs"), REF_SHOWCASE)
+    finally:
+        del os.environ["PTB_LOADER_THREADS"]
     run_ptref(["--scene-file", scene, "--base", REF_SHOWCASE, "dump-scene", str(tmp_path / "ref.ptbs")])
     with open(tmp_path / "ref.ptbs", "rb") as f:
-        assert mine == f.read()
+        ref = f.read()
+    assert mine == ref and chunked == ref
 
 
 def test_refusals(ptb, tmp_path):
