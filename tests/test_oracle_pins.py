@@ -147,3 +147,52 @@ def test_textured_live_against_compiled_reference(textured_scenes):
     rimg, rec, _ = ptref_render(paths[1], W, H, MODE_BVH, 2, 6, 1)
     assert (_bits(img) == _bits(rimg)).all()
     assert st["tri_tests"] == rec["tri_tests"] and st["as_tests"] == rec["as_tests"]
+
+
+# ---- a second scene: two models, one of them a flat Blender export (zero-thickness boxes in every structure) -----------------
+TWO_MODELS = """[Models]
+file: objects/cornel.obj
+pos:  0,-250,0
+scale: 300,300,300
+file: objects/test.obj
+pos: 40,-60,-120
+scale: 18,14,300
+
+[Materials]
+name: Material.004
+color: 1.0,1.0,0.8
+emission: 0
+roughness: 0.1
+weights: 0,0,1
+
+[Camera]
+pos: 0,0,-500
+forward: 0,0.0,1
+focus: 1
+"""
+
+
+@pytest.mark.skipif(not (have_ref() and os.path.isfile("/root/reference/showcase/objects/test.obj")), reason="needs ptref and the reference's showcase/ assets")
+@pytest.mark.parametrize("mode", [MODE_BVH, MODE_TWO_PLANE])
+def test_live_two_model_scene_with_a_flat_mesh(tmp_path, mode):
+    """Cornell plus showcase/objects/test.obj (1,932 coplanar triangles, 23 % of the frame) loaded from scene text: hits, frame
+    and both counters of the restatement equal the compiled reference's.  (Subbeams are left out: the reference's beam
+    recursion has no depth guard and does not terminate on this mesh)"""
+    import ptb_b200
+    scene, ptbs = str(tmp_path / "two.scene"), str(tmp_path / "two.ptbs")
+    with open(scene, "w") as f:
+        f.write(TWO_MODELS)
+    ptb_b200.convert_scene_file(scene, ptbs, base_dir="/root/reference/showcase")
+    W, H = 96, 80
+    o = Oracle(ptbs)
+    o.build(grid=(mode == MODE_TWO_PLANE))
+    o.configure(W, H, mode, nee=1, max_depth=5)
+    t, tri, mat = o.primary_hits()
+    img, _, _, st = o.render(2)
+    o.close()
+    rt, rtri, rmat, _, _ = ptref_primary_hits(ptbs, W, H, mode)
+    rimg, rec, _ = ptref_render(ptbs, W, H, mode, 2, 5, 1)
+    assert (_bits(t) == _bits(rt)).all() and (tri == rtri).all() and (mat == rmat).all()
+    assert 0.1 < float((mat == mat.max()).mean()) < 0.5  # the flat mesh is in view
+    assert (_bits(img) == _bits(rimg)).all()
+    assert st["tri_tests"] == rec["tri_tests"] and st["as_tests"] == rec["as_tests"]
