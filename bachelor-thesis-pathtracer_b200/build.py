@@ -13,7 +13,7 @@ INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 OUT = os.path.join(_HERE, "libptb.so")
 OBJDIR = os.path.join(CSRC, "build")
 
-SOURCES = ["ptb_api.cu", "ptb_lbvh.cu", "ptb_grid_gpu.cu", "ptb_beam_gpu.cu", "ptb_group.cu", "ptb_bvh_build.cpp", "ptb_grid_build.cpp", "ptb_scene_loader.cpp"]
+SOURCES = ["ptb_api.cu", "ptb_lbvh.cu", "ptb_grid_gpu.cu", "ptb_beam_gpu.cu", "ptb_group.cu", "ptb_bvh_build.cpp", "ptb_grid_build.cpp", "ptb_scene_loader.cpp", "ptb_png.cpp"]
 
 # -fmad=false / -prec-div / -prec-sqrt / -ftz=false: the arithmetic contract of ptb_device.cuh
 NVCC_FLAGS = [
@@ -81,5 +81,5 @@ def build_native(force=False, verbose=False, defines=(), out=None):
         logs = list(ex.map(_run, jobs))
     if verbose:
         print("\n".join(logs))
-    _run([_nvcc(), "-shared", "-Xcompiler", "-pthread", "-o", out] + objs)
+    _run([_nvcc(), "-shared", "-Xcompiler", "-pthread", "-o", out] + objs + ["-lz"])  # zlib: PNG textures (ptb_png.cpp)
     return out

@@ -616,6 +616,11 @@ extern "C" int ptb_load_scene_file(ptb_ctx *c, const char *scene_file, const cha
     if ((r = ptb_upload_triangles(c, s.pos9.data(), s.nrm9.data(), s.uv6.data(), s.mat.data(), s.triangles()))) return r;
     if ((r = ptb_upload_materials(c, s.materials.data(), (uint32_t)s.materials.size()))) return r;
     if ((r = ptb_upload_objects(c, s.objects.data(), (uint32_t)s.objects.size()))) return r;
+    if (!s.texels.empty()) {
+        std::vector<ptb_texture> tex;
+        for (const auto &t : s.texels) tex.push_back(ptb_texture{t.rgba.data(), t.width, t.height});
+        if ((r = ptb_upload_textures(c, tex.data(), (uint32_t)tex.size(), s.mat_tex.data(), (uint32_t)s.materials.size()))) return r;
+    }
     ptb_camera cam{};
     for (int k = 0; k < 3; ++k) {
         cam.origin[k] = s.cam_pos[k];

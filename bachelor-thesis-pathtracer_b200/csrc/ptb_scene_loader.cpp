@@ -2,6 +2,8 @@
 // `v * size + position` rounds twice like the reference's build (-O3 -mavx2, no FMA; object.cpp:107-109).
 #include "ptb_scene_loader.h"
 
+#include "ptb_png.h"
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -622,12 +624,6 @@ bool load_obj(const std::string &file, const float position[3], const float size
                 tex[k].clear();
             }
         }
-        if ((!tex[0].empty() || !tex[1].empty()) && !(flags & kSceneIgnoreTextures)) {
-            err = "material " + me.name + " names the texture file " + (tex[0].empty() ? tex[1] : tex[0]) +
-                  ": image decoding (stbi_load, texture.cpp:34) is not part of this loader; decode it on the caller's side and hand the "
-                  "texels to ptb_upload_textures, or load with the ignore-textures flag";
-            return false;
-        }
         if (flags & kSceneIgnoreTextures) tex = {};
         sc.materials.push_back(m);
         sc.textures.push_back(tex);
@@ -790,13 +786,37 @@ bool load_scene_file(const std::string &scene_file, const std::string &base_dir,
             sc.materials[i] = r;
             sc.textures[i] = {};
         }
+    return decode_textures(sc, err);
+}
+
+bool decode_textures(LoadedScene &sc, std::string &err) {
+    sc.texels.clear();
+    sc.mat_tex.assign(2 * sc.materials.size(), -1);
+    for (size_t i = 0; i < sc.materials.size(); ++i)
+        for (int k = 0; k < 2; ++k) {
+            const std::string &path = sc.textures[i][k];
+            if (path.empty()) continue;
+            std::vector<unsigned char> px;
+            LoadedScene::Texels t;
+            if (!decode_png(path, px, t.width, t.height, err)) {
+                err = "material " + std::string(sc.materials[i].name) + ": " + err +
+                      " — convert the texture to PNG, hand texels to ptb_upload_textures yourself, or load with the ignore-textures flag";
+                return false;
+            }
+            t.rgba.resize(px.size());
+            for (size_t j = 0; j < px.size(); ++j) t.rgba[j] = px[j] / 255.0f; // texture.cpp:44-47
+            sc.mat_tex[2 * i + k] = (int32_t)sc.texels.size();
+            sc.texels.push_back(std::move(t));
+            sc.log += "loaded texture " + path + "\n";
+        }
     return true;
 }
 
 bool write_ptbs(const std::string &path, const LoadedScene &sc, std::string &err) {
     ptbs_header h{};
     h.magic = PTBS_MAGIC;
-    h.version = PTBS_VERSION;
+    h.version = sc.texels.empty() ? PTBS_VERSION : PTBS_VERSION_TEXTURES;
+    h.reserved[0] = (uint32_t)sc.texels.size();
     h.n_tris = (uint32_t)sc.triangles();
     h.n_objects = (uint32_t)sc.objects.size();
     h.n_materials = (uint32_t)sc.materials.size();
@@ -819,6 +839,14 @@ bool write_ptbs(const std::string &path, const LoadedScene &sc, std::string &err
     put(sc.mat.data(), sc.mat.size() * 4);
     put(sc.objects.data(), sc.objects.size() * sizeof(ptbs_object));
     put(sc.materials.data(), sc.materials.size() * sizeof(ptbs_material));
+    if (!sc.texels.empty()) {
+        put(sc.mat_tex.data(), sc.mat_tex.size() * 4);
+        for (const LoadedScene::Texels &t : sc.texels) {
+            const ptbs_texture_hdr th{t.width, t.height};
+            put(&th, sizeof th);
+            put(t.rgba.data(), t.rgba.size() * 4);
+        }
+    }
     ok = fclose(f) == 0 && ok;
     if (!ok) err = "short write to " + path;
     return ok;

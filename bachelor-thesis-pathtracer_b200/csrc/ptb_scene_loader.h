@@ -19,9 +19,10 @@
 namespace ptb {
 
 enum SceneLoadFlags : int {
-    // stbi_load (src/types/texture.cpp:34) has no counterpart here: a material that names an EXISTING texture file makes
-    // the load fail unless this flag says to drop the textures (the material keeps its Kd colour); a file that does not
-    // exist is skipped with the reference's "could not load" message, as loadTexture does (texture.cpp:36-39)
+    // Texture files (map_Kd, bump) are decoded when they are PNG (ptb_png.cpp); any other format stbi_load
+    // (src/types/texture.cpp:34) would read makes the load fail unless this flag says to drop the textures (the material
+    // keeps its Kd colour).  A file that does not exist is skipped with the reference's "could not load" message, as
+    // loadTexture does (texture.cpp:36-39)
     kSceneIgnoreTextures = 1,
 };
 
@@ -31,6 +32,11 @@ struct LoadedScene {
     std::vector<ptbs_object> objects;
     std::vector<ptbs_material> materials;
     std::vector<std::array<std::string, 2>> textures; // per material: map_Kd, bump file (resolved path) or ""
+    // filled by load_scene_file / decode_textures: Texture::data as loadTexture leaves it (byte / 255.0f, texture.cpp:41-50),
+    // numbered in material order, albedo before normal map
+    struct Texels { int width = 0, height = 0; std::vector<float> rgba; };
+    std::vector<Texels> texels;
+    std::vector<int32_t> mat_tex; // 2 per material: index into texels or -1
     float cam_pos[3] = {0, 0, 0}, cam_forward[3] = {0, 0, 0}, cam_focus = 0, cam_dof = 0;
     std::string log; // what the reference prints while loading + tinyobj-style warnings
     size_t triangles() const { return mat.size(); }
@@ -44,7 +50,10 @@ bool load_obj(const std::string &file, const float position[3], const float size
 // directory, like the reference, which is started inside showcase/).
 bool load_scene_file(const std::string &scene_file, const std::string &base_dir, LoadedScene &scene, std::string &err, int flags = 0);
 
-// the .ptbs v1 container (include/ptbs_format.h)
+// decodes the files named in `textures` into `texels` / `mat_tex` (load_scene_file calls it after the overrides)
+bool decode_textures(LoadedScene &scene, std::string &err);
+
+// the .ptbs container (include/ptbs_format.h): v1, or v2 when the scene holds texels
 bool write_ptbs(const std::string &path, const LoadedScene &scene, std::string &err);
 
 } // namespace ptb

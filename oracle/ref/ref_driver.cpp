@@ -259,7 +259,20 @@ static void dumpScene(const char *path) {
     auto &mats = *getMaterials();
     ptbs_header h{};
     h.magic = PTBS_MAGIC;
-    h.version = PTBS_VERSION;
+    // version 2 iff a material carries texels: textures numbered in material order, albedo before normal map
+    std::vector<Texture *> texs;
+    std::vector<int32_t> matTex;
+    for (auto &m : mats)
+        for (Texture *t : {&m.pbr.texture, &m.pbr.normal}) {
+            if (t->data.empty()) {
+                matTex.push_back(-1);
+            } else {
+                matTex.push_back((int32_t)texs.size());
+                texs.push_back(t);
+            }
+        }
+    h.version = texs.empty() ? PTBS_VERSION : PTBS_VERSION_TEXTURES;
+    h.reserved[0] = (uint32_t)texs.size();
     h.n_tris = tris.size();
     h.n_objects = objs.size();
     h.n_materials = mats.size();
@@ -314,6 +327,17 @@ static void dumpScene(const char *path) {
         pm.w_refraction = m.weights.refraction;
         strncpy(pm.name, m.name.c_str(), sizeof pm.name - 1);
         fwrite(&pm, sizeof pm, 1, f);
+    }
+    if (!texs.empty()) {
+        fwrite(matTex.data(), 4, matTex.size(), f);
+        for (Texture *t : texs) {
+            ptbs_texture_hdr th{t->width, t->height};
+            fwrite(&th, sizeof th, 1, f);
+            for (auto &px : t->data) {
+                float c[4] = {px[0], px[1], px[2], px[3]};
+                fwrite(c, 4, 4, f);
+            }
+        }
     }
     fclose(f);
 }

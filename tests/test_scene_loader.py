@@ -214,3 +214,112 @@ def test_refusals(ptb, tmp_path):
         f.write("[Models]\nfile: objs/none.obj\n")
     with pytest.raises(ptb.PtbError, match="Cannot open file"):
         ptb.convert_scene_file(os.path.join(d, "s2.scene"), os.path.join(d, "o.ptbs"), base_dir=d)
+
+
+# ---- PNG textures (csrc/ptb_png.cpp) against stb_image as compiled into the reference -----------------------------------------
+def _png_bytes(samples, colour, depth, filters, plte=None, trns=None):
+    """samples: (H, W, channels) integer array of raw sample values; one filter type per row, cycling through `filters`"""
+    import struct
+    import zlib
+    h, w, ch = samples.shape
+    rows = []
+    for y in range(h):
+        s = samples[y].reshape(-1)
+        if depth == 8:
+            raw = bytes(int(v) for v in s)
+        elif depth == 16:
+            raw = b"".join(struct.pack(">H", int(v)) for v in s)
+        else:
+            bits = "".join(format(int(v), "0%db" % depth) for v in s)
+            bits += "0" * (-len(bits) % 8)
+            raw = bytes(int(bits[i:i + 8], 2) for i in range(0, len(bits), 8))
+        rows.append(raw)
+    bpp = max(1, ch * depth // 8)
+    out = b""
+    prev = bytes(len(rows[0]))
+    for y, raw in enumerate(rows):
+        f = filters[y % len(filters)]
+        line = bytearray()
+        for i, v in enumerate(raw):
+            a = raw[i - bpp] if i >= bpp else 0
+            b = prev[i]
+            c = prev[i - bpp] if i >= bpp else 0
+            if f == 0:
+                p = 0
+            elif f == 1:
+                p = a
+            elif f == 2:
+                p = b
+            elif f == 3:
+                p = (a + b) // 2
+            else:
+                q = a + b - c
+                pa, pb, pc = abs(q - a), abs(q - b), abs(q - c)
+                p = a if pa <= pb and pa <= pc else (b if pb <= pc else c)
+            line.append((v - p) & 255)
+        out += bytes([f]) + bytes(line)
+        prev = raw
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    z = zlib.compress(out, 6)
+    body = chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, colour, 0, 0, 0))
+    if plte is not None:
+        body += chunk(b"PLTE", bytes(plte))
+    if trns is not None:
+        body += chunk(b"tRNS", bytes(trns))
+    body += chunk(b"IDAT", z[: len(z) // 2]) + chunk(b"IDAT", z[len(z) // 2:])  # two IDAT chunks
+    return b"\x89PNG\r\n\x1a\n" + body + chunk(b"IEND", b"")
+
+
+def _textured_tree(d):
+    """seven materials, each with a PNG of another kind as map_Kd (and one bump map), on seven triangles"""
+    rng = np.random.default_rng(11)
+    os.makedirs(os.path.join(d, "objs"))
+    kinds = [  # name, colour type, depth, channels, extra chunks
+        ("rgba8", 6, 8, 4, {}), ("rgb8", 2, 8, 3, {}), ("grey8", 0, 8, 1, {}), ("ga8", 4, 8, 2, {}), ("rgb16", 2, 16, 3, {}),
+        ("pal4", 3, 4, 1, {"plte": rng.integers(0, 256, 48).tolist(), "trns": rng.integers(0, 256, 9).tolist()}),
+        ("grey2", 0, 2, 1, {"trns": [0, 2]}), ("rgbkey", 2, 8, 3, {"trns": [0, 7, 0, 7, 0, 7]}),
+    ]
+    mtl, obj = "", "mtllib m.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nvt 0 0\nvt 1 0\nvt 0 1\n"
+    for i, (name, colour, depth, ch, extra) in enumerate(kinds):
+        w, h = 5 + i, 7 - (i % 3)
+        s = rng.integers(0, 1 << depth, (h, w, ch))
+        if name == "rgbkey":
+            s[1, 2] = 7  # a pixel equal to the colour key
+        with open(os.path.join(d, "objs", name + ".png"), "wb") as f:
+            f.write(_png_bytes(s, colour, depth, [0, 1, 2, 3, 4], **extra))
+        mtl += f"newmtl m{i}\nKd 0.5 0.5 0.5\nmap_Kd {name}.png\n"
+        if i == 1:
+            mtl += "map_Bump -bm 0.3 rgba8.png\n"
+        obj += f"usemtl m{i}\nf 1/1/1 2/2/1 3/3/1\n"
+    with open(os.path.join(d, "objs", "m.mtl"), "w") as f:
+        f.write(mtl)
+    with open(os.path.join(d, "objs", "a.obj"), "w") as f:
+        f.write(obj)
+    with open(os.path.join(d, "s.scene"), "w") as f:
+        f.write("[Models]\nfile: objs/a.obj\npos: 0,0,0\nscale: 1,1,1\n\n[Materials]\nname: m2\ncolor: 1,0,0\n\n[Camera]\npos: 0,0,-5\nforward: 0,0,1\nfocus: 1\n")
+    return os.path.join(d, "s.scene")
+
+
+def test_png_textures_decode(ptb, tmp_path):
+    """8-bit RGBA texels survive the trip exactly; the override of m2 drops its texture like `mat.pbr = m.mat.pbr` does"""
+    scene = _textured_tree(str(tmp_path))
+    _convert(ptb, scene, str(tmp_path / "s.ptbs"), str(tmp_path))
+    s = ptb.scenes.read_ptbs(str(tmp_path / "s.ptbs"))
+    assert len(s["textures"]) == 8  # 8 albedo maps - the overridden one + the bump map
+    bind = [(m.get("tex", -1), m.get("nrm", -1)) for m in s["materials"]]
+    assert bind == [(-1, -1), (0, -1), (1, 2), (-1, -1), (3, -1), (4, -1), (5, -1), (6, -1), (7, -1)]
+    assert (s["textures"][0] == s["textures"][2]).all() and s["textures"][0].shape == (7, 5, 4)
+    assert float(s["textures"][1][..., 3].min()) == 1.0  # RGB: opaque
+    assert (s["textures"][7][1, 2] == np.array([7 / 255, 7 / 255, 7 / 255, 0], np.float32)).all()  # the colour key
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref/ptref not built (needs the reference sources)")
+def test_png_textures_equal_stb_image_in_the_compiled_reference(ptb, tmp_path):
+    scene = _textured_tree(str(tmp_path))
+    mine = _convert(ptb, scene, str(tmp_path / "mine.ptbs"), str(tmp_path))
+    run_ptref(["--scene-file", scene, "--base", str(tmp_path), "dump-scene", str(tmp_path / "ref.ptbs")])
+    with open(tmp_path / "ref.ptbs", "rb") as f:
+        assert mine == f.read()
