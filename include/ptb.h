@@ -104,8 +104,9 @@ int ptb_load_ptbs(ptb_ctx *ctx, const char *path); /* the uploads + camera from 
  * object.cpp:35-174) without the 280-byte Triangle AoS in between: .scene / OBJ / MTL text straight into
  * the arrays of ptb_upload_*, and the scene-file camera.  OBJ/MTL are read the way tinyobjloader 2.0.0 reads them (its
  * number parser included), so the arrays are the reference's bit for bit; triangles and quads only.  Model paths are
- * relative to base_dir (NULL or "": the working directory, like the reference).  flags: PTB_SCENE_IGNORE_TEXTURES drops
- * map_Kd / bump files instead of failing on them (no image decoder here; hand texels to ptb_upload_textures). */
+ * relative to base_dir (NULL or "": the working directory, like the reference).  map_Kd / bump files are decoded when they
+ * are PNG (texels = byte / 255.0f like loadTexture, texture.cpp:33-50) and uploaded with the scene; other image formats
+ * fail the load unless flags has PTB_SCENE_IGNORE_TEXTURES (then hand texels to ptb_upload_textures yourself). */
 #define PTB_SCENE_IGNORE_TEXTURES 1
 int ptb_load_scene_file(ptb_ctx *ctx, const char *scene_file, const char *base_dir, int flags);
 /* The same loader without a context or a GPU: writes the .ptbs container.  Returns PTB_OK or PTB_ERR_IO with the reason in
