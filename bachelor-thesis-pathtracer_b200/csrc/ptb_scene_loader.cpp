@@ -394,11 +394,94 @@ template <class F> void run_parallel(size_t n, F f) {
 
 struct FaceRange { const Chunk *c; uint32_t b, e; };
 
+// even-odd point-in-polygon test on a triangle (pnpoly, tiny_obj_loader.h:1438-1450), fp32 like the reference's real_t
+bool inside_triangle(const float *x, const float *y, float tx, float ty) {
+    bool in = false;
+    for (int i = 0, j = 2; i < 3; j = i++)
+        if (((y[i] > ty) != (y[j] > ty)) && (tx < (x[j] - x[i]) * (ty - y[i]) / (y[j] - y[i]) + x[i])) in = !in;
+    return in;
+}
+
+// Polygons of five or more corners: tinyobj's built-in ear clipping (:1740-1958; the reference does not enable the earcut
+// variant).  The polygon is projected on the two axes that the first non-degenerate corner's normal is NOT largest along;
+// a candidate corner (g, g+1, g+2) is an ear when cross * area >= 0 — with `area` the reference's (x0*y1 - y0*x1)/2 —
+// and no other remaining vertex lies inside it; its middle vertex is removed; the search gives up after a full round
+// without progress, and a last triangle is emitted when exactly three vertices remain.  Vertices not read yet (index
+// >= nv) count as (0, 0) in the tests, as there.
+void clip_ears(const Corner *f, size_t n, const std::vector<float> &v, size_t nv, Shape &shape, int material) {
+    const size_t vsize = 3 * nv;
+    size_t ax[2] = {1, 2};
+    for (size_t k = 0; k < n; ++k) {
+        const size_t i0 = (size_t)f[k % n].v, i1 = (size_t)f[(k + 1) % n].v, i2 = (size_t)f[(k + 2) % n].v;
+        if (3 * i0 + 2 >= vsize || 3 * i1 + 2 >= vsize || 3 * i2 + 2 >= vsize) continue;
+        const float e0x = v[3 * i1] - v[3 * i0], e0y = v[3 * i1 + 1] - v[3 * i0 + 1], e0z = v[3 * i1 + 2] - v[3 * i0 + 2];
+        const float e1x = v[3 * i2] - v[3 * i1], e1y = v[3 * i2 + 1] - v[3 * i1 + 1], e1z = v[3 * i2 + 2] - v[3 * i1 + 2];
+        const float cx = std::fabs(e0y * e1z - e0z * e1y), cy = std::fabs(e0z * e1x - e0x * e1z), cz = std::fabs(e0x * e1y - e0y * e1x);
+        const float eps = 1.1920929e-07f; // numeric_limits<float>::epsilon()
+        if (cx > eps || cy > eps || cz > eps) {
+            if (!(cx > cy && cx > cz)) {
+                ax[0] = 0;
+                if (cz > cx && cz > cy) ax[1] = 1;
+            }
+            break;
+        }
+    }
+    std::vector<Corner> rest(f, f + n);
+    size_t guess = 0, budget = n, before = n;
+    auto emit = [&](const Corner &a, const Corner &b, const Corner &c) {
+        shape.corners.push_back(a);
+        shape.corners.push_back(b);
+        shape.corners.push_back(c);
+        shape.material_ids.push_back(material);
+    };
+    while (rest.size() > 3 && budget > 0) {
+        const size_t m = rest.size();
+        if (guess >= m) guess -= m;
+        if (before != m) {
+            before = m;
+            budget = m;
+        } else {
+            --budget;
+        }
+        Corner ind[3];
+        float x[3], y[3];
+        for (size_t k = 0; k < 3; ++k) {
+            ind[k] = rest[(guess + k) % m];
+            const size_t vi = (size_t)ind[k].v;
+            const bool out = vi * 3 + ax[0] >= vsize || vi * 3 + ax[1] >= vsize;
+            x[k] = out ? 0.0f : v[vi * 3 + ax[0]];
+            y[k] = out ? 0.0f : v[vi * 3 + ax[1]];
+        }
+        const float e0x = x[1] - x[0], e0y = y[1] - y[0], e1x = x[2] - x[1], e1y = y[2] - y[1];
+        const float cross = e0x * e1y - e0y * e1x;
+        const float area = (x[0] * y[1] - y[0] * x[1]) * 0.5f;
+        if (cross * area < 0.0f) { // an internal angle
+            ++guess;
+            continue;
+        }
+        bool overlap = false;
+        for (size_t other = 3; other < m && !overlap; ++other) {
+            const size_t idx = (guess + other) % m;
+            const size_t ovi = (size_t)rest[idx].v;
+            if (ovi * 3 + ax[0] >= vsize || ovi * 3 + ax[1] >= vsize) continue;
+            overlap = inside_triangle(x, y, v[ovi * 3 + ax[0]], v[ovi * 3 + ax[1]]);
+        }
+        if (overlap) {
+            ++guess;
+            continue;
+        }
+        emit(ind[0], ind[1], ind[2]);
+        rest.erase(rest.begin() + (long)((guess + 1) % m));
+    }
+    if (rest.size() == 3) emit(rest[0], rest[1], rest[2]);
+}
+
 // exportGroupsToShape (:1481-1960), faces only: triangles as they are, quads cut along the shorter diagonal (ties: 1-3),
-// larger polygons are refused — tinyobj ear-clips them, which is not restated here.  `nv`: vertices read so far (a quad
-// that names a later one is dropped like the reference drops it).
+// larger polygons ear-clipped (clip_ears).  `nv`: vertices read so far (a quad that names a later one is dropped like the
+// reference drops it).
 bool flush_faces(Shape &shape, const std::vector<FaceRange> &pending, int material, const std::string &name, const std::vector<float> &v,
                  size_t nv, std::string &log, std::string &err) {
+    (void)err; // nothing is refused at this point any more
     size_t total = 0;
     for (const FaceRange &r : pending) total += r.e - r.b;
     if (total == 0) return false;
@@ -428,8 +511,7 @@ bool flush_faces(Shape &shape, const std::vector<FaceRange> &pending, int materi
                 shape.material_ids.push_back(material);
                 shape.material_ids.push_back(material);
             } else {
-                err = "polygon with " + std::to_string(n) + " vertices: triangulate the mesh (only triangles and quads are loaded)";
-                return false;
+                clip_ears(f, n, v, nv, shape, material);
             }
         }
     return true;

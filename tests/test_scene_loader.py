@@ -204,10 +204,6 @@ def test_refusals(ptb, tmp_path):
         ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d)
     ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d, ignore_textures=True)
     assert ptb.scenes.read_ptbs(os.path.join(d, "o.ptbs"))["pos"].shape == (1, 9)
-    with open(os.path.join(d, "objs", "a.obj"), "a") as f:
-        f.write("f 1/1/1 2/1/1 3/1/1 4/1/1 5/1/1\n")
-    with pytest.raises(ptb.PtbError, match="polygon with 5 vertices"):
-        ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d, ignore_textures=True)
     with pytest.raises(ptb.PtbError, match="cannot open"):
         ptb.convert_scene_file(os.path.join(d, "missing.scene"), os.path.join(d, "o.ptbs"))
     with open(os.path.join(d, "s2.scene"), "w") as f:
@@ -319,6 +315,62 @@ def test_png_textures_decode(ptb, tmp_path):
 @pytest.mark.skipif(not have_ref(), reason="oracle/_ref/ptref not built (needs the reference sources)")
 def test_png_textures_equal_stb_image_in_the_compiled_reference(ptb, tmp_path):
     scene = _textured_tree(str(tmp_path))
+    mine = _convert(ptb, scene, str(tmp_path / "mine.ptbs"), str(tmp_path))
+    run_ptref(["--scene-file", scene, "--base", str(tmp_path), "dump-scene", str(tmp_path / "ref.ptbs")])
+    with open(tmp_path / "ref.ptbs", "rb") as f:
+        assert mine == f.read()
+
+
+# ---- polygons of five and more corners: tinyobj's built-in ear clipping ------------------------------------------------------
+def _polygon_tree(d):
+    rng = np.random.default_rng(5)
+    lines, nv = ["mtllib m.mtl", "vn 0 0 1", "vt 0.5 0.5", "usemtl a"], 0
+
+    def poly(pts):
+        nonlocal nv
+        lines.extend("v %.6f %.6f %.6f" % tuple(p) for p in pts)
+        lines.append("f " + " ".join("%d/1/1" % (nv + i + 1) for i in range(len(pts))))
+        nv += len(pts)
+
+    poly([(np.cos(a), np.sin(a), 0.0) for a in np.linspace(0, 2 * np.pi, 6)[:-1]])          # convex pentagon
+    poly([(0, 0, 1), (2, 0, 1), (2, 1, 1), (1, 1, 1), (1, 2, 1), (0, 2, 1)])                # concave L
+    poly([(3, 0, 0), (3, 0, 2), (3, 1, 1), (3, 2, 2), (3, 2, 0), (3, 1, 0.5), (3, 0.5, 0.2)])  # clockwise, in the yz plane
+    ang, r = np.linspace(0, 2 * np.pi, 11)[:-1], np.where(np.arange(10) % 2 == 0, 2.0, 0.8)
+    poly([(r[i] * np.cos(ang[i]), r[i] * np.sin(ang[i]), 0.3 * r[i] * np.cos(ang[i]) + 5) for i in range(10)])  # tilted star
+    for t in range(40):  # star-shaped polygons of 5..12 corners in random planes, both windings
+        k = int(rng.integers(5, 13))
+        a, rad = np.sort(rng.uniform(0, 2 * np.pi, k)), rng.uniform(0.3, 1.5, k)
+        u = rng.normal(size=3)
+        u /= np.linalg.norm(u)
+        w = np.cross(u, rng.normal(size=3))
+        w /= np.linalg.norm(w)
+        c = rng.uniform(-5, 5, 3)
+        pts = [c + rad[i] * (np.cos(a[i]) * u + np.sin(a[i]) * w) for i in range(k)]
+        poly(pts[::-1] if t % 2 else pts)
+    poly([(0, 0, 9), (1, 0, 9), (2, 0, 9), (3, 0, 9), (4, 0, 9)])  # collinear: no ear is ever found
+    os.makedirs(os.path.join(d, "objs"))
+    with open(os.path.join(d, "objs", "a.obj"), "w") as f:
+        f.write("\n".join(lines) + "\n")
+    with open(os.path.join(d, "objs", "m.mtl"), "w") as f:
+        f.write("newmtl a\nKd 1 0 0\n")
+    with open(os.path.join(d, "s.scene"), "w") as f:
+        f.write("[Models]\nfile: objs/a.obj\npos: 0,0,0\nscale: 1,1,1\n")
+    return os.path.join(d, "s.scene")
+
+
+def test_polygons_are_ear_clipped(ptb, tmp_path):
+    scene = _polygon_tree(str(tmp_path))
+    _convert(ptb, scene, str(tmp_path / "s.ptbs"), str(tmp_path))
+    p = ptb.scenes.read_ptbs(str(tmp_path / "s.ptbs"))["pos"].astype(np.float64).reshape(-1, 3, 3)
+    area = 0.5 * np.linalg.norm(np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]), axis=1)
+    # pentagon -> 3 triangles covering 5/2 sin(72 deg); the L -> 4 triangles of total area 3
+    assert np.isclose(area[:3].sum(), 2.5 * np.sin(2 * np.pi / 5), rtol=1e-5) and np.isclose(area[3:7].sum(), 3.0, rtol=1e-6)
+    assert (p[3:7, :, 2] == 1).all() and (p[7:12, :, 0] == 3).all()  # 7 corners -> 5 triangles in x = 3
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref/ptref not built (needs the reference sources)")
+def test_polygons_equal_the_compiled_reference(ptb, tmp_path):
+    scene = _polygon_tree(str(tmp_path))
     mine = _convert(ptb, scene, str(tmp_path / "mine.ptbs"), str(tmp_path))
     run_ptref(["--scene-file", scene, "--base", str(tmp_path), "dump-scene", str(tmp_path / "ref.ptbs")])
     with open(tmp_path / "ref.ptbs", "rb") as f:
