@@ -9,6 +9,7 @@
 #include "ptb_beam_gpu.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -145,7 +146,11 @@ cudaError_t subbeams_build_gpu(const float *d_vtx, const uint32_t *d_id_of_tri, 
     const char *what = "";
     if (e == cudaSuccess) {
         DeviceExec x(stream);
-        what = build_beam_levels(x, G, (uint32_t)n, d_vtx, d_id_of_tri, m, max_depth, R);
+        // PTB_BEAM_DEEP_CHUNK=k (experiments): below the roots, too, one thread per (beam, k entries of the parent's list)
+        // instead of one per beam; same pools (tests/native/subbeam_levels_check.cpp runs both), not the default until measured
+        const char *deep = getenv("PTB_BEAM_DEEP_CHUNK");
+        const uint32_t deepChunk = deep && atoi(deep) > 0 ? (uint32_t)atoi(deep) : 0u;
+        what = build_beam_levels(x, G, (uint32_t)n, d_vtx, d_id_of_tri, m, max_depth, R, deepChunk);
         e = x.status;
         if (e == cudaSuccess && *what) e = cudaErrorInvalidValue; // a size limit of the driver, nothing wrong with the device
         if (e == cudaSuccess) e = cudaEventRecord(ev1, stream);

@@ -155,6 +155,71 @@ struct BeamRootGather { // a root's list = its chunks' slots, contiguous after t
     }
 };
 
+// ---- depth >= 1, opt-in: a beam's walk over its parent's list cut into workers of `chunk` entries ------------------------
+struct BeamSlotCount { // how many workers beam b needs
+    BeamLevelDev L, P;
+    uint32_t chunk;
+    uint32_t *nSlots;
+    PTB_HD void operator()(uint32_t b) const { nSlots[b] = (P.cnt[L.parent[b]] + chunk - 1) / chunk; }
+};
+
+template <bool FILL>
+struct BeamSlots { // worker i -> (beam b with slotBase[b] <= i < slotBase[b + 1], chunk c = i - slotBase[b])
+    BeamLevelDev L, P;
+    BeamGeom G;
+    uint32_t chunk;
+    const float *tri9;
+    const uint32_t *remap;
+    const uint32_t *slotBase;   // [L.n + 1], exclusive scan of nSlots
+    uint32_t *slotCnt;          // [slots + 1]
+    const uint32_t *slotStart;  // its exclusive scan (FILL)
+    PTB_HD void operator()(uint32_t i) const {
+        uint32_t lo = 0, hi = L.n; // the last b with slotBase[b] <= i (beams without workers share their successor's base)
+        while (hi - lo > 1) {
+            const uint32_t mid = lo + (hi - lo) / 2;
+            if (slotBase[mid] <= i) lo = mid;
+            else hi = mid;
+        }
+        const uint32_t b = lo, c = i - slotBase[b];
+        const int axis = (int)(L.tree[b] / G.cells);
+        float mn[4], mx[4];
+        for (int k = 0; k < 4; ++k) {
+            mn[k] = L.mn[4 * (size_t)b + k] * G.inv;
+            mx[k] = L.mx[4 * (size_t)b + k] * G.inv;
+        }
+        Channel ch;
+        make_channel(V3{G.gmin[axis][0], G.gmin[axis][1], G.gmin[axis][2]}, V3{G.gmax[axis][0], G.gmax[axis][1], G.gmax[axis][2]}, axis,
+                     mn[0], mn[1], mx[0], mx[1], mn[2], mn[3], mx[2], mx[3], ch);
+        const uint32_t p = L.parent[b], total = P.cnt[p];
+        const uint32_t *cand = P.pool + P.start[p];
+        const uint32_t k0 = c * chunk, k1 = (total - k0 < chunk) ? total : k0 + chunk;
+        uint32_t *out = FILL ? L.pool + slotStart[i] : nullptr;
+        uint32_t n = 0;
+        for (uint32_t k = k0; k < k1; ++k) {
+            const uint32_t ti = cand[k];
+            const float *q = tri9 + 9 * (size_t)(remap ? remap[ti] : ti);
+            float t9[9];
+            PTB_UNROLL
+            for (int j = 0; j < 9; ++j) t9[j] = q[j];
+            if (tri_in_channel(t9, ch)) {
+                if (FILL) out[n] = ti;
+                n++;
+            }
+        }
+        if (!FILL) slotCnt[i] = n;
+    }
+};
+
+struct BeamSlotGather {
+    BeamLevelDev L;
+    const uint32_t *slotBase, *slotStart;
+    PTB_HD void operator()(uint32_t b) const {
+        const uint32_t s = slotStart[slotBase[b]];
+        L.start[b] = s;
+        L.cnt[b] = slotStart[slotBase[b + 1]] - s;
+    }
+};
+
 struct BeamClassify { // SubBeams.cpp:286: leaf iff fewer than maxTris triangles remain (or the depth guard fires)
     BeamLevelDev L;
     uint32_t maxTris;
@@ -289,9 +354,10 @@ struct BeamLevelsResult {
 // Executor X: T *alloc<T>(count) (scratch, freed by X), T *alloc_out<T>(count) (results, owned by the caller),
 // run(n, functor), scan(in, out, n) (exclusive, u32), sum64(in, n), fail() (a device error happened).
 // Returns an empty string or what went wrong.
+// deepChunk > 0 (opt-in): below the roots, too, a beam's list is walked by workers of `deepChunk` entries (BeamSlots).
 template <class X>
 const char *build_beam_levels(X &x, const BeamGeom &G, uint32_t nTris, const float *tri9, const uint32_t *remap, uint32_t maxTris,
-                              int maxDepth, BeamLevelsResult &out) {
+                              int maxDepth, BeamLevelsResult &out, uint32_t deepChunk = 0) {
     const uint32_t roots = 3u * G.cells;
     std::vector<BeamLevelDev> lv;
     auto new_level = [&](uint32_t n) {
@@ -333,6 +399,22 @@ const char *build_beam_levels(X &x, const BeamGeom &G, uint32_t nTris, const flo
             x.run(slots, BeamRootChunks<true>{L, G, nTris, nChunks, chunk, tri9, remap, slotCnt, slotStart});
             x.run(roots, BeamRootGather{L, nChunks, slotStart});
             totalPool += L.poolSize;
+        } else if (d > 0 && deepChunk > 0) {
+            uint32_t *nSlots = x.template alloc<uint32_t>((size_t)L.n + 1), *slotBase = x.template alloc<uint32_t>((size_t)L.n + 1);
+            x.run(L.n, BeamSlotCount{L, P, deepChunk, nSlots});
+            const uint64_t slots64 = x.sum64(nSlots, L.n);
+            if (slots64 >= (1ull << 31)) return "Subbeam level needs more than 2^31 workers: raise the chunk size";
+            const uint32_t slots = (uint32_t)slots64;
+            x.scan(nSlots, slotBase, L.n + 1);
+            uint32_t *slotCnt = x.template alloc<uint32_t>((size_t)slots + 1), *slotStart = x.template alloc<uint32_t>((size_t)slots + 1);
+            x.run(slots, BeamSlots<false>{L, P, G, deepChunk, tri9, remap, slotBase, slotCnt, slotStart});
+            L.poolSize = x.sum64(slotCnt, slots);
+            totalPool += L.poolSize;
+            if (totalPool >= (1ull << 32)) return "Subbeam pools exceed 2^32 entries: lower beam_max_depth (ptb_set_build_limits) or the grid size";
+            x.scan(slotCnt, slotStart, slots + 1);
+            L.pool = x.template alloc<uint32_t>((size_t)L.poolSize);
+            x.run(slots, BeamSlots<true>{L, P, G, deepChunk, tri9, remap, slotBase, slotCnt, slotStart});
+            x.run(L.n, BeamSlotGather{L, slotBase, slotStart});
         } else {
             x.run(L.n, BeamCount<false>{L, P, G, d, nTris, tri9, remap});
             L.poolSize = x.sum64(L.cnt, L.n);

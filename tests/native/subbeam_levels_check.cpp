@@ -44,6 +44,13 @@ int main() {
         const char *e = build_beam_levels(x, G, (uint32_t)n, pos.data(), b.order.data(), cs.m, cs.depth, out);
         bool ok = !*e && out.nBeams == R.beams.size() && out.nIdx == R.idx.size() &&
                   !memcmp(out.beams, R.beams.data(), R.beams.size() * sizeof(BeamRec)) && !memcmp(out.idx, R.idx.data(), R.idx.size() * 4);
+        for (uint32_t deep : {1u, 64u}) { // the opt-in (beam, chunk-of-the-parent's-list) workers below the roots
+            HostExec y; BeamLevelsResult o2;
+            const char *e2 = build_beam_levels(y, G, (uint32_t)n, pos.data(), b.order.data(), cs.m, cs.depth, o2, deep);
+            ok = ok && !*e2 && o2.nBeams == R.beams.size() && o2.nIdx == R.idx.size() &&
+                 !memcmp(o2.beams, R.beams.data(), R.beams.size() * sizeof(BeamRec)) && !memcmp(o2.idx, R.idx.data(), R.idx.size() * 4);
+            free(o2.beams); free(o2.idx);
+        }
         printf("n=%d gs=%u m=%u depth=%d beams=%zu idx=%zu levels=%d %s %s\n", n, cs.gs, cs.m, cs.depth, R.beams.size(), R.idx.size(), out.depth, e, ok ? "IDENTICAL" : "DIFFERENT");
         if (!ok) bad = 1;
         free(out.beams); free(out.idx);
