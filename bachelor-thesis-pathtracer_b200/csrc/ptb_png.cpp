@@ -6,6 +6,8 @@
 // zlib does the inflate.  Adam7-interlaced files are refused (none among the reference's assets).
 #include "ptb_png.h"
 
+#include <algorithm>
+#include <cctype>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -40,7 +42,7 @@ bool decode_png(const std::string &path, std::vector<unsigned char> &rgba, int &
     }
     static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1a, '\n'};
     if (file.size() < 8 || memcmp(file.data(), sig, 8) != 0) {
-        err = path + ": not a PNG file (only PNG textures are decoded)";
+        err = path + ": not a PNG file (PNG and TGA textures are decoded)";
         return false;
     }
     uint32_t w = 0, h = 0;
@@ -164,6 +166,93 @@ bool decode_png(const std::string &path, std::vector<unsigned char> &rgba, int &
         }
     }
     return true;
+}
+
+// Truevision TGA, the subset stb_image's loader (stbi__tga_load) is asked for by the reference's kind of assets: image types 2
+// (true colour), 3 (grey) and their run-length flavours 10 / 11, at 24 / 32 / 8 bits per pixel; rows bottom-up unless bit 5
+// of the descriptor says top-down; BGR(A) in the file.  Colour-mapped and 15/16-bit files are refused.
+bool decode_tga(const std::string &path, std::vector<unsigned char> &rgba, int &width, int &height, std::string &err) {
+    std::vector<unsigned char> file;
+    {
+        FILE *f = fopen(path.c_str(), "rb");
+        if (!f) {
+            err = "cannot open " + path;
+            return false;
+        }
+        unsigned char buf[65536];
+        size_t n;
+        while ((n = fread(buf, 1, sizeof buf, f)) > 0) file.insert(file.end(), buf, buf + n);
+        fclose(f);
+    }
+    if (file.size() < 18) {
+        err = path + ": truncated TGA header";
+        return false;
+    }
+    const int id_len = file[0], indexed = file[1];
+    int type = file[2];
+    const int w = file[12] | (file[13] << 8), h = file[14] | (file[15] << 8), bpp = file[16];
+    const bool top_down = (file[17] >> 5) & 1;
+    const bool rle = type >= 8;
+    if (rle) type -= 8;
+    const int comp = bpp == 8 ? 1 : bpp == 24 ? 3 : bpp == 32 ? 4 : 0;
+    if (indexed || (type != 2 && type != 3) || !comp || w <= 0 || h <= 0) {
+        err = path + ": unsupported TGA flavour (colour-mapped, 15/16-bit or empty)";
+        return false;
+    }
+    const size_t npx = (size_t)w * h;
+    std::vector<unsigned char> px(npx * comp);
+    size_t off = 18 + (size_t)id_len;
+    if (!rle) {
+        if (off + px.size() > file.size()) {
+            err = path + ": truncated TGA pixel data";
+            return false;
+        }
+        memcpy(px.data(), &file[off], px.size());
+    } else {
+        for (size_t i = 0; i < npx;) { // packets: 1 + (cmd & 127) pixels, one value repeated if bit 7 is set
+            if (off >= file.size()) {
+                err = path + ": truncated TGA run-length data";
+                return false;
+            }
+            const int cmd = file[off++];
+            const size_t count = 1 + (size_t)(cmd & 127), n = std::min(count, npx - i);
+            const size_t need = (cmd & 128) ? (size_t)comp : count * comp;
+            if (off + need > file.size()) {
+                err = path + ": truncated TGA run-length data";
+                return false;
+            }
+            for (size_t k = 0; k < n; ++k) memcpy(&px[(i + k) * comp], &file[off + ((cmd & 128) ? 0 : k * comp)], (size_t)comp);
+            off += need;
+            i += n;
+        }
+    }
+    width = w;
+    height = h;
+    rgba.assign(npx * 4, 255);
+    for (int y = 0; y < h; ++y) {
+        const unsigned char *row = &px[(size_t)(top_down ? y : h - 1 - y) * w * comp];
+        for (int x = 0; x < w; ++x) {
+            unsigned char *o = &rgba[((size_t)y * w + x) * 4];
+            const unsigned char *q = row + (size_t)x * comp;
+            if (comp == 1) {
+                o[0] = o[1] = o[2] = q[0];
+            } else {
+                o[0] = q[2];
+                o[1] = q[1];
+                o[2] = q[0];
+                if (comp == 4) o[3] = q[3];
+            }
+        }
+    }
+    return true;
+}
+
+bool decode_image(const std::string &path, std::vector<unsigned char> &rgba, int &width, int &height, std::string &err) {
+    const size_t dot = path.find_last_of('.');
+    std::string ext = dot == std::string::npos ? "" : path.substr(dot + 1);
+    for (char &c : ext) c = (char)tolower((unsigned char)c);
+    if (ext == "tga") return decode_tga(path, rgba, width, height, err); // TGA has no signature; stb tries it last, too
+    return decode_png(path, rgba, width, height, err);
 }
 
 } // namespace ptb

@@ -8,5 +8,9 @@
 namespace ptb {
 
 bool decode_png(const std::string &path, std::vector<unsigned char> &rgba, int &width, int &height, std::string &err);
+// true-colour / grey TGA (types 2, 3, 10, 11 at 24 / 32 / 8 bits), rows top to bottom, RGBA out
+bool decode_tga(const std::string &path, std::vector<unsigned char> &rgba, int &width, int &height, std::string &err);
+// by file name: .tga -> decode_tga, everything else must be PNG
+bool decode_image(const std::string &path, std::vector<unsigned char> &rgba, int &width, int &height, std::string &err);
 
 } // namespace ptb

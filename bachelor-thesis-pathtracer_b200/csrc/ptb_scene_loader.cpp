@@ -880,9 +880,9 @@ bool decode_textures(LoadedScene &sc, std::string &err) {
             if (path.empty()) continue;
             std::vector<unsigned char> px;
             LoadedScene::Texels t;
-            if (!decode_png(path, px, t.width, t.height, err)) {
+            if (!decode_image(path, px, t.width, t.height, err)) {
                 err = "material " + std::string(sc.materials[i].name) + ": " + err +
-                      " — convert the texture to PNG, hand texels to ptb_upload_textures yourself, or load with the ignore-textures flag";
+                      " — convert the texture to PNG or TGA, hand texels to ptb_upload_textures yourself, or load with the ignore-textures flag";
                 return false;
             }
             t.rgba.resize(px.size());

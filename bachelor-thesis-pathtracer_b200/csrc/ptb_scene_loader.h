@@ -19,7 +19,7 @@
 namespace ptb {
 
 enum SceneLoadFlags : int {
-    // Texture files (map_Kd, bump) are decoded when they are PNG (ptb_png.cpp); any other format stbi_load
+    // Texture files (map_Kd, bump) are decoded when they are PNG or TGA (ptb_png.cpp); any other format stbi_load
     // (src/types/texture.cpp:34) would read makes the load fail unless this flag says to drop the textures (the material
     // keeps its Kd colour).  A file that does not exist is skipped with the reference's "could not load" message, as
     // loadTexture does (texture.cpp:36-39)

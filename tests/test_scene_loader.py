@@ -375,3 +375,71 @@ def test_polygons_equal_the_compiled_reference(ptb, tmp_path):
     run_ptref(["--scene-file", scene, "--base", str(tmp_path), "dump-scene", str(tmp_path / "ref.ptbs")])
     with open(tmp_path / "ref.ptbs", "rb") as f:
         assert mine == f.read()
+
+
+# ---- TGA textures (decode_tga) against stb_image in the compiled reference ---------------------------------------------------
+def _tga_bytes(px, rle, top_down):
+    """px: (H, W, C) uint8 in RGB(A) / grey order; the file stores BGR(A), rows bottom-up unless top_down"""
+    import struct
+    h, w, c = px.shape
+    rows = px if top_down else px[::-1]
+    data = rows[..., [2, 1, 0, 3][:c]] if c >= 3 else rows
+    flat = np.ascontiguousarray(data, np.uint8).reshape(-1, c)
+    hdr = struct.pack("<BBBHHBHHHHBB", 0, 0, (3 if c == 1 else 2) + (8 if rle else 0), 0, 0, 0, 0, 0, w, h, 8 * c, (0x20 if top_down else 0) | (8 if c == 4 else 0))
+    if not rle:
+        return hdr + flat.tobytes()
+    out, i, n = b"", 0, len(flat)
+    while i < n:  # alternate run packets and raw packets, crossing row ends on purpose
+        run = 1
+        while i + run < n and run < 128 and (flat[i + run] == flat[i]).all():
+            run += 1
+        if run > 1:
+            out += bytes([0x80 | (run - 1)]) + flat[i].tobytes()
+            i += run
+        else:
+            k = min(5, n - i)
+            out += bytes([k - 1]) + flat[i:i + k].tobytes()
+            i += k
+    return hdr + out
+
+
+def _tga_tree(d):
+    rng = np.random.default_rng(21)
+    os.makedirs(os.path.join(d, "objs"))
+    mtl, obj = "", "mtllib m.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nvt 0 0\nvt 1 0\nvt 0 1\n"
+    for i, (c, rle, top) in enumerate([(3, False, False), (4, False, True), (1, False, False), (3, True, False), (4, True, True), (1, True, True)]):
+        px = rng.integers(0, 4, (6 + i, 9 - i, c)).astype(np.uint8) * 60  # few values: real runs for the RLE flavours
+        with open(os.path.join(d, "objs", f"t{i}.tga"), "wb") as f:
+            f.write(_tga_bytes(px, rle, top))
+        mtl += f"newmtl m{i}\nKd 0.5 0.5 0.5\nmap_Kd t{i}.tga\n"
+        obj += f"usemtl m{i}\nf 1/1/1 2/2/1 3/3/1\n"
+    with open(os.path.join(d, "objs", "m.mtl"), "w") as f:
+        f.write(mtl)
+    with open(os.path.join(d, "objs", "a.obj"), "w") as f:
+        f.write(obj)
+    with open(os.path.join(d, "s.scene"), "w") as f:
+        f.write("[Models]\nfile: objs/a.obj\npos: 0,0,0\nscale: 1,1,1\n")
+    return os.path.join(d, "s.scene")
+
+
+def test_tga_textures_decode(ptb, tmp_path):
+    scene = _tga_tree(str(tmp_path))
+    _convert(ptb, scene, str(tmp_path / "s.ptbs"), str(tmp_path))
+    tex = ptb.scenes.read_ptbs(str(tmp_path / "s.ptbs"))["textures"]
+    rng = np.random.default_rng(21)
+    for i, c in enumerate([3, 4, 1, 3, 4, 1]):  # the generator's pixels, row 0 = top, whatever the file's row order / packing
+        px = rng.integers(0, 4, (6 + i, 9 - i, c)).astype(np.uint8) * 60
+        want = np.full((6 + i, 9 - i, 4), 255, np.uint8)
+        want[..., :3] = px[..., :3] if c >= 3 else px
+        if c == 4:
+            want[..., 3] = px[..., 3]
+        assert (tex[i] == want.astype(np.float32) / np.float32(255)).all(), i
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref/ptref not built (needs the reference sources)")
+def test_tga_textures_equal_stb_image_in_the_compiled_reference(ptb, tmp_path):
+    scene = _tga_tree(str(tmp_path))
+    mine = _convert(ptb, scene, str(tmp_path / "mine.ptbs"), str(tmp_path))
+    run_ptref(["--scene-file", scene, "--base", str(tmp_path), "dump-scene", str(tmp_path / "ref.ptbs")])
+    with open(tmp_path / "ref.ptbs", "rb") as f:
+        assert mine == f.read()
