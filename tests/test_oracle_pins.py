@@ -9,11 +9,12 @@
 3. The reference's own cross-mode consistency: ALL == BVH == TWO_PLANE on tmax.
 """
 import os
+import tempfile
 
 import numpy as np
 import pytest
 
-from oracle_lib import MODE_ALL, MODE_BVH, MODE_SUB_BEAMS, MODE_TWO_PLANE, Oracle, have_ref, ptref_primary_hits, ptref_render
+from oracle_lib import MODE_ALL, MODE_BVH, MODE_SUB_BEAMS, MODE_TWO_PLANE, Oracle, have_ref, ptref_primary_hits, ptref_render, run_ptref
 
 MODES = [MODE_ALL, MODE_BVH, MODE_TWO_PLANE, MODE_SUB_BEAMS]
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cornel_ref_64.npz")
@@ -194,5 +195,33 @@ def test_live_two_model_scene_with_a_flat_mesh(tmp_path, mode):
     rimg, rec, _ = ptref_render(ptbs, W, H, mode, 2, 5, 1)
     assert (_bits(t) == _bits(rt)).all() and (tri == rtri).all() and (mat == rmat).all()
     assert 0.1 < float((mat == mat.max()).mean()) < 0.5  # the flat mesh is in view
+    assert (_bits(img) == _bits(rimg)).all()
+    assert st["tri_tests"] == rec["tri_tests"] and st["as_tests"] == rec["as_tests"]
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref/ptref not built (needs the reference sources)")
+@pytest.mark.parametrize("mode", [MODE_BVH, MODE_TWO_PLANE])
+def test_live_from_scene_text_end_to_end(tmp_path, mode):
+    """The whole chain against the unmodified reference started from TEXT: the reference reads .scene / OBJ / MTL / PNG with
+    its own loader (tinyobjloader, stb_image) and renders; the restatement renders the .ptbs this repo's loader wrote from the
+    same text (tests/test_gpu_scene_file.py's room: a PNG-textured wall, a lamp, quads).  Frames and counters must agree."""
+    import ptb_b200
+    from test_gpu_scene_file import _tree
+    d = str(tmp_path)
+    scene, ptbs = _tree(d), os.path.join(d, "s.ptbs")
+    ptb_b200.convert_scene_file(scene, ptbs, base_dir=d)
+    W, H, spp = 64, 48, 2
+    o = Oracle(ptbs)
+    o.build(grid=(mode == MODE_TWO_PLANE))
+    o.configure(W, H, mode, nee=1, max_depth=4)
+    img, _, _, st = o.render(spp)
+    o.close()
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "img.bin")
+        recs = run_ptref(["--scene-file", scene, "--base", d, "--mode", mode, "--width", W, "--height", H, "--spp", spp, "--max-depth", 4,
+                          "--nee", 1, "render", out])
+        rimg = np.fromfile(out, np.float32).reshape(H, W, 4)
+    rec = [r for r in recs if r["cmd"] == "render"][0]
+    assert float(rimg[..., :3].max()) > 0
     assert (_bits(img) == _bits(rimg)).all()
     assert st["tri_tests"] == rec["tri_tests"] and st["as_tests"] == rec["as_tests"]
