@@ -60,6 +60,17 @@ def _run(cmd):
     return r.stdout
 
 
+def _have_zlib():
+    """zlib header + link library present?  (PNG textures need them; without, ptb_png.cpp is built with PTB_NO_ZLIB.)"""
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        src = os.path.join(d, "z.cpp")
+        with open(src, "w") as f:
+            f.write("#include <zlib.h>\nint main() { return zlibVersion() == nullptr; }\n")
+        r = subprocess.run(["g++", src, "-o", os.path.join(d, "z"), "-lz"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        return r.returncode == 0
+
+
 def build_native(force=False, verbose=False, defines=(), out=None):
     """Compile csrc/ into libptb.so if sources are newer than the library.  `defines`/`out` build a
     tuning variant beside it (loaded with PTB_LIB=<path>; scripts/ only)."""
@@ -67,7 +78,8 @@ def build_native(force=False, verbose=False, defines=(), out=None):
     out = out or OUT
     objdir = OBJDIR + ("_variant" if variant else "")
     os.makedirs(objdir, exist_ok=True)
-    flags = NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else [])
+    zlib = _have_zlib()
+    flags = NVCC_FLAGS + [f"-D{d}" for d in defines] + ([] if zlib else ["-DPTB_NO_ZLIB"]) + (["-Xptxas", "-v"] if verbose else [])
     jobs = []
     for s in SOURCES:
         src = os.path.join(CSRC, s)
@@ -81,5 +93,5 @@ def build_native(force=False, verbose=False, defines=(), out=None):
         logs = list(ex.map(_run, jobs))
     if verbose:
         print("\n".join(logs))
-    _run([_nvcc(), "-shared", "-Xcompiler", "-pthread", "-o", out] + objs + ["-lz"])  # zlib: PNG textures (ptb_png.cpp)
+    _run([_nvcc(), "-shared", "-Xcompiler", "-pthread", "-o", out] + objs + (["-lz"] if zlib else []))  # zlib: PNG textures (ptb_png.cpp)
     return out

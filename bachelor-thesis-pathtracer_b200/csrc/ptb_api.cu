@@ -9,6 +9,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -21,8 +23,15 @@
 #include "ptb_lbvh.h"
 #include "ptb_kernels.cuh"
 #include "ptb_mega.cuh"
+// k_pool (warp pools) and k_duo (two paths per lane): measured and rejected in round 1.  Kept as
+// scripts/ variants behind a build define (scripts/build_variants.py x=PTB_WITH_ALT_SCHEDULERS), not in the product library.
+#ifdef PTB_WITH_ALT_SCHEDULERS
 #include "ptb_pool.cuh"
 #include "ptb_duo.cuh"
+#else
+#define PTB_POOL_MINBLOCKS 8
+#define PTB_DUO_MINBLOCKS 8
+#endif
 
 #ifndef PTB_POOL_NP
 #define PTB_POOL_NP 64 /* paths per warp pool */
@@ -65,7 +74,7 @@ struct ptb_ctx {
     int poolCtas = PTB_POOL_MINBLOCKS;
     int duoCtas = PTB_DUO_MINBLOCKS; // PTB_DUO_CTAS
     int duoLogicKeep = 24, duoSampleKeep = 16, duoWalkMin = 20, duoRefillMin = 8, duoLeafKeep = 8; // PTB_DUO_LOGIC / _SAMPLE / _WALK / _REFILL
-    ShadowRec *dShScratch = nullptr; // NEE shadow records of the pool kernel (grid warps x NP)
+    void *dShScratch = nullptr; // NEE shadow records of the pool kernel (grid warps x NP)
     size_t shScratchN = 0;
     int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
     int logicKeep = 26;
@@ -74,6 +83,7 @@ struct ptb_ctx {
     int leafMax = 3;    // PTB_LEAF_MAX: triangles per BVH leaf (<= 16)
     int megaChunk = 0;  // PTB_MEGA_CHUNK: samples per work item, 0 = chosen from pixels/lanes // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it
     bool pendingRender = false, asyncRequested = false; // ptb_render_async: a path-kernel launch awaits ptb_sync
+    bool matsChecked = false;   // every triangle's material index lies inside the material table (check_mode_ready)
     bool uniformSamples = true; // every owned pixel has the same sample count (false after ptb_write_state)
     int beamMaxDepth = 12; // guard on the reference's unbounded Subbeam recursion, ptb_set_build_limits  // refill a warp's idle lanes when fewer than this many are still walking
     cudaStream_t stream = nullptr;
@@ -287,6 +297,12 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     cudaEventCreate(&c->evStart);
     cudaEventCreate(&c->evStop);
     if (const char *e = getenv("PTB_MEGA")) c->useMega = std::max(0, std::min(3, atoi(e)));
+#ifndef PTB_WITH_ALT_SCHEDULERS
+    if (c->useMega > 1) {
+        delete c;
+        return fail(nullptr, PTB_ERR_INVALID, "PTB_MEGA=2/3 (k_pool / k_duo) are not in this build: compile with -DPTB_WITH_ALT_SCHEDULERS");
+    }
+#endif
     if (const char *e = getenv("PTB_DUO_CTAS")) c->duoCtas = std::max(1, std::min(PTB_DUO_MINBLOCKS, atoi(e)));
     if (const char *e = getenv("PTB_DUO_LOGIC")) c->duoLogicKeep = std::max(1, std::min(33, atoi(e)));
     if (const char *e = getenv("PTB_DUO_SAMPLE")) c->duoSampleKeep = std::max(1, std::min(33, atoi(e)));
@@ -374,7 +390,7 @@ extern "C" const char *ptb_last_error(const ptb_ctx *c) { return c ? c->err.c_st
 // =============================================================================================
 // scene
 // =============================================================================================
-extern "C" int ptb_upload_triangles(ptb_ctx *c, const float *pos9, const float *nrm9, const float *uv6, const int32_t *mat, uint64_t n) {
+static int ptb_upload_triangles_impl(ptb_ctx *c, const float *pos9, const float *nrm9, const float *uv6, const int32_t *mat, uint64_t n) {
     GUARD(c);
     if (n && (!pos9 || !nrm9 || !mat)) return fail(c, PTB_ERR_INVALID, "null triangle arrays");
     if (n >= (1ull << 27)) return fail(c, PTB_ERR_INVALID, "more than 2^27 triangles");
@@ -383,6 +399,7 @@ extern "C" int ptb_upload_triangles(ptb_ctx *c, const float *pos9, const float *
     c->pos9.assign(pos9, pos9 + 9 * n);
     c->nrm9.assign(nrm9, nrm9 + 9 * n);
     c->mat.assign(mat, mat + n);
+    c->matsChecked = false;
     c->bvhBuilt = c->gridBuilt = c->beamBuilt = false;
     c->refBvhLoaded = c->useRefBvh = false; // its indices refer to the previous triangle list
     return PTB_OK;
@@ -408,7 +425,7 @@ static int upload_lights(ptb_ctx *c) {
     return PTB_OK;
 }
 
-extern "C" int ptb_upload_objects(ptb_ctx *c, const ptbs_object *objects, uint32_t n) {
+static int ptb_upload_objects_impl(ptb_ctx *c, const ptbs_object *objects, uint32_t n) {
     GUARD(c);
     if (n && !objects) return fail(c, PTB_ERR_INVALID, "null objects");
     c->objects.assign(objects, objects + n);
@@ -448,11 +465,12 @@ static int upload_matdev(ptb_ctx *c) {
     return PTB_OK;
 }
 
-extern "C" int ptb_upload_materials(ptb_ctx *c, const ptbs_material *materials, uint32_t n) {
+static int ptb_upload_materials_impl(ptb_ctx *c, const ptbs_material *materials, uint32_t n) {
     GUARD(c);
     if (n && !materials) return fail(c, PTB_ERR_INVALID, "null materials");
     if (n != c->materials.size()) c->matTex.clear(); // another material list: the bindings no longer apply
     c->materials.assign(materials, materials + n);
+    c->matsChecked = false;
     if (int r = upload_matdev(c)) return r;
     return upload_lights(c);
 }
@@ -481,7 +499,7 @@ static int upload_uv(ptb_ctx *c) {
 // (texture.h:7-11, byte/255.0f as loadTexture leaves them, texture.cpp:33-50).  The albedo copy is gamma-expanded
 // here with the host libm — the reference applies powf(c, 2.2f) to every texel it reads (shader.cpp:214) — so the
 // kernel never evaluates powf; normal maps are kept raw.
-extern "C" int ptb_upload_textures(ptb_ctx *c, const ptb_texture *textures, uint32_t n_textures, const int32_t *material_tex2, uint32_t n_materials) {
+static int ptb_upload_textures_impl(ptb_ctx *c, const ptb_texture *textures, uint32_t n_textures, const int32_t *material_tex2, uint32_t n_materials) {
     GUARD(c);
     SETTLE(c);
     if (n_textures && !textures) return fail(c, PTB_ERR_INVALID, "null textures");
@@ -517,6 +535,13 @@ extern "C" int ptb_upload_textures(ptb_ctx *c, const ptb_texture *textures, uint
     }
     c->matTex.assign(material_tex2, material_tex2 + 2 * (size_t)n_materials);
     devFree(c->dTexTable); devFree(c->dTexels);
+    if (n_textures == 0) { // unbind everything
+        c->texData.clear();
+        c->A.tex = nullptr;
+        c->A.texels = nullptr;
+        if (int r = upload_matdev(c)) return r;
+        return upload_uv(c);
+    }
     CK(cudaMalloc(&c->dTexTable, std::max<size_t>(1, table.size()) * sizeof(TexDev)));
     CK(cudaMalloc(&c->dTexels, std::max<size_t>(1, pool.size()) * sizeof(float4)));
     if (!table.empty()) CK(cudaMemcpy(c->dTexTable, table.data(), table.size() * sizeof(TexDev), cudaMemcpyHostToDevice));
@@ -554,7 +579,7 @@ extern "C" int ptb_set_camera_basis(ptb_ctx *c, const float origin[3], const flo
     return PTB_OK;
 }
 
-extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
+static int ptb_load_ptbs_impl(ptb_ctx *c, const char *path) {
     GUARD(c);
     FILE *f = path ? fopen(path, "rb") : nullptr;
     if (!f) return fail(c, PTB_ERR_IO, std::string("cannot open ") + (path ? path : "(null)"));
@@ -563,7 +588,20 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
         fclose(f);
         return fail(c, PTB_ERR_IO, "not a .ptbs v1/v2 container");
     }
+    // the header is untrusted: its counts must fit the file before anything is allocated from them
     size_t n = h.n_tris;
+    {
+        const long at = ftell(f);
+        fseek(f, 0, SEEK_END);
+        const uint64_t fileBytes = (uint64_t)ftell(f);
+        fseek(f, at, SEEK_SET);
+        const uint64_t need = (uint64_t)sizeof h + (uint64_t)h.n_tris * (9 + 9 + 6 + 1) * 4 + (uint64_t)h.n_objects * sizeof(ptbs_object) +
+                              (uint64_t)h.n_materials * sizeof(ptbs_material);
+        if (h.n_tris >= (1ull << 27) || h.n_objects > (1u << 24) || h.n_materials > (1u << 24) || need > fileBytes) {
+            fclose(f);
+            return fail(c, PTB_ERR_IO, "corrupt .ptbs header: element counts exceed the file size (or 2^27 triangles)");
+        }
+    }
     std::vector<float> pos(n * 9), nrm(n * 9), uv(n * 6);
     std::vector<int32_t> mat(n);
     std::vector<ptbs_object> objs(h.n_objects);
@@ -593,7 +631,9 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
     if ((r = ptb_upload_materials(c, mats.data(), (uint32_t)mats.size()))) return r;
     if ((r = ptb_upload_objects(c, objs.data(), (uint32_t)objs.size()))) return r;
     for (size_t k = 0; k < tex.size(); ++k) tex[k].rgba = texData[k].data();
-    if (!tex.empty() && (r = ptb_upload_textures(c, tex.data(), (uint32_t)tex.size(), matTex.data(), (uint32_t)mats.size()))) return r;
+    // always re-bind: a scene without textures must not inherit the bindings of the scene this context held before
+    if (tex.empty()) std::fill(matTex.begin(), matTex.end(), -1);
+    if ((r = ptb_upload_textures(c, tex.data(), (uint32_t)tex.size(), matTex.data(), (uint32_t)mats.size()))) return r;
     ptb_camera cam{};
     for (int k = 0; k < 3; ++k) {
         cam.origin[k] = h.cam_pos[k];
@@ -606,7 +646,7 @@ extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
 }
 
 // .scene / OBJ / MTL text -> the same uploads (csrc/ptb_scene_loader.cpp)
-extern "C" int ptb_load_scene_file(ptb_ctx *c, const char *scene_file, const char *base_dir, int flags) {
+static int ptb_load_scene_file_impl(ptb_ctx *c, const char *scene_file, const char *base_dir, int flags) {
     GUARD(c);
     if (!scene_file) return fail(c, PTB_ERR_INVALID, "null scene file");
     LoadedScene s;
@@ -616,10 +656,12 @@ extern "C" int ptb_load_scene_file(ptb_ctx *c, const char *scene_file, const cha
     if ((r = ptb_upload_triangles(c, s.pos9.data(), s.nrm9.data(), s.uv6.data(), s.mat.data(), s.triangles()))) return r;
     if ((r = ptb_upload_materials(c, s.materials.data(), (uint32_t)s.materials.size()))) return r;
     if ((r = ptb_upload_objects(c, s.objects.data(), (uint32_t)s.objects.size()))) return r;
-    if (!s.texels.empty()) {
+    {
         std::vector<ptb_texture> tex;
         for (const auto &t : s.texels) tex.push_back(ptb_texture{t.rgba.data(), t.width, t.height});
-        if ((r = ptb_upload_textures(c, tex.data(), (uint32_t)tex.size(), s.mat_tex.data(), (uint32_t)s.materials.size()))) return r;
+        std::vector<int32_t> bind(2 * s.materials.size(), -1); // no textures: clear what an earlier scene bound
+        if (!tex.empty() && s.mat_tex.size() == bind.size()) bind = s.mat_tex;
+        if ((r = ptb_upload_textures(c, tex.data(), (uint32_t)tex.size(), bind.data(), (uint32_t)s.materials.size()))) return r;
     }
     ptb_camera cam{};
     for (int k = 0; k < 3; ++k) {
@@ -649,7 +691,7 @@ extern "C" int ptb_convert_scene_file(const char *scene_file, const char *base_d
 // =============================================================================================
 // structures
 // =============================================================================================
-extern "C" int ptb_build_bvh(ptb_ctx *c) {
+static int ptb_build_bvh_impl(ptb_ctx *c) {
     GUARD(c);
     const uint64_t n = c->mat.size();
     const auto t0 = std::chrono::steady_clock::now();
@@ -712,7 +754,7 @@ extern "C" int ptb_build_bvh(ptb_ctx *c) {
 // constructBVH on the device (ptb_lbvh.cu): the triangles go up once in reference order, everything else —
 // keys, sort, hierarchy, boxes, nodes, leaf-ordered arrays — is produced in HBM.  The only host copies
 // kept are the leaf order (Subbeam builder input) and the scene bounds.
-extern "C" int ptb_build_bvh_gpu(ptb_ctx *c) {
+static int ptb_build_bvh_gpu_impl(ptb_ctx *c) {
     GUARD(c);
     SETTLE(c);
     const uint64_t n = c->mat.size();
@@ -772,7 +814,7 @@ extern "C" int ptb_bvh_depth(const ptb_ctx *c) { return (c && c->bvhBuilt) ? c->
 // The reference's own BVH — what constructBVH (bvh.cpp:222-390) left behind getNode / getNodeAABB / bvhGetTrisIndex
 // (bvh.h:27-29) and Object::root — for count-exact traversal (refbvh_closest).  Validated here, because the kernel
 // trusts it: every link in range, no cycles, and the worst-case stack of the reference's push order below PTB_STACK.
-extern "C" int ptb_upload_ref_bvh(ptb_ctx *c, const ptb_ref_bvh_node *nodes, uint32_t n_nodes, const uint32_t *indices, uint32_t n_indices,
+static int ptb_upload_ref_bvh_impl(ptb_ctx *c, const ptb_ref_bvh_node *nodes, uint32_t n_nodes, const uint32_t *indices, uint32_t n_indices,
                                   const int32_t *object_roots, uint32_t n_objects, int32_t scene_root) {
     GUARD(c);
     SETTLE(c);
@@ -997,6 +1039,16 @@ static int reset_frame(ptb_ctx *c, int reseed) {
 }
 
 static int check_mode_ready(ptb_ctx *c, int mode) {
+    // every kernel reads A.mats[material id of the hit triangle]: an id outside the material table is rejected here, once per
+    // (triangles, materials) pair, instead of becoming an out-of-bounds read on the device
+    if (!c->matsChecked) {
+        const int32_t nm = (int32_t)c->materials.size();
+        for (size_t i = 0; i < c->mat.size(); ++i)
+            if (c->mat[i] < 0 || c->mat[i] >= nm)
+                return fail(c, PTB_ERR_INVALID, "triangle " + std::to_string(i) + " has material index " + std::to_string(c->mat[i]) +
+                                                    " outside the " + std::to_string(nm) + " uploaded materials");
+        c->matsChecked = true;
+    }
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (it also lays out the triangles)");
     if (mode == PTB_MODE_TWO_PLANE && !c->gridBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_subgrid first");
     if (mode == PTB_MODE_SUB_BEAMS && !c->beamBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_subbeams first");
@@ -1180,6 +1232,7 @@ int render_mega(ptb_ctx *c, int add) {
     CK(cudaMemsetAsync(c->dCounters + 8, 0, sizeof(unsigned long long), c->stream));
     CK(cudaEventRecord(c->evStart, c->stream));
     bool launched = false;
+#ifdef PTB_WITH_ALT_SCHEDULERS
     if constexpr (MODE != 4) {
     if (pool) {
         launched = true;
@@ -1198,13 +1251,14 @@ int render_mega(ptb_ctx *c, int add) {
             CK(cudaFuncSetAttribute(k_pool<MODE, COUNT, PTB_POOL_NP>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attrSet[MODE][COUNT ? 1 : 0] = true;
         }
-        k_pool<MODE, COUNT, PTB_POOL_NP><<<grid, kThreads, smem, c->stream>>>(P, c->S, c->A, c->F, M, nee ? c->dShScratch : nullptr);
+        k_pool<MODE, COUNT, PTB_POOL_NP><<<grid, kThreads, smem, c->stream>>>(P, c->S, c->A, c->F, M, nee ? (ShadowRec *)c->dShScratch : nullptr);
     } else if (duo) {
         launched = true;
         if (P.nee && P.n_lights > 0) k_duo<MODE, COUNT, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
         else k_duo<MODE, COUNT, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);
     }
     }
+#endif
     if (!launched) {
         const bool nee = P.nee && P.n_lights > 0;
         const bool tex = c->haveTextures; // a material binds a texture: the build of the kernel with the texture branches
@@ -1564,7 +1618,7 @@ static int mirror_gpu_bvh(ptb_ctx *c) {
     return PTB_OK;
 }
 
-extern "C" int ptb_build_subgrid(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
+static int ptb_build_subgrid_impl(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
     GUARD(c);
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (the Subgrid hierarchy derives from the BVH)");
     if (gs < 1 || gs > 64 || os < 1 || os > 64) return fail(c, PTB_ERR_INVALID, "grid sizes must be 1..64");
@@ -1593,7 +1647,7 @@ extern "C" int ptb_build_subgrid(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t 
 // constructGrid with the channel population on the device (ptb_grid_gpu.cu): the hierarchy is walked on the host
 // (microseconds per grid), every (grid, channel) pair is one GPU thread.  Produces the same pools as
 // ptb_build_subgrid, byte for byte (tests/test_gpu_builders.py compares the digests).
-extern "C" int ptb_build_subgrid_gpu(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
+static int ptb_build_subgrid_gpu_impl(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
     GUARD(c);
     SETTLE(c);
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (the Subgrid hierarchy derives from the BVH)");
@@ -1671,7 +1725,7 @@ extern "C" uint64_t ptb_structure_digest(ptb_ctx *c, int mode) {
 }
 extern "C" double ptb_last_build_device_ms(const ptb_ctx *c) { return c ? c->lastBuildDeviceMs : 0.0; }
 
-extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
+static int ptb_build_subbeams_impl(ptb_ctx *c, uint32_t gs, uint32_t m) {
     GUARD(c);
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (it lays out the triangles)");
     if (gs < 1 || gs > 64) return fail(c, PTB_ERR_INVALID, "grid size must be 1..64");
@@ -1711,7 +1765,7 @@ extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
 
 // buildGridsWithSubBeams on the device (ptb_beam_gpu.cu): one data-parallel step per tree depth instead of the host's
 // depth-first recursion; same pools, byte for byte (ptb_structure_digest, tests/test_gpu_subbeam_build.py).
-extern "C" int ptb_build_subbeams_gpu(ptb_ctx *c, uint32_t gs, uint32_t m) {
+static int ptb_build_subbeams_gpu_impl(ptb_ctx *c, uint32_t gs, uint32_t m) {
     GUARD(c);
     SETTLE(c);
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (it lays out the triangles)");
@@ -1754,4 +1808,62 @@ extern "C" int ptb_build_subbeams_gpu(ptb_ctx *c, uint32_t gs, uint32_t m) {
     c->lastBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     c->lastBuildDeviceMs = D.ms;
     return PTB_OK;
+}
+
+// =============================================================================================
+// exception barrier of the entry points that allocate from caller- or file-supplied sizes
+// =============================================================================================
+// C++ exceptions (std::bad_alloc / length_error from a corrupt count, anything a builder throws) must not cross the extern "C"
+// boundary: under ctypes or inside the facade they would abort the host process.  They become a status + ptb_last_error.
+template <typename F>
+static int guarded(ptb_ctx *c, F &&f) {
+    try {
+        return f();
+    } catch (const std::bad_alloc &) {
+        return fail(c, PTB_ERR_INVALID, "out of host memory (corrupt element count?)");
+    } catch (const std::exception &e) {
+        return fail(c, PTB_ERR_INVALID, std::string("exception: ") + e.what());
+    } catch (...) {
+        return fail(c, PTB_ERR_INVALID, "unknown C++ exception");
+    }
+}
+extern "C" int ptb_upload_triangles(ptb_ctx *c, const float *pos9, const float *nrm9, const float *uv6, const int32_t *mat, uint64_t n) {
+    return guarded(c, [&]() { return ptb_upload_triangles_impl(c, pos9, nrm9, uv6, mat, n); });
+}
+extern "C" int ptb_upload_objects(ptb_ctx *c, const ptbs_object *objects, uint32_t n) {
+    return guarded(c, [&]() { return ptb_upload_objects_impl(c, objects, n); });
+}
+extern "C" int ptb_upload_materials(ptb_ctx *c, const ptbs_material *materials, uint32_t n) {
+    return guarded(c, [&]() { return ptb_upload_materials_impl(c, materials, n); });
+}
+extern "C" int ptb_upload_textures(ptb_ctx *c, const ptb_texture *textures, uint32_t n_textures, const int32_t *material_tex2, uint32_t n_materials) {
+    return guarded(c, [&]() { return ptb_upload_textures_impl(c, textures, n_textures, material_tex2, n_materials); });
+}
+extern "C" int ptb_load_ptbs(ptb_ctx *c, const char *path) {
+    return guarded(c, [&]() { return ptb_load_ptbs_impl(c, path); });
+}
+extern "C" int ptb_load_scene_file(ptb_ctx *c, const char *scene_file, const char *base_dir, int flags) {
+    return guarded(c, [&]() { return ptb_load_scene_file_impl(c, scene_file, base_dir, flags); });
+}
+extern "C" int ptb_build_bvh(ptb_ctx *c) {
+    return guarded(c, [&]() { return ptb_build_bvh_impl(c); });
+}
+extern "C" int ptb_build_bvh_gpu(ptb_ctx *c) {
+    return guarded(c, [&]() { return ptb_build_bvh_gpu_impl(c); });
+}
+extern "C" int ptb_upload_ref_bvh(ptb_ctx *c, const ptb_ref_bvh_node *nodes, uint32_t n_nodes, const uint32_t *indices, uint32_t n_indices,
+                                  const int32_t *object_roots, uint32_t n_objects, int32_t scene_root) {
+    return guarded(c, [&]() { return ptb_upload_ref_bvh_impl(c, nodes, n_nodes, indices, n_indices, object_roots, n_objects, scene_root); });
+}
+extern "C" int ptb_build_subgrid(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
+    return guarded(c, [&]() { return ptb_build_subgrid_impl(c, gs, os, m); });
+}
+extern "C" int ptb_build_subgrid_gpu(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t m) {
+    return guarded(c, [&]() { return ptb_build_subgrid_gpu_impl(c, gs, os, m); });
+}
+extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
+    return guarded(c, [&]() { return ptb_build_subbeams_impl(c, gs, m); });
+}
+extern "C" int ptb_build_subbeams_gpu(ptb_ctx *c, uint32_t gs, uint32_t m) {
+    return guarded(c, [&]() { return ptb_build_subbeams_gpu_impl(c, gs, m); });
 }

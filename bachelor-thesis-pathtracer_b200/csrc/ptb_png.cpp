@@ -13,7 +13,17 @@
 #include <cstdlib>
 #include <cstring>
 
+// zlib is optional at build time: build.py probes for the header and the link library and defines PTB_NO_ZLIB when either is
+// missing, so a box without the zlib development files still builds the renderer (PNG textures are then refused with a
+// clear message; hand texels to ptb_upload_textures instead).
+#if !defined(PTB_NO_ZLIB) && defined(__has_include)
+#if !__has_include(<zlib.h>)
+#define PTB_NO_ZLIB 1
+#endif
+#endif
+#ifndef PTB_NO_ZLIB
 #include <zlib.h>
+#endif
 
 namespace ptb {
 namespace {
@@ -28,6 +38,11 @@ int paeth(int a, int b, int c) {
 } // namespace
 
 bool decode_png(const std::string &path, std::vector<unsigned char> &rgba, int &width, int &height, std::string &err) {
+#ifdef PTB_NO_ZLIB
+    (void)rgba; (void)width; (void)height;
+    err = path + ": PNG textures are unsupported in this build of libptb (compiled without zlib)";
+    return false;
+#else
     std::vector<unsigned char> file;
     {
         FILE *f = fopen(path.c_str(), "rb");
@@ -166,6 +181,7 @@ bool decode_png(const std::string &path, std::vector<unsigned char> &rgba, int &
         }
     }
     return true;
+#endif
 }
 
 // Truevision TGA, the subset stb_image's loader (stbi__tga_load) is asked for by the reference's kind of assets: image types 2

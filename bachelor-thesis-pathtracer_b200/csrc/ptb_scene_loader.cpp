@@ -714,6 +714,10 @@ bool load_obj(const std::string &file, const float position[3], const float size
 
     const size_t nv = obj.v.size() / 3, nn = obj.vn.size() / 3, nt = obj.vt.size() / 2;
     for (const Shape &sh : obj.shapes) { // :89-172
+        // a group whose faces were all dropped (degenerate, or quads with an invalid index) is still pushed by tinyobjloader
+        // with an empty mesh; the reference then reads material_ids[0] of an empty vector (object.cpp:92, undefined
+        // behaviour).  Such a shape carries no triangle: skipped here.
+        if (sh.material_ids.empty() || sh.corners.empty()) continue;
         sc.log += "loaded: " + sh.name + "\n";
         const int start = (int)sc.triangles();
         int shape_mat = sh.material_ids[0];

@@ -23,7 +23,19 @@ build container (the reference sources do not travel); the outputs do:
         img_m{mode}_nee{0,1}_d{0,4}_l{0,1}   fp32 image (l = the emissive cube carries a texture too)
         scene_sha256_l{0,1}           digest of the generated textures + uv (the generator is bit-reproducible)
 
-    python tests/golden/make_golden.py [--lucy [--lucy-two-plane]] [--textured]
+  tests/golden/configs_ref.npz         (--configs [--lucy-subgrid]) the BASELINE.json configurations at their own sizes
+        c0_tri, c0_t_sha256           config 0: Cornell 512x512, BVH: primary hit ids and the digest of the hit distances
+        c0_img_sha256, c0_thumb, c0_counts    ... the fp32 frame after 1 spp, max_depth 2, NEE off: digest of the bit
+                                      pattern, 8x8 block means (for a readable diff), [find_calls, rays_traversed,
+                                      rays_unique, tri_tests, as_tests] of the unmodified trace(true)
+        c1_*                          config 1 at the first 4 of its 64 spp: Cornell 1024x1024, max_depth 5
+        lucy_bvh_*                    Lucy stand-in 1920x1080, 2 spp, max_depth 9, BVH (scene digest: lucy_scene_sha256)
+        lucy_grid_*                   (--lucy-subgrid, 14 min / 11 GB) the same through the reference's Subgrids gs 8 os 8 m 50;
+                                      lucy_grid_img_f16 = the frame in half precision (the GPU builds its grids from another
+                                      hierarchy, so this frame is compared with a stated tolerance, not by digest)
+  tests/golden/cornel_rmse_ref.npz     (--rmse) config 1's converged-image bar, see rmse_golden()
+
+    python tests/golden/make_golden.py [--lucy [--lucy-two-plane]] [--textured] [--configs [--lucy-subgrid]] [--rmse]
 """
 import os
 import sys
@@ -92,7 +104,75 @@ def textured():
     print("wrote cornel_textured_ref_48.npz", len(out), "entries")
 
 
+def thumb(img, k=8):
+    h, w = img.shape[0] // k * k, img.shape[1] // k * k
+    return img[:h, :w, :3].astype(np.float64).reshape(h // k, k, w // k, k, 3).mean(axis=(1, 3)).astype(np.float32)
+
+
+def counts(rec):
+    return np.array([rec[k] for k in ("find_calls", "rays_traversed", "rays_unique", "tri_tests", "as_tests")], np.uint64)
+
+
+def configs():
+    import hashlib
+    import tempfile
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    import ptb_b200
+    sc = ptb_b200.scenes
+    path = os.path.join(HERE, "configs_ref.npz")
+    out = dict(np.load(path)) if os.path.isfile(path) else {}
+    cornel = os.path.join(HERE, "cornel.ptbs")
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+    def frame(prefix, ptbs, W, H, spp, depth, mode=1, extra=()):
+        img, rec, _ = ptref_render(ptbs, W, H, mode, spp, depth, 0, extra=extra)
+        out[prefix + "_img_sha256"] = sha(img)
+        out[prefix + "_thumb"] = thumb(img)
+        out[prefix + "_counts"] = counts(rec)
+        out[prefix + "_trace_ms"] = rec["trace_ms"]
+        print(prefix, out[prefix + "_img_sha256"], out[prefix + "_counts"], rec["trace_ms"], "ms")
+        return img
+
+    if "--lucy-subgrid" not in sys.argv:
+        t, tri, mat, rays, _ = ptref_primary_hits(cornel, 512, 512, 1)
+        out["c0_tri"], out["c0_t_sha256"] = tri, sha(t)
+        frame("c0", cornel, 512, 512, 1, 2)
+        frame("c1", cornel, 1024, 1024, 4, 5)
+    scene = sc.lucy_standin(sc.read_ptbs(cornel))
+    out["lucy_scene_sha256"] = hashlib.sha256(scene["pos"].tobytes()).hexdigest()
+    with tempfile.TemporaryDirectory() as d:
+        ptbs = os.path.join(d, "lucy.ptbs")
+        sc.write_ptbs(ptbs, scene)
+        if "--lucy-subgrid" in sys.argv:
+            img = frame("lucy_grid", ptbs, 1920, 1080, 2, 9, mode=2, extra=["--gs", 8, "--os", 8, "--m", 50])
+            out["lucy_grid_img_f16"] = np.clip(img[..., :3], 0, 65000).astype(np.float16)
+        else:
+            frame("lucy_bvh", ptbs, 1920, 1080, 2, 9)
+    np.savez_compressed(path, **out)
+    print("wrote", path, sorted(out))
+
+
+def rmse_golden():
+    """config 1's converged-image bar: the reference's own 4096-spp frame (stored in half precision, radiance
+    clamped to 64) and the RMSE of its 64-spp frame against it.  512x512 instead of 1024x1024: 4096 spp of the reference is
+    18 CPU-minutes at this size on 8 cores, 70 at the full size; the bar is per pixel."""
+    path = os.path.join(HERE, "cornel_rmse_ref.npz")
+    cornel = os.path.join(HERE, "cornel.ptbs")
+    W = H = 512
+    img64, _, _ = ptref_render(cornel, W, H, 1, 64, 5, 0)
+    ref, rec, _ = ptref_render(cornel, W, H, 1, 4096, 5, 0)
+    a, b = np.minimum(img64[..., :3], 64.0).astype(np.float64), np.minimum(ref[..., :3], 64.0).astype(np.float64)
+    out = {"ref4096_f16": np.minimum(ref[..., :3], 64.0).astype(np.float16), "rmse_cpu64": float(np.sqrt(((a - b) ** 2).mean())),
+           "ref_trace_ms": rec["trace_ms"], "size": np.array([W, H]), "spp": np.array([64, 4096]), "max_depth": 5}
+    np.savez_compressed(path, **out)
+    print("wrote", path, out["rmse_cpu64"], rec["trace_ms"])
+
+
 def main():
+    if "--rmse" in sys.argv:
+        return rmse_golden()
+    if "--configs" in sys.argv:
+        return configs()
     if "--lucy" in sys.argv:
         return lucy()
     if "--textured" in sys.argv:

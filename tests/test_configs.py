@@ -1,0 +1,219 @@
+"""Parity at the sizes BASELINE.json names, against outputs of the UNMODIFIED reference (tests/golden/configs_ref.npz, written
+by tests/golden/make_golden.py --configs from oracle/_ref/ptref):
+
+  config 0   Cornell 512x512, BVH, 1 spp, primary + 1 bounce (max_depth 2)
+  config 1   Cornell 1024x1024, BVH, max_depth 5 — the first 4 of its 64 spp.  At this size the frame has 4.6 pixels per
+             lane of the path kernel, so work items are ONE sample and a pixel's state is handed from lane to lane through
+             HBM (ptb_mega.cuh, LANE_WAIT): the regime bench.py times.
+  Lucy       the 524,310-triangle stand-in, 1920x1080, 2 spp, max_depth 9 (configs 2/3 geometry), BVH: the deep tree and the
+             EARLY build of the path kernel; and through the Subgrids gs 8 / os 8 / m 50 (frame compared with a stated
+             tolerance: the library derives its grids from its own BVH, the reference from its two-level one, and a ray that
+             leaves a grid's planes finds no cell in either — which rays those are depends on the hierarchy)
+
+The CPU tests pin the oracle restatement to those goldens; the GPU tests compare libptb.so (through the C ABI) with the
+goldens by digest and, where a digest differs, with the oracle's frame pixel by pixel — reporting how many pixels differ and
+by how much.  Bar: images bit-equal except where the hand-rolled double sincos (2^-29 per call, ptb_kernels.cuh) rounds the
+other way: at most max(2, W*H/100000) pixels may differ at all."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from oracle_lib import MODE_BVH, MODE_TWO_PLANE, Oracle
+
+CONFIGS = os.path.join(GOLDEN, "configs_ref.npz")
+CASES = {  # name: (W, H, spp, max_depth)
+    "c0": (512, 512, 1, 2),
+    "c1": (1024, 1024, 4, 5),
+    "lucy_bvh": (1920, 1080, 2, 9),
+}
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def thumb(img, k=8):
+    h, w = img.shape[0] // k * k, img.shape[1] // k * k
+    return img[:h, :w, :3].astype(np.float64).reshape(h // k, k, w // k, k, 3).mean(axis=(1, 3)).astype(np.float32)
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(CONFIGS)
+
+
+@pytest.fixture(scope="module")
+def lucy_ptbs(tmp_path_factory):
+    import ptb_b200
+    sc = ptb_b200.scenes
+    p = str(tmp_path_factory.mktemp("lucy") / "lucy.ptbs")
+    scene = sc.lucy_standin(sc.read_ptbs(os.path.join(GOLDEN, "cornel.ptbs")))
+    sc.write_ptbs(p, scene)
+    return p, scene
+
+
+def _scene_path(name, cornel_ptbs, lucy_ptbs):
+    return lucy_ptbs[0] if name.startswith("lucy") else cornel_ptbs
+
+
+_oracles = {}
+
+
+def _oracle(path):
+    """one oracle per scene for the whole module (its BVH over the stand-in takes 20 s)"""
+    if path not in _oracles:
+        o = Oracle(path)
+        o.build()
+        _oracles[path] = o
+    return _oracles[path]
+
+
+# ---- CPU: the restatement against the reference's goldens ---------------------------------------------------------------------
+@pytest.mark.parametrize("name", list(CASES))
+def test_oracle_equals_reference_at_config_size(name, gold, cornel_ptbs, lucy_ptbs):
+    W, H, spp, depth = CASES[name]
+    if name.startswith("lucy"):
+        assert hashlib.sha256(lucy_ptbs[1]["pos"].tobytes()).hexdigest() == str(gold["lucy_scene_sha256"])
+    o = _oracle(_scene_path(name, cornel_ptbs, lucy_ptbs))
+    o.configure(W, H, MODE_BVH, nee=0, max_depth=depth)
+    if name == "c0":
+        t, tri, _ = o.primary_hits()
+        assert sha(t) == str(gold["c0_t_sha256"])
+        assert (tri == gold["c0_tri"]).all()
+    img, samples, _, st = o.render(spp, threads=os.cpu_count() or 1)
+    assert sha(img) == str(gold[name + "_img_sha256"]), "the restatement's frame differs from the reference's"
+    want = gold[name + "_counts"]
+    got = [st["find_calls"], st["rays_traversed"], st["rays_unique"], st["tri_tests"], st["as_tests"]]
+    assert got == [int(v) for v in want]
+    assert (samples == spp).all()
+
+
+# ---- GPU ----------------------------------------------------------------------------------------------------------------------
+def _compare_with_oracle(name, img, path, W, H, spp, depth, mode=MODE_BVH):
+    """digest differs: where, how many pixels, by how much (vs the oracle's frame, which equals the reference's)"""
+    o = _oracle(path)
+    o.configure(W, H, mode, nee=0, max_depth=depth)
+    ref, _, _, _ = o.render(spp, threads=os.cpu_count() or 1)
+    diff = (img.view(np.uint32) != ref.view(np.uint32)).any(axis=-1)
+    n = int(diff.sum())
+    rel = 0.0
+    if n:
+        a, b = img[diff][:, :3].astype(np.float64), ref[diff][:, :3].astype(np.float64)
+        rel = float((np.abs(a - b) / np.maximum(np.abs(b), 1e-3)).max())
+    print(f"{name}: {n} of {W * H} pixels differ from the reference frame, max relative error {rel:.3e}")
+    return n, rel
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(CASES))
+def test_gpu_equals_reference_at_config_size(name, gold, ptb, cornel_ptbs, lucy_ptbs):
+    W, H, spp, depth = CASES[name]
+    path = _scene_path(name, cornel_ptbs, lucy_ptbs)
+    pt = ptb.PathTracer(0)
+    pt.load_ptbs(path)
+    pt.build_bvh()
+    pt.set_params(width=W, height=H, mode=MODE_BVH, nee=0, max_depth=depth)
+    if name == "c0":
+        t, tri, _ = pt.primary_hits()
+        assert sha(t) == str(gold["c0_t_sha256"]), "primary hit distances differ from the reference's"
+        ties = int((tri != gold["c0_tri"]).sum())
+        print(f"c0: {ties} primary hit ids differ at bit-equal distance (documented ties)")
+        assert ties <= W * H // 10000
+    pt.reset()
+    pt.render(spp)
+    img = pt.read_image()
+    samples, _ = pt.read_state()
+    c = pt.counters()
+    pt.close()
+    assert (samples == spp).all()
+    want = [int(v) for v in gold[name + "_counts"]]
+    if sha(img) == str(gold[name + "_img_sha256"]):
+        print(f"{name}: 0 of {W * H} pixels differ from the reference frame (digest equal)")
+        # rays executed = the reference's unique rays; rays it would have traversed incl. re-traced misses = its own count
+        assert c["rays"] == want[2] and c["ref_rays"] == want[1]
+        assert c["paths"] == W * H * spp
+        return
+    n, rel = _compare_with_oracle(name, img, path, W, H, spp, depth)
+    assert n <= max(2, W * H // 100000), f"{n} pixels differ"
+    assert np.abs(thumb(img) - gold[name + "_thumb"]).max() <= 0.05 * max(1.0, float(gold[name + "_thumb"].max()))
+    assert abs(c["rays"] - want[2]) <= 64 * n and abs(c["ref_rays"] - want[1]) <= 64 * n
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c0", "c1"])
+def test_gpu_counters_over_the_reference_tree_at_config_size(name, gold, ptb, cornel_ptbs):
+    """tracer.cpp:60-70 at the config's own size: both test counters of the unmodified reference, integer for integer."""
+    W, H, spp, depth = CASES[name]
+    o = _oracle(cornel_ptbs)
+    nodes, idx, roots, root = o.export_bvh()
+    pt = ptb.PathTracer(0)
+    pt.load_ptbs(cornel_ptbs)
+    pt.build_bvh()
+    pt.upload_ref_bvh(nodes, idx, roots, root)
+    pt.use_ref_bvh(True)
+    pt.set_params(width=W, height=H, mode=MODE_BVH, nee=0, max_depth=depth, count_tests=1)
+    pt.reset()
+    pt.render(spp)
+    c = pt.counters()
+    img = pt.read_image()
+    pt.close()
+    want = [int(v) for v in gold[name + "_counts"]]
+    if sha(img) == str(gold[name + "_img_sha256"]):
+        assert [c["tri_tests"], c["as_tests"]] == want[3:5]
+    else:  # a path diverged by one ulp somewhere (see the module docstring): counters within that path's share
+        assert abs(c["tri_tests"] - want[3]) <= 1e-5 * want[3] and abs(c["as_tests"] - want[4]) <= 1e-5 * want[4]
+
+
+@pytest.mark.gpu
+def test_gpu_subgrid_lucy_full_size_against_reference_frame(gold, ptb, lucy_ptbs):
+    """The reference's own Subgrid (TWO_PLANE, gs 8 os 8 m 50) frame of the stand-in at 1080p, 2 spp, max_depth 9.  Stated
+    tolerance: a pixel agrees when every channel is within 2^-9 relative (the golden is stored in half precision) or 1e-3
+    absolute; at most W*H/250 pixels may disagree (hierarchy-dependent misses, see the module docstring)."""
+    if "lucy_grid_img_f16" not in gold.files:
+        pytest.skip("golden not generated (make_golden.py --configs --lucy-subgrid: 14 min, 11 GB)")
+    W, H, spp, depth = 1920, 1080, 2, 9
+    pt = ptb.PathTracer(0)
+    pt.load_ptbs(lucy_ptbs[0])
+    pt.build_bvh()
+    frames = {}
+    for mode in (MODE_BVH, MODE_TWO_PLANE):
+        if mode == MODE_TWO_PLANE:
+            pt.build_subgrid(8, 8, 50, gpu=True)
+        pt.set_params(width=W, height=H, mode=mode, nee=0, max_depth=depth)
+        pt.reset()
+        pt.render(spp)
+        frames[mode] = pt.read_image()[..., :3].copy()
+    pt.close()
+    ref = gold["lucy_grid_img_f16"].astype(np.float32)
+    got = np.clip(frames[MODE_TWO_PLANE], 0, 65000)
+    bad = (np.abs(got - ref) > np.maximum(np.abs(ref) * 2.0 ** -9, 1e-3)).any(axis=-1)
+    between = (frames[MODE_BVH].view(np.uint32) != frames[MODE_TWO_PLANE].view(np.uint32)).any(axis=-1)
+    print(f"lucy subgrid: {int(bad.sum())} of {W * H} pixels disagree with the reference's Subgrid frame; "
+          f"{int(between.sum())} pixels differ between this library's BVH and Subgrid frames")
+    assert int(bad.sum()) <= W * H // 250
+
+
+@pytest.mark.gpu
+def test_gpu_rmse_against_4096_spp_reference(ptb, cornel_ptbs):
+    """per-pixel RMSE of linear radiance (clamped to 64) against the reference's 4096-spp frame;
+    bar: the GPU's 64-spp frame is no further from it than 1.5x the reference's own 64-spp frame.  512x512 (see
+    make_golden.py rmse_golden for why not 1024x1024)."""
+    p = os.path.join(GOLDEN, "cornel_rmse_ref.npz")
+    if not os.path.isfile(p):
+        pytest.skip("golden not generated (make_golden.py --rmse)")
+    g = np.load(p)
+    W, H = (int(v) for v in g["size"])
+    pt = ptb.PathTracer(0)
+    pt.load_ptbs(cornel_ptbs)
+    pt.build_bvh()
+    pt.set_params(width=W, height=H, mode=MODE_BVH, nee=0, max_depth=int(g["max_depth"]))
+    pt.reset()
+    pt.render(int(g["spp"][0]))
+    img = np.minimum(pt.read_image()[..., :3], 64.0).astype(np.float64)
+    pt.close()
+    rmse = float(np.sqrt(((img - g["ref4096_f16"].astype(np.float64)) ** 2).mean()))
+    print(f"RMSE vs the reference's 4096-spp frame: GPU 64 spp {rmse:.5f}, reference 64 spp {float(g['rmse_cpu64']):.5f}")
+    assert rmse <= 1.5 * float(g["rmse_cpu64"])

@@ -443,3 +443,18 @@ def test_tga_textures_equal_stb_image_in_the_compiled_reference(ptb, tmp_path):
     run_ptref(["--scene-file", scene, "--base", str(tmp_path), "dump-scene", str(tmp_path / "ref.ptbs")])
     with open(tmp_path / "ref.ptbs", "rb") as f:
         assert mine == f.read()
+
+
+def test_group_of_only_degenerate_faces_is_skipped(ptb, tmp_path):
+    """A group whose faces are all dropped (fewer than three corners) still becomes a shape in tinyobjloader, with an empty
+    mesh; the reference reads material_ids[0] of that empty vector (object.cpp:92).  The loader emits no object for it."""
+    d = str(tmp_path)
+    os.makedirs(os.path.join(d, "objs"))
+    with open(os.path.join(d, "objs", "a.obj"), "w") as f:
+        f.write("v 0 0 0\nv 1 0 0\nv 1 1 0\nvn 0 0 1\nvt 0 0\ng broken\nf 1/1/1 2/1/1\nf 3/1/1\ng good\nf 1/1/1 2/1/1 3/1/1\n")
+    with open(os.path.join(d, "s.scene"), "w") as f:
+        f.write("[Models]\nfile: objs/a.obj\n")
+    ptb.convert_scene_file(os.path.join(d, "s.scene"), os.path.join(d, "o.ptbs"), base_dir=d)
+    s = ptb.scenes.read_ptbs(os.path.join(d, "o.ptbs"))
+    assert s["pos"].shape == (1, 9)
+    assert len(s["objects"]) == 1 and s["objects"][0]["end"] - s["objects"][0]["start"] == 1
