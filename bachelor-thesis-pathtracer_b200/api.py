@@ -25,7 +25,7 @@ SYMBOLS = (
     "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_build_subbeams_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh", "ptb_upload_textures",
     "ptb_group_create", "ptb_group_destroy", "ptb_group_size", "ptb_group_ctx", "ptb_group_last_error", "ptb_group_peer_direct",
     "ptb_group_set_params", "ptb_group_reset", "ptb_group_clear", "ptb_group_render", "ptb_group_read_image", "ptb_group_read_counters",
-    "ptb_group_last_render_ms", "ptb_group_set_sharding",
+    "ptb_group_last_render_ms", "ptb_group_set_sharding", "ptb_trace_rays_static", "ptb_trace_rays_static_max",
 )
 
 
@@ -133,6 +133,9 @@ def load_library():
     L.ptb_primary_hits.argtypes = [vp, vp, vp, vp]
     L.ptb_trace_rays.argtypes = [vp, vp, cu64, ci, vp, vp]
     L.ptb_trace_rays_device.argtypes = [vp, vp, cu64, ci, vp, vp]
+    L.ptb_trace_rays_static.argtypes = [vp, vp, cu64, vp, vp]
+    L.ptb_trace_rays_static_max.restype = cu64
+    L.ptb_trace_rays_static_max.argtypes = []
     L.ptb_read_image.argtypes = [vp, vp]
     L.ptb_read_state.argtypes = [vp, vp, vp]
     L.ptb_write_state.argtypes = [vp, vp, vp, vp]
@@ -325,6 +328,15 @@ class PathTracer:
         t = np.empty(n, np.float32)
         tri = np.empty(n, np.int32)
         self._ck(self.L.ptb_trace_rays(self.h, _ptr(od6), n, mode, _ptr(t), _ptr(tri)), "ptb_trace_rays")
+        return t, tri
+
+    def trace_rays_static(self, od6):
+        """ptb_trace_rays in BVH mode with the scratch in the library's static device array: no allocation in the call."""
+        od6 = np.ascontiguousarray(od6, np.float32).reshape(-1, 6)
+        n = od6.shape[0]
+        t = np.empty(n, np.float32)
+        tri = np.empty(n, np.int32)
+        self._ck(self.L.ptb_trace_rays_static(self.h, _ptr(od6), n, _ptr(t), _ptr(tri)), "ptb_trace_rays_static")
         return t, tri
 
     def trace_rays_device(self, od6_ptr, n, mode, t_ptr, tri_ptr):

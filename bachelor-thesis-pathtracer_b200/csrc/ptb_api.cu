@@ -1867,3 +1867,73 @@ extern "C" int ptb_build_subbeams(ptb_ctx *c, uint32_t gs, uint32_t m) {
 extern "C" int ptb_build_subbeams_gpu(ptb_ctx *c, uint32_t gs, uint32_t m) {
     return guarded(c, [&]() { return ptb_build_subbeams_gpu_impl(c, gs, m); });
 }
+
+// =============================================================================================
+// ptb_trace_rays_static: ptb_trace_rays without any allocation
+// =============================================================================================
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  ptb_trace_rays stages the host rays and
+// the results in per-context scratch that ensure_scratch cudaMalloc's on demand; here the same kernel (k_trace_bvh: the
+// persistent dynamic-fetch BVH walk) runs on scratch that lives in ONE file-scope device array of fixed size:
+//
+//   [0, 256)                      the launch's work cursor (8 bytes used; must start at zero, cleared per call)
+//   + 24 B x PTB_STATIC_MAX_RAYS  staged rays (origin, direction)
+//   +  4 B x PTB_STATIC_MAX_RAYS  hit distances
+//   +  4 B x PTB_STATIC_MAX_RAYS  hit triangle ids
+//
+// = 2 MiB + 256 B at PTB_STATIC_MAX_RAYS = 65,536, held by every GPU that loads the library until the process exits.
+// All calls — from any context on that device — share the array, and it keeps the last call's contents: the call clears
+// the cursor and overwrites [0, n) of the other regions before the kernel reads them, and it is synchronous, so calls
+// issued one after the other are safe; calls that overlap on the GPU (two host threads, two contexts of one device) race.
+//
+// In host code `g_staticScratch` is a host-side stand-in for the symbol, NOT a device address: its device address is
+// resolved once per device with cudaGetSymbolAddress (that device current) and only that pointer is handed to copies
+// and kernels.
+static __device__ __align__(256) unsigned char g_staticScratch[256 + (size_t)PTB_STATIC_MAX_RAYS * 32];
+
+namespace {
+const int kMaxDevices = 64;
+unsigned char *g_staticScratchPtr[kMaxDevices] = {nullptr}; // device address of g_staticScratch on device i (0 = not resolved yet)
+} // namespace
+
+extern "C" uint64_t ptb_trace_rays_static_max(void) { return (uint64_t)PTB_STATIC_MAX_RAYS; }
+
+extern "C" int ptb_trace_rays_static(ptb_ctx *c, const float *od6, uint64_t n, float *t, int32_t *tri) {
+    GUARD(c); // makes c->device current
+    SETTLE(c);
+    if (n > (uint64_t)PTB_STATIC_MAX_RAYS)
+        return fail(c, PTB_ERR_INVALID, "ptb_trace_rays_static: " + std::to_string(n) + " rays exceed the static scratch of " +
+                                            std::to_string(PTB_STATIC_MAX_RAYS) + " rays (PTB_STATIC_MAX_RAYS); split the batch or use ptb_trace_rays");
+    int r = check_mode_ready(c, PTB_MODE_BVH);
+    if (r) return r;
+    if (n == 0) return PTB_OK;
+    if (!od6 || !t || !tri) return fail(c, PTB_ERR_INVALID, "null ray / result pointers");
+    if (c->device < 0 || c->device >= kMaxDevices) return fail(c, PTB_ERR_INVALID, "device index beyond the static-scratch table");
+    unsigned char *base = g_staticScratchPtr[c->device];
+    if (!base) { // set-up, once per device, with that device current
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_staticScratch));
+        if (!p) return fail(c, PTB_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_staticScratchPtr[c->device] = base = (unsigned char *)p;
+    }
+    unsigned long long *cursor = reinterpret_cast<unsigned long long *>(base);
+    float *dRays = reinterpret_cast<float *>(base + 256);
+    float *dT = reinterpret_cast<float *>(base + 256 + (size_t)PTB_STATIC_MAX_RAYS * 24);
+    int *dTri = reinterpret_cast<int *>(base + 256 + (size_t)PTB_STATIC_MAX_RAYS * 28);
+    CK(cudaMemsetAsync(cursor, 0, 256, c->stream)); // what must start at zero
+    CK(cudaMemcpyAsync(dRays, od6, n * 6 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    const int gp = (int)std::min<uint64_t>((uint64_t)c->sms * c->extendCtas, (n + 127) / 128);
+    CK(cudaEventRecord(c->evStart, c->stream));
+    k_trace_bvh<false, false><<<gp, 128, 0, c->stream>>>(c->S, dRays, n, dT, dTri, c->dIdOfTri, c->dCounters, cursor, c->fetchKeep, 0);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->evStop, c->stream));
+    CK(cudaMemcpyAsync(t, dT, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(tri, dTri, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->evStart, c->evStop);
+    c->lastMs = ms;
+    c->counters[PTB_CNT_KERNELS]++;
+    c->counters[PTB_CNT_RAYS] += n;
+    return PTB_OK;
+}

@@ -182,6 +182,19 @@ int ptb_primary_hits(ptb_ctx *ctx, float *t, int32_t *tri, int32_t *mat);
 int ptb_trace_rays(ptb_ctx *ctx, const float *od6, uint64_t n, int mode, float *t, int32_t *tri);
 int ptb_trace_rays_device(ptb_ctx *ctx, const float *od6_device, uint64_t n, int mode, float *t_device, int32_t *tri_device);
 
+/* ptb_trace_rays in BVH mode WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernel, same results as ptb_trace_rays(ctx, od6, n, PTB_MODE_BVH, t, tri) over the library's own tree, but the
+ * staged rays, the results and the launch's work cursor live in one file-scope `static __device__` array inside the
+ * library (2 MiB + 256 B, held by every GPU that loads libptb.so until the process exits) instead of per-context scratch
+ * from cudaMalloc.  n > PTB_STATIC_MAX_RAYS is refused with PTB_ERR_INVALID.  Host pointers in and out; synchronous.  The
+ * array is shared by every call on that device and keeps the previous call's contents (the call clears / overwrites what it
+ * reads): calls issued one after the other are safe, calls that overlap on the GPU (several host threads or contexts on one
+ * device) race.  The scene must be uploaded and ptb_build_bvh[_gpu] done beforehand (those do allocate). */
+#define PTB_STATIC_MAX_RAYS 65536
+int ptb_trace_rays_static(ptb_ctx *ctx, const float *od6, uint64_t n, float *t, int32_t *tri);
+uint64_t ptb_trace_rays_static_max(void); /* PTB_STATIC_MAX_RAYS of the loaded library */
+
 /* ---- read-back ------------------------------------------------------------------------------ */
 int ptb_read_image(ptb_ctx *ctx, float *rgba);                       /* tracerGetPixel for every pixel, row-major y*W+x, alpha 1 */
 int ptb_read_state(ptb_ctx *ctx, int32_t *samples, uint32_t *rng);   /* samples[][] / randomStates[][] (tracer.cpp:25-26), y*W+x */
