@@ -173,6 +173,58 @@ __device__ __forceinline__ bool slab_fast(f3 lo, f3 hi, f3 o, f3 inv, float tmax
 }
 __device__ __forceinline__ bool finite3(f3 v) { return fabsf(v.x) < PTB_INF && fabsf(v.y) < PTB_INF && fabsf(v.z) < PTB_INF; }
 
+// Box test for TREE NAVIGATION only, one FFMA per plane: t = bound * inv + (-(origin * inv)).  Which boxes a walk visits does not
+// enter the result — the hit record comes from intersect_tri alone, in the reference's arithmetic — provided no box the
+// reference-order test accepts is rejected.  The FMA form rounds origin * inv once (0.5 ulp of |origin * inv|, which can exceed
+// the slab distance itself when the origin is far from the box along a near-parallel axis), so the interval is widened by
+// `pad` = 2^-21 * max|origin * inv| (absolute) and 2^-22 (relative) on both ends: a superset of the exact test's acceptances.
+// The entry distance only orders the children and culls at pop time; the widened (smaller) value is conservative for both.
+// Callers use it only for rays whose inv_dir is finite and below 2^100 in magnitude (no inf - inf).
+#ifndef PTB_SLAB_FMA
+#define PTB_SLAB_FMA 0
+#endif
+__device__ __forceinline__ bool slab_fma(f3 lo, f3 hi, f3 inv, f3 noi, float pad, float tmax, float &tn) {
+    const float tx1 = __fmaf_rn(lo.x, inv.x, noi.x), tx2 = __fmaf_rn(hi.x, inv.x, noi.x);
+    const float ty1 = __fmaf_rn(lo.y, inv.y, noi.y), ty2 = __fmaf_rn(hi.y, inv.y, noi.y);
+    const float tz1 = __fmaf_rn(lo.z, inv.z, noi.z), tz2 = __fmaf_rn(hi.z, inv.z, noi.z);
+    const float a = fmaxf(fmaxf(fminf(tx1, tx2), fminf(ty1, ty2)), fminf(tz1, tz2));
+    const float b = fminf(fminf(fmaxf(tx1, tx2), fmaxf(ty1, ty2)), fmaxf(tz1, tz2));
+    // a < 0 clamps to 0 whatever the factor; b < 0 (box behind the origin) only needs the absolute pad
+    const float t0 = fmaxf(__fmaf_rn(a, 0.99999976f, -pad), 0.0f);
+    const float t1 = fminf(__fmaf_rn(b, 1.00000024f, pad), tmax);
+    tn = t0;
+    return t0 <= t1;
+}
+__device__ __forceinline__ bool slab_fma_ok(f3 v) {
+    const float lim = 1.2676506e30f; // 2^100
+    return fabsf(v.x) < lim && fabsf(v.y) < lim && fabsf(v.z) < lim;
+}
+
+// ---- traversal stacks ------------------------------------------------------------------------------------------------
+// LocalStack: the whole stack in local memory (per-thread, interleaved by the hardware).  HybridStack: entries [0, NS) in shared
+// memory — column `tid` of an [NS][CTA threads] array, conflict-free for any mix of per-lane depths — and the overflow in local
+// memory.  ncu on the round-1 kernel: 512 B of local stack per lane x 227 k lanes = 116 MB, the size of the L2, written back
+// to DRAM at 1 GB per 4-spp Lucy launch and competing with node fetches for the L1 tag stage (LDL + STL 5 % of issue).
+#ifndef PTB_SSTACK
+#define PTB_SSTACK 0
+#endif
+#define PTB_CTA 128 /* threads per CTA of every traversal kernel (kThreads in ptb_api.cu) */
+struct LocalStack {
+    int2 *p;
+    __device__ __forceinline__ int2 get(int i) const { return p[i]; }
+    __device__ __forceinline__ void put(int i, int2 e) const { p[i] = e; }
+};
+template <int NS>
+struct HybridStack {
+    int2 *sm; // &shared[threadIdx.x]
+    int2 *lm; // local overflow, PTB_STACK - NS entries
+    __device__ __forceinline__ int2 get(int i) const { return i < NS ? sm[i * PTB_CTA] : lm[i - NS]; }
+    __device__ __forceinline__ void put(int i, int2 e) const {
+        if (i < NS) sm[i * PTB_CTA] = e;
+        else lm[i - NS] = e;
+    }
+};
+
 #ifndef PTB_STACK
 #define PTB_STACK 64
 #endif
@@ -200,47 +252,48 @@ struct BvhWalk {
     Hit h;
     int ref;   // >= 0 inner node, < 0 leaf, PTB_REF_DONE finished
     int sp;
-    bool fast; // inv_dir finite: FMNMX slab test allowed
+    bool fast; // inv_dir finite: FMNMX / FMA slab test allowed
+#if PTB_SLAB_FMA
+    float pad; // slab_fma: 2^-21 * max|o * inv|
+#endif
     // The stack itself (far child reference + its entry distance) is NOT a member: a dynamically
     // indexed array inside the struct drags every scalar above into local memory with it (seen in
-    // ncu as 9 % LDL/STL).  Callers own `int2 stack[PTB_STACK]` and pass it to pop()/round().
+    // ncu as 9 % LDL/STL).  Callers own the storage and pass a LocalStack / HybridStack to pop()/round().
 
-    __device__ __forceinline__ void begin(const SceneDev &S, f3 o_, f3 d_, const Hit &h0) {
+    // `inv_` = the reciprocal direction, possibly computed elsewhere (k_duo prepares it in its batched passes)
+    __device__ __forceinline__ void begin_inv(const SceneDev &S, f3 o_, f3 d_, f3 inv_, const Hit &h0) {
         o = o_;
         d = d_;
-        inv = rcp3(d_);
+        inv = inv_;
+#if PTB_SLAB_FMA
+        fast = slab_fma_ok(inv);
+        pad = fmaxf(fmaxf(fabsf(o.x * inv.x), fabsf(o.y * inv.y)), fabsf(o.z * inv.z)) * 4.7683716e-7f;
+#else
         fast = finite3(inv);
+#endif
         h = h0;
         sp = 0;
         ref = S.n_tris ? S.bvh_root : PTB_REF_DONE;
     }
-    __device__ __forceinline__ void pop(const int2 *stack) {
+    __device__ __forceinline__ void begin(const SceneDev &S, f3 o_, f3 d_, const Hit &h0) { begin_inv(S, o_, d_, rcp3(d_), h0); }
+    template <class ST>
+    __device__ __forceinline__ void pop(const ST &stack) {
         for (;;) {
             if (sp == 0) {
                 ref = PTB_REF_DONE;
                 return;
             }
             sp--;
-            const int2 e = stack[sp];
+            const int2 e = stack.get(sp);
             if (!(__int_as_float(e.y) > h.t)) {
                 ref = e.x;
                 return;
             }
         }
     }
-    // same with the reciprocal direction computed elsewhere (k_duo prepares it in its batched passes)
-    __device__ __forceinline__ void begin_inv(const SceneDev &S, f3 o_, f3 d_, f3 inv_, const Hit &h0) {
-        o = o_;
-        d = d_;
-        inv = inv_;
-        fast = finite3(inv);
-        h = h0;
-        sp = 0;
-        ref = S.n_tris ? S.bvh_root : PTB_REF_DONE;
-    }
     // one inner node (ref >= 0): both children's boxes, near child next, far child pushed
-    template <bool COUNT>
-    __device__ __forceinline__ void node_step(const SceneDev &S, int2 *stack, uint32_t &nBox) {
+    template <bool COUNT, class ST>
+    __device__ __forceinline__ void node_step(const SceneDev &S, const ST &stack, uint32_t &nBox) {
         const float4 *n = S.nodes + 4 * (size_t)ref;
         const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
         const int4 q3 = __ldg(reinterpret_cast<const int4 *>(n + 3));
@@ -248,8 +301,14 @@ struct BvhWalk {
         float d0, d1;
         bool h0, h1;
         if (fast) {
+#if PTB_SLAB_FMA
+            const f3 noi = mk3(-(o.x * inv.x), -(o.y * inv.y), -(o.z * inv.z));
+            h0 = slab_fma(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), inv, noi, pad, h.t, d0);
+            h1 = slab_fma(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), inv, noi, pad, h.t, d1);
+#else
             h0 = slab_fast(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
             h1 = slab_fast(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
+#endif
         } else {
             h0 = slab(mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), o, inv, h.t, d0);
             h1 = slab(mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), o, inv, h.t, d1);
@@ -257,7 +316,7 @@ struct BvhWalk {
         if (h0 && h1) {
             // bvh.cpp:75-84: left first unless the right child is strictly nearer
             const bool leftFirst = d1 >= d0;
-            stack[sp++] = make_int2(leftFirst ? q3.y : q3.x, __float_as_int(leftFirst ? d1 : d0));
+            stack.put(sp++, make_int2(leftFirst ? q3.y : q3.x, __float_as_int(leftFirst ? d1 : d0)));
             ref = leftFirst ? q3.x : q3.y;
         } else if (h0) {
             ref = q3.x;
@@ -268,8 +327,8 @@ struct BvhWalk {
         }
     }
     // one leaf (ref < 0, not PTB_REF_DONE): its triangles, then the next reference from the stack
-    template <bool COUNT>
-    __device__ __forceinline__ void leaf(const SceneDev &S, const int2 *stack, uint32_t &nTri) {
+    template <bool COUNT, class ST>
+    __device__ __forceinline__ void leaf(const SceneDev &S, const ST &stack, uint32_t &nTri) {
         int first, count;
         leaf_decode(ref, first, count);
         for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
@@ -280,8 +339,8 @@ struct BvhWalk {
     // that already hold a leaf stop waiting for the last stragglers, which resume next round.  Pays on deep
     // trees (Lucy stand-in +17 %); on a 100-node tree the vote per step costs more than it saves
     // (profiles/r1_sweep_mega_leaf.txt), hence a compile-time switch.
-    template <bool COUNT, bool EARLY = false>
-    __device__ __forceinline__ bool round(const SceneDev &S, int2 *stack, uint32_t &nTri, uint32_t &nBox, int minActive = 0) {
+    template <bool COUNT, bool EARLY = false, class ST>
+    __device__ __forceinline__ bool round(const SceneDev &S, const ST &stack, uint32_t &nTri, uint32_t &nBox, int minActive = 0) {
         while (ref >= 0) {
             node_step<COUNT>(S, stack, nBox);
             if (EARLY && __popc(__activemask()) < minActive) break;
@@ -294,7 +353,8 @@ struct BvhWalk {
 template <bool COUNT>
 __device__ __forceinline__ void bvh_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nBox) {
     BvhWalk w;
-    int2 stack[PTB_STACK];
+    int2 stackMem[PTB_STACK];
+    const LocalStack stack{stackMem};
     w.begin(S, o, d, h);
     while (w.round<COUNT>(S, stack, nTri, nBox)) {
     }
@@ -412,6 +472,67 @@ __device__ __forceinline__ void subgrid_closest(const SceneDev &S, f3 o, f3 d, H
     }
 }
 
+// The reference keeps a LIFO of grid ids and pushes every child of the cell it lands in (lightFieldGrid.cpp:127-145: ascending
+// for a negative dominant direction, descending otherwise, so that pops come back-to-front resp. front-to-back).  A cell's
+// children are one contiguous slice of the index pool, so the same pop order falls out of a LIFO of SLICES consumed from one
+// end: one 8-byte push per visited inner grid instead of one load + store per child (14 % of the issued instructions of the
+// round-1 kernel at 3 active lanes), and a stack as deep as the grid hierarchy — at most 1 + ceil(BVH depth / 4) <= 17 slices,
+// a bound the builders guarantee (PTB_STACK) — instead of 160 ids that could overflow silently.
+#ifndef PTB_GRID_SLICES
+#define PTB_GRID_SLICES 0
+#endif
+#define PTB_GDEPTH 20
+template <bool COUNT>
+__device__ __forceinline__ void subgrid_closest_slices(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
+    const f3 inv = rcp3(d);
+    const int axis = dominant_axis(d);
+    const int right = axis == 0 ? 1 : 0, up = axis == 2 ? 1 : 2; // lightFieldGrid.cpp:26-35
+    const float oa = comp(o, axis), ia = comp(inv, axis), da = comp(d, axis);
+    const float orr = comp(o, right), dr = comp(d, right), ou = comp(o, up), du = comp(d, up);
+    const bool fromEnd = da < 0.0f; // ascending pushes pop from the end of the slice
+    uint2 stack[PTB_GDEPTH];
+    int sp = 0;
+    uint32_t g = (uint32_t)axis; // grids 0..2 are the roots per dominant axis
+    for (;;) {
+        const float4 *hd = S.grid_hdr + 4 * (size_t)g;
+        const float4 h0 = __ldg(hd), h1 = __ldg(hd + 1);
+        if (COUNT) nAS++;
+        float tn;
+        if (slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)) {
+            if (COUNT) nAS++;
+            const float4 h2 = __ldg(hd + 2), h3 = __ldg(hd + 3);
+            const f3 gmin = mk3(h2.x, h2.y, h2.z), idl = mk3(h3.x, h3.y, h3.z);
+            const float gmaxA = comp(mk3(h1.x, h1.y, h1.z), axis) + 0.1f;
+            const float d1 = (comp(gmin, axis) - oa) * ia;
+            const float d2 = (gmaxA - oa) * ia;
+            // in = (origin + d1*dir - min) * inv_delta, out likewise (lightFieldGrid.cpp:116-117)
+            const float inR = ((orr + d1 * dr) - comp(gmin, right)) * comp(idl, right);
+            const float inU = ((ou + d1 * du) - comp(gmin, up)) * comp(idl, up);
+            const float outR = ((orr + d2 * dr) - comp(gmin, right)) * comp(idl, right);
+            const float outU = ((ou + d2 * du) - comp(gmin, up)) * comp(idl, up);
+            const uint32_t sz = __float_as_uint(h0.w) & 0x7fffffffu;
+            const bool hasTris = (__float_as_uint(h0.w) >> 31) != 0u;
+            const float fs = (float)sz;
+            const int iu = (int)(inR * fs), iv = (int)(inU * fs), is = (int)(outR * fs), it = (int)(outU * fs);
+            // the reference indexes without a bounds check (A.12); outside the planes means no cell
+            if ((unsigned)iu < sz && (unsigned)iv < sz && (unsigned)is < sz && (unsigned)it < sz) {
+                const uint32_t cell = ((((uint32_t)iu * sz + (uint32_t)iv) * sz + (uint32_t)is) * sz + (uint32_t)it);
+                const uint2 se = __ldg(&S.grid_lut[(size_t)__float_as_uint(h1.w) + cell]);
+                if (hasTris) {
+                    for (uint32_t i = se.x; i < se.y; ++i) intersect_tri<COUNT>(S.tri, (int)__ldg(&S.grid_idx[i]), o, d, h, nTri);
+                } else if (se.x < se.y && sp < PTB_GDEPTH) {
+                    stack[sp++] = se;
+                }
+            }
+        }
+        if (sp == 0) break;
+        uint2 e = stack[sp - 1];
+        g = __ldg(&S.grid_idx[fromEnd ? --e.y : e.x++]);
+        if (e.x == e.y) sp--;
+        else stack[sp - 1] = e;
+    }
+}
+
 // ---- Subbeam closest hit: stands in for intersectSubBeamGrid (SubBeams.cpp:73-170) ---------
 template <bool COUNT>
 __device__ __forceinline__ void subbeam_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
@@ -469,6 +590,7 @@ __device__ __forceinline__ void subbeam_closest(const SceneDev &S, f3 o, f3 d, H
 template <int MODE, bool COUNT>
 __device__ __forceinline__ void closest_hit(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
     if (MODE == 1) bvh_closest<COUNT>(S, o, d, h, nTri, nAS);
+    else if (MODE == 2 && PTB_GRID_SLICES) subgrid_closest_slices<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 2) subgrid_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 3) subbeam_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 4) refbvh_closest<COUNT>(S, o, d, h, nTri, nAS); // BVH mode over the reference's own tree

@@ -63,7 +63,8 @@ __global__ void __launch_bounds__(128, PTB_DUO_MINBLOCKS) k_duo(ParamsDev P, Sce
     bool more = true;                   // warp-uniform: the cursor still has items
     BvhWalk w;
     w.ref = PTB_REF_DONE;
-    int2 stack[PTB_STACK];
+    int2 stackMem[PTB_STACK];
+    const LocalStack stack{stackMem};
     uint32_t nTri = 0, nAS = 0;
     uint32_t cPaths = 0, cRef = 0, cRays = 0, cShadow = 0;
     unsigned long long cTri = 0, cAS = 0;

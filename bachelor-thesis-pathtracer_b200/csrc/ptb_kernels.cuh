@@ -401,7 +401,8 @@ __global__ void __launch_bounds__(128) k_extend_bvh(SceneDev S, FrameDev F, cons
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     BvhWalk w;
-    int2 stack[PTB_STACK];
+    int2 stackMem[PTB_STACK];
+    const LocalStack stack{stackMem};
     bool active = false, more = true, shadow = false;
     uint32_t slot = 0, nTri = 0, nAS = 0;
     for (;;) {
@@ -709,7 +710,8 @@ __global__ void __launch_bounds__(128) k_trace_bvh(SceneDev S, const float *__re
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     BvhWalk w;
-    int2 stack[PTB_STACK];
+    int2 stackMem[PTB_STACK];
+    const LocalStack stack{stackMem};
     bool active = false, more = true;
     uint64_t ray = 0;
     uint32_t nTri = 0, nAS = 0;

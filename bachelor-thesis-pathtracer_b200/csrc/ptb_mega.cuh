@@ -74,7 +74,15 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
     int shadowTri = -1;
     float shadowU = 0.0f, shadowV = 0.0f; // TEX only: where the shadow ray ended (a textured light is sampled there)
     BvhWalk w;
-    int2 stack[PTB_STACK];
+#if PTB_SSTACK > 0
+    // the first PTB_SSTACK stack entries of every lane live in shared memory (BVH mode; the other modes keep their own stacks)
+    __shared__ int2 sstack[MODE == 1 ? PTB_SSTACK * PTB_CTA : 1];
+    int2 stackMem[PTB_STACK - PTB_SSTACK];
+    const HybridStack<PTB_SSTACK> stack{sstack + (MODE == 1 ? threadIdx.x : 0), stackMem};
+#else
+    int2 stackMem[PTB_STACK];
+    const LocalStack stack{stackMem};
+#endif
     uint32_t nTri = 0, nAS = 0;
     uint32_t cPaths = 0, cRef = 0, cRays = 0, cShadow = 0; // per lane and launch: far below 2^32
     unsigned long long cTri = 0, cAS = 0;

@@ -82,7 +82,8 @@ __global__ void __launch_bounds__(128, PTB_POOL_MINBLOCKS) k_pool(ParamsDev P, S
     int cur = -1;
     bool shadowWalk = false;
     BvhWalk w;
-    int2 stack[PTB_STACK];
+    int2 stackMem[PTB_STACK];
+    const LocalStack stack{stackMem};
     uint32_t nTri = 0, nAS = 0;
     bool more = true;
     unsigned long long cTri = 0, cAS = 0, cPaths = 0, cRef = 0, cRays = 0, cShadow = 0;
