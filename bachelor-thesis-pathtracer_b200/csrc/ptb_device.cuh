@@ -479,7 +479,7 @@ __device__ __forceinline__ void subgrid_closest(const SceneDev &S, f3 o, f3 d, H
 // round-1 kernel at 3 active lanes), and a stack as deep as the grid hierarchy — at most 1 + ceil(BVH depth / 4) <= 17 slices,
 // a bound the builders guarantee (PTB_STACK) — instead of 160 ids that could overflow silently.
 #ifndef PTB_GRID_SLICES
-#define PTB_GRID_SLICES 0
+#define PTB_GRID_SLICES 1
 #endif
 #define PTB_GDEPTH 20
 template <bool COUNT>
