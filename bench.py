@@ -6,12 +6,17 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus N --steps K --warmup W
 
-Workload (BASELINE.json configs[1], the single-GPU configuration the metric is quoted on):
-Cornell box (showcase/scenes/cornel.scene), BVH, 1024x1024, 64 spp, primary + 4 bounces
-(max_depth 5), NEE off like the reference's own --testing protocol (src/main.cpp:101).
-A "step" is one full 64-spp frame: initTracer (ptb_reset) + trace (ptb_render).  With N > 1 the
-same frame is tile-sharded over the ranks (strong scaling: total work fixed) and the radiance is
-sum-reduced to rank 0 over NCCL inside the timed region.
+Default workload = the scene BASELINE.json's north_star states its target on: the Lucy stand-in (524,310 triangles: the
+Cornell room with a displaced 8x-subdivided octahedron sphere; the real lucy.obj is not shipped),
+BVH, 1920x1080, 256 spp, primary + 8 bounces (max_depth 9) — the frame of BASELINE configs[3] — NEE off like the
+reference's own --testing protocol (src/main.cpp:101).  --workload cornell = configs[1] (Cornell box, BVH, 1024x1024,
+64 spp, 4 bounces: the round-1 default); --workload lucy = the Lucy frame at 16 spp (profiling runs).
+A "step" is one full frame: initTracer (ptb_reset) + trace (ptb_render).  With N > 1 the same frame is sharded over
+the ranks (strong scaling: total work fixed; tiles while every GPU keeps >= 400k pixels, else sample ranges) and the
+radiance is sum-reduced to rank 0 over NCCL inside the timed region.  Outside the timed region the line also gets
+`parity`: primary-ray hit ids / hit distances of this very process against the golden written by the unmodified reference
+(tests/golden/lucy_standin_ref_1080p.npz), and for a tile-sharded run the bitwise comparison of the reduced frame with a
+1-GPU frame rendered by rank 0.
 
   value      Mrays/s, rays = traversals executed (primary + bounce; the reference's re-traced
              misses are NOT counted: SURVEY.md §8d "unique rays"), state resident in HBM, device time
@@ -49,12 +54,45 @@ METRIC = "Mrays/s (primary+bounce), full path tracing"
 WORKLOADS = {
     # name: (W, H, spp, max_depth, mode, description)
     "cornell": dict(W=1024, H=1024, spp=64, max_depth=5, mode=1,
-                    name="Cornell box, BVH, 1024x1024, 64 spp, 4 bounces (BASELINE configs[1])"),
+                    name="Cornell box, 1024x1024, 64 spp, 4 bounces (BASELINE configs[1])"),
     "lucy": dict(W=1920, H=1080, spp=16, max_depth=9, mode=1,
-                 name="Lucy stand-in (524,310 triangles), BVH, 1920x1080, 16 spp, 8 bounces (configs[3] at 1/16 of the samples)"),
+                 name="Lucy stand-in (524,310 triangles), 1920x1080, 16 spp, 8 bounces (configs[3] at 1/16 of the samples)"),
     "lucy256": dict(W=1920, H=1080, spp=256, max_depth=9, mode=1,
-                    name="Lucy stand-in (524,310 triangles), BVH, 1920x1080, 256 spp, 8 bounces (BASELINE configs[3] frame)"),
+                    name="Lucy stand-in (524,310 triangles), 1920x1080, 256 spp, 8 bounces (BASELINE configs[3] frame; north_star target scene)"),
 }
+
+
+def workload_config(args, wl, world, shard, triangles):
+    """`config` of the JSON line: the same keys and values in both arms (ours / reference)."""
+    structure = {"bvh": "BVH" + (" (ours: BVH2 built on the GPU, Morton radix tree)" if args.builder == "gpu" else ""),
+                 "subgrid": "Subgrid / 2Plane hierarchy gs 8 os 8 m 50", "subbeams": "Subbeams gs 6 m 50 depth 1"}[args.structure]
+    if world == 1:
+        par = "1 GPU"
+    elif shard == "tiles":
+        par = f"tiles32x8 round-robin over {world} GPUs, NCCL sum-reduce to rank 0 (bit-identical to 1 GPU)"
+    else:
+        par = f"sample ranges: {world} GPUs x all pixels x spp/{world} from per-rank seeds, NCCL sum-reduce (statistical parity)"
+    return {"workload": wl["name"], "width": wl["W"], "height": wl["H"], "spp": wl["spp"], "max_depth": wl["max_depth"], "nee": 0,
+            "structure": structure, "triangles": int(triangles), "parallelism": par,
+            "l2": "flushed between timed steps (512 MiB fill)"}
+
+
+def choose_shard(args, wl, world):
+    shard = args.shard
+    if shard == "auto":
+        shard = "tiles" if world == 1 or (wl["W"] * wl["H"]) // world >= 400_000 else "samples"
+    return shard if world > 1 else "tiles"
+
+
+def ncu_counters(args):
+    """Measured bound of the path kernel from the committed ncu capture of the same workload / structure
+    (profiles/r2_ncu_counters.json, written by scripts/ncu_counters.py from the .ncu-rep of `bench.py --spp ...`)."""
+    try:
+        tab = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_counters.json")))
+        key = ("cornell" if args.workload == "cornell" else "lucy") + "_" + args.structure
+        return tab.get(key)
+    except Exception:
+        return None
 
 
 def peaks():
@@ -124,6 +162,17 @@ def scene_file(workload, tmpdir):
     return path
 
 
+def cpu_reference_passes(ptbs, wl, spp, timed_passes):
+    """`timed_passes` uninstrumented renders + one counted render of the same deterministic frame in ONE ptref process
+    (oracle/ref/ref_driver.cpp --repeat): the scene load and the reference's constructBVH (26 s on the stand-in) are paid once.
+    Returns ([trace seconds per timed pass], counted record)."""
+    import oracle_lib
+    args = ["--ptbs", ptbs, "--mode", wl["mode"], "--width", wl["W"], "--height", wl["H"], "--spp", spp, "--max-depth", wl["max_depth"],
+            "--nee", 0, "--repeat", timed_passes + 1, "render", "-"]
+    recs = [r for r in oracle_lib.run_ptref(args, timeout=6 * 3600) if r["cmd"] == "render"]
+    return [r["trace_ms"] / 1e3 for r in recs[:-1]], recs[-1]
+
+
 def cpu_reference_run(ptbs, wl, spp):
     """One bounded sample on the CPU.  Returns (unique rays, seconds, kind, threads).
     kind "reference": oracle/_ref/ptref = the reference's own sources; timing from an uninstrumented
@@ -132,11 +181,8 @@ def cpu_reference_run(ptbs, wl, spp):
     import oracle_lib
     ncpu = os.cpu_count() or 1
     if oracle_lib.have_ref():
-        args = ["--ptbs", ptbs, "--mode", wl["mode"], "--width", wl["W"], "--height", wl["H"], "--spp", spp, "--max-depth",
-                wl["max_depth"], "--nee", 0]
-        timed = [r for r in oracle_lib.run_ptref(args + ["--no-count", "render", "-"]) if r["cmd"] == "render"][0]
-        counted = [r for r in oracle_lib.run_ptref(args + ["render", "-"]) if r["cmd"] == "render"][0]
-        return counted["rays_unique"], timed["trace_ms"] / 1e3, "reference", min(16, ncpu)
+        secs, counted = cpu_reference_passes(ptbs, wl, spp, 1)
+        return counted["rays_unique"], secs[0], "reference", min(16, ncpu), counted["rays_traversed"]
     o = oracle_lib.Oracle(ptbs)
     o.build()
     o.configure(wl["W"], wl["H"], wl["mode"], nee=0, max_depth=wl["max_depth"])
@@ -144,34 +190,45 @@ def cpu_reference_run(ptbs, wl, spp):
     _, _, _, st = o.render(spp, threads=ncpu)
     dt = time.perf_counter() - t0
     o.close()
-    return st["rays_unique"], dt, "port", ncpu
+    return st["rays_unique"], dt, "port", ncpu, st["rays_traversed"]
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    import oracle_lib
     wl = WORKLOADS[args.workload]
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     import tempfile
     ptbs = scene_file(args.workload, tempfile.gettempdir())
     spp = args.ref_spp
-    for _ in range(args.warmup):
-        cpu_reference_run(ptbs, wl, 1)
-    rays = secs = 0.0
-    kind, cores = "port", 1
-    for _ in range(args.steps):
-        r, s, kind, cores = cpu_reference_run(ptbs, wl, spp)
-        rays += r
-        secs += s
-    v = rays / secs / 1e6
-    sample = f"{wl['W']}x{wl['H']} frame at {spp} spp per step (of {wl['spp']}), max_depth {wl['max_depth']}, NEE off"
+    ncpu = os.cpu_count() or 1
+    if oracle_lib.have_ref():
+        secs, counted = cpu_reference_passes(ptbs, wl, spp, args.warmup + args.steps)
+        secs = secs[args.warmup:]
+        rays, counted_rays, kind, cores = counted["rays_unique"], counted["rays_traversed"], "reference", min(16, ncpu)
+    else:
+        secs = []
+        for k in range(args.warmup + args.steps):
+            rays, dt, kind, cores, counted_rays = cpu_reference_run(ptbs, wl, spp if k >= args.warmup else 1)
+            if k >= args.warmup:
+                secs.append(dt)
+    total = sum(secs)
+    v = rays * len(secs) / total / 1e6
+    sample = (f"{wl['W']}x{wl['H']} frame at {spp} spp per step (of {wl['spp']}), max_depth {wl['max_depth']}, NEE off; "
+              f"{'reference trace(true), 16 std::threads' if kind == 'reference' else 'oracle port'}; structure build outside the timed region "
+              "like src/main.cpp:97 vs :116")
+    triangles = 202 if args.workload == "cornell" else 524310
     emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+        "warmup": args.warmup, "ms_per_step": total / len(secs) * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["name"], "sample": sample},
-        "spp_per_s": spp * args.steps / secs,
-        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample, "host_cpus": os.cpu_count(),
+        "config": workload_config(args, wl, world, choose_shard(args, wl, world), triangles),
+        "spp_per_s": spp * len(secs) / total,
+        "rays_per_step": rays, "reference_counted_rays_per_step": counted_rays,
+        "value_reference_counted": counted_rays * len(secs) / total / 1e6,
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample, "host_cpus": ncpu,
                          "threads": 16 if kind == "reference" else cores},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -217,9 +274,7 @@ def run_ours(args):
     # Sharding: tiles (bit-identical to the 1-GPU frame) while every GPU keeps >= 400k pixels in flight; below
     # that the serial samples of a pixel starve the lanes and the frame is sharded by sample ranges instead
     # (every rank renders all pixels, spp/N samples from its own seeds; statistical parity)
-    shard = args.shard
-    if shard == "auto":
-        shard = "tiles" if world == 1 or (W * H) // world >= 400_000 else "samples"
+    shard = choose_shard(args, wl, world)
     if shard == "samples" and world > 1:
         base = dict(width=W, height=H, mode=mode, nee=0, max_depth=wl["max_depth"], rank=0, world=1, tile_w=32, tile_h=8, seed_offset=rank)
         my_spp = ptb_b200.multigpu.sample_share(spp, rank, world)
@@ -272,7 +327,7 @@ def run_ours(args):
         step()
     # ---- value: device time, state resident in HBM --------------------------------------------
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    rays = paths = kernels = 0
+    rays = paths = kernels = ref_rays = 0
     ext_ms = logic_ms = 0.0
     ext_launches = 0
     barrier()
@@ -284,7 +339,7 @@ def run_ours(args):
         ev[k][1].record(stream)
         cc = pt.counters()
         st = pt.stage_ms()
-        rays += cc["rays"]; paths += cc["paths"]; kernels += cc["kernels"]
+        rays += cc["rays"]; paths += cc["paths"]; kernels += cc["kernels"]; ref_rays += cc["ref_rays"]
         ext_ms += st["extend_ms"]; logic_ms += st["logic_ms"]; ext_launches += st["extend_launches"]
     barrier()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
@@ -311,12 +366,49 @@ def run_ours(args):
     d2h = W * H * 16
 
     # ---- aggregate over ranks -------------------------------------------------------------------
-    vals = torch.tensor([float(rays), float(paths), float(kernels), float(e2e_rays)], dtype=torch.float64, device=f"cuda:{local}")
+    # ---- parity of THIS process against the reference's golden, outside the timed region -------------------------------
+    parity = None
+    tiles_equal = None
+    if world > 1 and shard == "tiles":
+        # the reduced N-GPU frame (rank 0 holds it after the last e2e step) against a 1-GPU frame of rank 0, bit for bit
+        reduced = host_img.copy() if rank == 0 else None
+        barrier()
+        if rank == 0:
+            pt.set_params(count_tests=0, **dict(base, rank=0, world=1))
+            pt.reset()
+            pt.render(spp)
+            single = pt.read_image()
+            tiles_equal = bool((single.view(np.uint32) == reduced.view(np.uint32)).all())
+        barrier()
+    if rank == 0 and args.workload.startswith("lucy"):
+        import hashlib
+        gpath = os.path.join(ROOT, "tests", "golden", "lucy_standin_ref_1080p.npz")
+        if os.path.isfile(gpath) and W == 1920 and H == 1080:
+            g = np.load(gpath)
+            pt.set_params(count_tests=0, **dict(base, rank=0, world=1, seed_offset=0))
+            t_hit, tri_hit, _ = pt.primary_hits()
+            agree = float((tri_hit == g["tri"]).mean())
+            parity = {"against": "tests/golden/lucy_standin_ref_1080p.npz (unmodified reference, BVH mode, primary rays of every pixel)",
+                      "hit_id_agreement": agree, "hit_ids_differing": int((tri_hit != g["tri"]).sum()),
+                      "t_digest_equal": hashlib.sha256(t_hit.tobytes()).hexdigest() == str(g["t_sha256"]),
+                      "structure_checked": args.structure}
+    elif rank == 0:
+        import hashlib
+        g = np.load(os.path.join(ROOT, "tests", "golden", "configs_ref.npz"))
+        pt.set_params(count_tests=0, **dict(base, rank=0, world=1, seed_offset=0, width=512, height=512))
+        t_hit, tri_hit, _ = pt.primary_hits()
+        parity = {"against": "tests/golden/configs_ref.npz c0 (unmodified reference, Cornell 512x512 primary rays)",
+                  "hit_id_agreement": float((tri_hit == g["c0_tri"]).mean()), "hit_ids_differing": int((tri_hit != g["c0_tri"]).sum()),
+                  "t_digest_equal": hashlib.sha256(t_hit.tobytes()).hexdigest() == str(g["c0_t_sha256"]), "structure_checked": args.structure}
+    if parity is not None and tiles_equal is not None:
+        parity["n_gpu_tile_frame_equals_1_gpu_frame"] = tiles_equal
+
+    vals = torch.tensor([float(rays), float(paths), float(kernels), float(e2e_rays), float(ref_rays)], dtype=torch.float64, device=f"cuda:{local}")
     tmax = torch.tensor([dev_ms, e2e_s, ext_ms, logic_ms], dtype=torch.float64, device=f"cuda:{local}")
     if dist is not None:
         dist.all_reduce(vals, op=dist.ReduceOp.SUM)
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    rays_all, paths_all, kernels_all, e2e_rays_all = (float(x) for x in vals.tolist())
+    rays_all, paths_all, kernels_all, e2e_rays_all, ref_rays_all = (float(x) for x in vals.tolist())
     dev_ms_max, e2e_s_max, ext_ms_max, logic_ms_max = (float(x) for x in tmax.tolist())
 
     result = None
@@ -337,39 +429,51 @@ def run_ours(args):
         ext_share = ext_ms / (ext_ms + logic_ms) if ext_ms + logic_ms > 0 else 0.0
         ext_time_ms = dev_ms * ext_share
         ach = bytes_per_ray * rays / (ext_time_ms / 1e3) / 1e9 if ext_time_ms > 0 else None
+        kname = {"bvh": "k_mega<BVH>", "subgrid": "k_mega<TWO_PLANE>", "subbeams": "k_mega<SUB_BEAMS>"}[args.structure]
+        roofline = {"bound": "hbm", "kernel": (kname + " (one fused launch per render: raygen + traversal + shade + accumulate)") if ext_launches == args.steps else "k_extend_bvh",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None,
+                    "frac_is": "ALGORITHMIC bytes (SURVEY.md 8d) / kernel time / measured HBM copy peak: nominal, the structure is L1/L2 resident; "
+                               "the bound that binds is `lane_issue_frac` below",
+                    "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_kind,
+                    "bytes_per_ray": bytes_per_ray, "boxes_per_ray": boxes_per_ray, "tris_per_ray": tris_per_ray,
+                    "avg_launch_ms": ext_time_ms / max(1, ext_launches), "launches": ext_launches,
+                    "avg_launch_event_ms": ext_ms / max(1, ext_launches),
+                    "share_of_step": ext_share, "logic_share_of_step": 1.0 - ext_share,
+                    "overlap": (ext_ms + logic_ms) / dev_ms if dev_ms > 0 else None}
+        nc = ncu_counters(args)
+        if nc:  # measured by ncu on the same workload (committed capture; refreshed whenever the kernel changes)
+            roofline.update({"binding_bound": "issue slots at the lane occupancy divergence leaves (not HBM)",
+                             "lanes_per_inst": nc["lanes_per_inst"], "issue_active_pct": nc["issue_active_pct"],
+                             "lane_issue_frac": nc["issue_active_pct"] / 100.0 * nc["lanes_per_inst"] / 32.0,
+                             "dram_gbs": nc["dram_gbs"], "dram_frac_of_peak": nc["dram_gbs"] / peak, "l2_gbs": nc["l2_gbs"],
+                             "l1_hit_pct": nc.get("l1_hit_pct"), "l2_hit_pct": nc.get("l2_hit_pct"), "ncu_source": nc["source"]})
+            traffic = nc["dram_bytes_per_ray"] * rays / max(1, ext_launches)
+            roofline["traffic"], roofline["traffic_source"] = traffic, nc["source"]
         result = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["name"], "width": W, "height": H, "spp": spp, "max_depth": wl["max_depth"], "nee": 0,
-                       "structure": {"bvh": "BVH2, 64-byte two-box nodes" + (" (built on the GPU: Morton radix tree)" if args.builder == "gpu" else " (host binned SAH)"), "subgrid": "Subgrid / 2Plane hierarchy gs 8 os 8 m 50",
-                                     "subbeams": "Subbeams gs 6 m 50 depth 1"}[args.structure], "triangles": int(scene["pos"].shape[0]),
-                       "parallelism": "1 GPU" if world == 1 else (f"tiles32x8 round-robin over {world} GPUs, NCCL sum-reduce to rank 0 (bit-identical to 1 GPU)"
-                                                                 if shard == "tiles" else
-                                                                 f"sample ranges: {world} GPUs x all pixels x spp/{world} from per-rank seeds, NCCL sum-reduce (statistical parity)"),
-                       "l2": "flushed between timed steps (512 MiB fill)", "bvh_build_s": round(build_s, 3)},
+            "config": workload_config(args, wl, world, shard, scene["pos"].shape[0]),
+            "structure_build_s": round(build_s, 3),
             "spp_per_s": spp * args.steps / (dev_ms_max / 1e3),
             "mpaths_per_s": paths_all / (dev_ms_max / 1e3) / 1e6,
             "rays_per_step": rays_all / args.steps,
+            "reference_counted_rays_per_step": ref_rays_all / args.steps,  # incl. the reference's re-traced misses
+            "value_reference_counted": ref_rays_all / (dev_ms_max / 1e3) / 1e6,
+            "parity": parity,
             "gpu_launches": int(kernels_all),
             "clocks": clk,
             "e2e": {"value": e2e_rays_all / e2e_s_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_s_max / args.steps * 1e3},
-            "roofline": {"bound": "hbm", "kernel": "k_mega<BVH> (fused traversal + shade)" if ext_launches == args.steps else "k_extend_bvh", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": (ach / peak) if ach else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_kind,
-                         "bytes_per_ray": bytes_per_ray, "boxes_per_ray": boxes_per_ray, "tris_per_ray": tris_per_ray,
-                         "avg_launch_ms": ext_time_ms / max(1, ext_launches), "launches": ext_launches,
-                         "avg_launch_event_ms": ext_ms / max(1, ext_launches),
-                         "share_of_step": ext_share, "logic_share_of_step": 1.0 - ext_share,
-                         "overlap": (ext_ms + logic_ms) / dev_ms if dev_ms > 0 else None},
+            "roofline": roofline,
         }
     pt.close()
     if rank == 0 and world == 1 and not args.no_cpu:
         import tempfile
         ptbs = scene_file(args.workload, tempfile.gettempdir())
-        r, s, kind, cores = cpu_reference_run(ptbs, wl, args.cpu_spp)
+        r, s, kind, cores, r_counted = cpu_reference_run(ptbs, wl, args.cpu_spp)
         result["cpu_baseline"] = {
-            "value": r / s / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind, "host_cpus": os.cpu_count(),
+            "value": r / s / 1e6, "value_reference_counted": r_counted / s / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind, "host_cpus": os.cpu_count(),
             "threads": 16 if kind == "reference" else cores, "seconds": s,
             "sample": f"same {W}x{H} frame at {args.cpu_spp} spp (of {spp}), max_depth {wl['max_depth']}, NEE off, "
                       f"{'reference trace(true), 16 std::threads' if kind == 'reference' else 'oracle port'}"}
@@ -409,8 +513,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS))
-    ap.add_argument("--cpu-spp", type=int, default=8, help="spp of the bounded cpu_baseline sample")
+    ap.add_argument("--workload", default="lucy256", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-spp", type=int, default=0, help="spp of the bounded cpu_baseline sample (0: 8 for Cornell, 4 for the Lucy frame)")
     ap.add_argument("--ref-spp", type=int, default=4, help="spp per step of the --impl reference arm")
     ap.add_argument("--structure", default="bvh", choices=["bvh", "subgrid", "subbeams"],
                     help="acceleration structure (subgrid: gs 8 / os 8 / m 50 like the published runs; subbeams: gs 6 / m 50 / depth 1)")
@@ -428,6 +532,8 @@ def main():
         rw, rh = (int(v) for v in args.res.lower().split("x"))
         WORKLOADS[args.workload] = dict(WORKLOADS[args.workload], W=rw, H=rh,
                                         name=WORKLOADS[args.workload]["name"] + f" [frame overridden to {rw}x{rh}]")
+    if args.cpu_spp <= 0:
+        args.cpu_spp = 8 if args.workload == "cornell" else 4
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
     world = int(os.environ.get("WORLD_SIZE", "1"))
