@@ -6,7 +6,7 @@ The directory name carries a hyphen (it mirrors the reference repository's name)
 or through the repo-root shim `ptb_b200.py`.
 """
 from .api import (  # noqa: F401
-    LIB_PATH, REF_BVH_NODE, MODE_ALL, MODE_BVH, MODE_NAMES, MODE_SUB_BEAMS, MODE_TWO_PLANE, SYMBOLS, Camera, Params, PathTracer, PathTracerGroup, PtbError,
+    LIB_PATH, REF_BVH_NODE, REF_GRID, MODE_ALL, MODE_BVH, MODE_NAMES, MODE_SUB_BEAMS, MODE_TWO_PLANE, SYMBOLS, Camera, Params, PathTracer, PathTracerGroup, PtbError,
     convert_scene_file, load_library,
 )
 from .build import build_native  # noqa: F401

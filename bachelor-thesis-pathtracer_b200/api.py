@@ -25,7 +25,7 @@ SYMBOLS = (
     "ptb_build_bvh_gpu", "ptb_last_build_ms", "ptb_bvh_depth", "ptb_build_subgrid_gpu", "ptb_build_subbeams_gpu", "ptb_last_build_device_ms", "ptb_structure_digest", "ptb_upload_ref_bvh", "ptb_use_ref_bvh", "ptb_upload_textures",
     "ptb_group_create", "ptb_group_destroy", "ptb_group_size", "ptb_group_ctx", "ptb_group_last_error", "ptb_group_peer_direct",
     "ptb_group_set_params", "ptb_group_reset", "ptb_group_clear", "ptb_group_render", "ptb_group_read_image", "ptb_group_read_counters",
-    "ptb_group_last_render_ms", "ptb_group_set_sharding", "ptb_trace_rays_static", "ptb_trace_rays_static_max",
+    "ptb_group_last_render_ms", "ptb_group_set_sharding", "ptb_trace_rays_static", "ptb_trace_rays_static_max", "ptb_tone_thresholds", "ptb_upload_subgrid", "ptb_ref_subgrid_bytes",
 )
 
 
@@ -43,6 +43,12 @@ class Params(ctypes.Structure):
 # ptb_ref_bvh_node (include/ptb.h): BvhNode (bvh.h:14-24) with its box inlined, 48 bytes
 REF_BVH_NODE = np.dtype([("bmin", np.float32, 3), ("start_idx", np.int32), ("bmax", np.float32, 3), ("end_idx", np.int32),
                          ("child_left", np.int32), ("child_right", np.int32), ("has_tris", np.int32), ("pad", np.int32)])
+
+
+# ptb_ref_grid (include/ptb.h): Grid (lightFieldGrid.h:10-22) without its vectors, 80 bytes
+REF_GRID = np.dtype([("aabb_min", np.float32, 3), ("size", np.uint32), ("aabb_max", np.float32, 3), ("has_tris", np.uint32),
+                     ("min", np.float32, 3), ("splitting_axis", np.int32), ("max", np.float32, 3), ("n_cells", np.uint32),
+                     ("inv_delta", np.float32, 3), ("n_indices", np.uint32)])
 
 
 class Texture(ctypes.Structure):  # ptb_texture
@@ -133,6 +139,10 @@ def load_library():
     L.ptb_primary_hits.argtypes = [vp, vp, vp, vp]
     L.ptb_trace_rays.argtypes = [vp, vp, cu64, ci, vp, vp]
     L.ptb_trace_rays_device.argtypes = [vp, vp, cu64, ci, vp, vp]
+    L.ptb_tone_thresholds.argtypes = [vp]
+    L.ptb_upload_subgrid.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, cu64, vp, cu64]
+    L.ptb_ref_subgrid_bytes.restype = cu64
+    L.ptb_ref_subgrid_bytes.argtypes = [vp]
     L.ptb_trace_rays_static.argtypes = [vp, vp, cu64, vp, vp]
     L.ptb_trace_rays_static_max.restype = cu64
     L.ptb_trace_rays_static_max.argtypes = []
@@ -261,6 +271,15 @@ class PathTracer:
         object_roots = np.ascontiguousarray(object_roots, np.int32)
         self._ck(self.L.ptb_upload_ref_bvh(self.h, _ptr(nodes), nodes.shape[0], _ptr(indices), indices.shape[0], _ptr(object_roots),
                                            object_roots.shape[0], int(scene_root)), "ptb_upload_ref_bvh")
+
+    def upload_subgrid(self, grids, lut_start, lut_end, indices):
+        """The reference's own Subgrid hierarchy (structured array of REF_GRID + its pools); see ptb_upload_subgrid."""
+        grids = np.ascontiguousarray(grids, REF_GRID)
+        lut_start = np.ascontiguousarray(lut_start, np.uint32)
+        lut_end = np.ascontiguousarray(lut_end, np.uint32)
+        indices = np.ascontiguousarray(indices, np.uint32)
+        self._ck(self.L.ptb_upload_subgrid(self.h, _ptr(grids), grids.shape[0], _ptr(lut_start), _ptr(lut_end), lut_start.shape[0],
+                                           _ptr(indices), indices.shape[0]), "ptb_upload_subgrid")
 
     def use_ref_bvh(self, on=True):
         """Mode BVH walks the uploaded reference tree: counters and heat maps become the reference's own numbers."""

@@ -123,6 +123,7 @@ struct ptb_ctx {
     double lastBuildDeviceMs = 0.0; // device part of the last *_gpu build (CUDA events)
     std::vector<uint32_t> triOfId; // reference id -> leaf position
     uint64_t gridBytes = 0, beamBytes = 0;
+    uint64_t refGridBytes = 0; // getMemory2Plane of the uploaded reference grids (ptb_upload_subgrid)
     uint64_t beamCounts[3] = {0, 0, 0}; // beams, leaf entries, root-table entries per axis (ptb_structure_digest)
     uint64_t gridCounts[3] = {0, 0, 0}; // grids, LUT cells, index entries (ptb_structure_digest)
 
@@ -1543,6 +1544,41 @@ extern "C" int ptb_write_state(ptb_ctx *c, const float *rgba, const int32_t *sam
     return PTB_OK;
 }
 
+// the reference's display expression (window.cpp:513-522) per channel, evaluated with the host libm
+static unsigned char tone_byte_host(float v) {
+    float p = powf(v, 0.4545f);
+    p = fminf(p, 1.0f);
+    return (unsigned char)(p * 255);
+}
+// t[b] = smallest float v in [0, 1] with tone_byte_host(v) >= b: binary search over the bit patterns (non-negative floats
+// order like their bits); the step function is non-decreasing (checked exhaustively by tests/native/tonemap_check.cpp)
+static const ToneTable &tone_thresholds() {
+    static ToneTable T;
+    static bool built = false;
+    if (!built) {
+        T.t[0] = 0.0f;
+        for (int b = 1; b < 256; ++b) {
+            uint32_t lo = 0u, hi = 0x3f800000u; // byte(1.0f) = 255 >= b
+            while (lo < hi) {
+                const uint32_t mid = lo + (hi - lo) / 2;
+                float v;
+                memcpy(&v, &mid, 4);
+                if (tone_byte_host(v) >= b) hi = mid;
+                else lo = mid + 1;
+            }
+            memcpy(&T.t[b], &lo, 4);
+        }
+        built = true;
+    }
+    return T;
+}
+// for tests: the table the kernel searches
+extern "C" int ptb_tone_thresholds(float out[256]) {
+    if (!out) return PTB_ERR_INVALID;
+    memcpy(out, tone_thresholds().t, sizeof(float) * 256);
+    return PTB_OK;
+}
+
 extern "C" int ptb_read_rgba8(ptb_ctx *c, uint8_t *rgba8, int tone_mapping) {
     GUARD(c);
     SETTLE(c);
@@ -1550,7 +1586,7 @@ extern "C" int ptb_read_rgba8(ptb_ctx *c, uint8_t *rgba8, int tone_mapping) {
     const uint32_t n = (uint32_t)c->W * c->H;
     uchar4 *d = nullptr;
     CK(cudaMalloc(&d, (size_t)n * 4));
-    k_tonemap<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, d, n, tone_mapping);
+    k_tonemap<<<grid_for(c), 256, 0, c->stream>>>(c->F.image, d, n, tone_mapping, tone_thresholds());
     c->counters[PTB_CNT_KERNELS]++;
     cudaError_t e = cudaMemcpyAsync(rgba8, d, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
@@ -1641,6 +1677,7 @@ static int ptb_build_subgrid_impl(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t
     c->gridBytes = R.hdr.size() * sizeof(GridHdr) + R.lut.size() * sizeof(GridCell) + R.idx.size() * sizeof(uint32_t);
     c->gridCounts[0] = R.hdr.size(); c->gridCounts[1] = R.lut.size(); c->gridCounts[2] = R.idx.size();
     c->gridBuilt = true;
+    c->S.ref_grids = 0;
     return PTB_OK;
 }
 
@@ -1674,6 +1711,7 @@ static int ptb_build_subgrid_gpu_impl(ptb_ctx *c, uint32_t gs, uint32_t os, uint
     c->gridBytes = D.n_grids * sizeof(GridHdr) + D.n_cells * sizeof(GridCell) + D.n_idx * sizeof(uint32_t);
     c->gridCounts[0] = D.n_grids; c->gridCounts[1] = D.n_cells; c->gridCounts[2] = D.n_idx;
     c->gridBuilt = true;
+    c->S.ref_grids = 0;
     c->lastBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     c->lastBuildDeviceMs = D.ms;
     return PTB_OK;
@@ -1811,6 +1849,105 @@ static int ptb_build_subbeams_gpu_impl(ptb_ctx *c, uint32_t gs, uint32_t m) {
 }
 
 // =============================================================================================
+// ptb_upload_subgrid: the reference's own Subgrid hierarchy
+// =============================================================================================
+// Takes std::vector<Grid> (lightFieldGrid.h:10-22) flattened — one ptb_ref_grid per Grid plus its three vectors concatenated
+// in grid order — and lays it out in the device pools subgrid_closest walks (64-byte header, {start,end} cells, index pool).
+// intersectGrid (lightFieldGrid.cpp:71-147) and subgrid_closest are the same statements, so over these grids the two test
+// counters and the heat maps are the reference's numbers.  The input is untrusted: every range, link and the nesting depth
+// are checked before anything reaches the device.
+static int ptb_upload_subgrid_impl(ptb_ctx *c, const ptb_ref_grid *grids, uint32_t n_grids, const uint32_t *lut_start, const uint32_t *lut_end,
+                                   uint64_t n_cells, const uint32_t *indices, uint64_t n_indices) {
+    GUARD(c);
+    SETTLE(c);
+    if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (it lays out the triangles the grids index)");
+    if (!grids || n_grids < 3) return fail(c, PTB_ERR_INVALID, "reference grids: at least the three axis roots are needed");
+    if ((n_cells && (!lut_start || !lut_end)) || (n_indices && !indices)) return fail(c, PTB_ERR_INVALID, "reference grids: null pools");
+    if (n_cells >= (1ull << 32) || n_indices >= (1ull << 32)) return fail(c, PTB_ERR_INVALID, "reference grids: pools exceed 2^32 entries");
+    const uint64_t nTris = c->mat.size();
+    std::vector<GridHdr> hdr(n_grids);
+    std::vector<GridCell> lut((size_t)n_cells);
+    std::vector<uint32_t> idx((size_t)n_indices);
+    std::vector<int> depth(n_grids, 1); // inner grids nested below and including g (the slice stack of subgrid_closest_slices)
+    uint64_t cellAt = 0, idxAt = 0;
+    std::vector<uint64_t> cellBase(n_grids), idxBase(n_grids);
+    for (uint32_t g = 0; g < n_grids; ++g) {
+        const ptb_ref_grid &G = grids[g];
+        const std::string at = "reference grid " + std::to_string(g) + ": ";
+        if (G.size < 1 || G.size > 256) return fail(c, PTB_ERR_INVALID, at + "size out of range");
+        const uint64_t want = (uint64_t)G.size * G.size * G.size * G.size;
+        if (G.n_cells != want) return fail(c, PTB_ERR_INVALID, at + "LUT has " + std::to_string(G.n_cells) + " cells, size^4 = " + std::to_string(want));
+        if (G.splitting_axis < 0 || G.splitting_axis > 2) return fail(c, PTB_ERR_INVALID, at + "splitting axis");
+        if (cellAt + G.n_cells > n_cells || idxAt + G.n_indices > n_indices) return fail(c, PTB_ERR_INVALID, at + "pools shorter than the grids claim");
+        // the walk derives grid.max[axis] as aabb.max[axis] + 0.1f (adjustGridSize, lightFieldGrid.cpp:176-178): hold the input to it
+        const float derived = G.aabb_max[G.splitting_axis] + 0.1f;
+        if (memcmp(&derived, &G.max[G.splitting_axis], 4) != 0)
+            return fail(c, PTB_ERR_INVALID, at + "max[axis] is not aabb.max[axis] + 0.1f (not a grid constructGrid built)");
+        cellBase[g] = cellAt;
+        idxBase[g] = idxAt;
+        GridHdr &H = hdr[g];
+        for (int k = 0; k < 3; ++k) {
+            H.amin[k] = G.aabb_min[k];
+            H.amax[k] = G.aabb_max[k];
+            H.gmin[k] = G.min[k];
+            H.inv_delta[k] = G.inv_delta[k];
+        }
+        H.size_flags = G.size | (G.has_tris ? 0x80000000u : 0u);
+        H.lut_base = (uint32_t)cellAt;
+        H.pad0 = H.pad1 = 0;
+        for (uint64_t k = 0; k < G.n_cells; ++k) {
+            const uint32_t s0 = lut_start[cellAt + k], e0 = lut_end[cellAt + k];
+            if (s0 > e0 || e0 > G.n_indices) return fail(c, PTB_ERR_INVALID, at + "LUT cell outside the grid's index list");
+            lut[cellAt + k] = GridCell{(uint32_t)(idxAt + s0), (uint32_t)(idxAt + e0)};
+        }
+        for (uint64_t k = 0; k < G.n_indices; ++k) {
+            const uint32_t v = indices[idxAt + k];
+            if (G.has_tris) {
+                if (v >= nTris) return fail(c, PTB_ERR_INVALID, at + "triangle id out of range");
+                idx[idxAt + k] = c->triOfId[v]; // reference triangle id -> leaf position
+            } else {
+                // children are constructed after their parent (lightFieldGrid.cpp:857-859), object grids after the roots: a
+                // larger id — which also rules out cycles
+                if (v >= n_grids || v <= g) return fail(c, PTB_ERR_INVALID, at + "child grid id out of range or not after its parent");
+                if (grids[v].splitting_axis != G.splitting_axis) return fail(c, PTB_ERR_INVALID, at + "child grid of another axis");
+                idx[idxAt + k] = v;
+            }
+        }
+        cellAt += G.n_cells;
+        idxAt += G.n_indices;
+    }
+    if (cellAt != n_cells || idxAt != n_indices) return fail(c, PTB_ERR_INVALID, "reference grids: pools longer than the grids claim");
+    for (uint32_t g = n_grids; g-- > 0;) { // children have larger ids: their depth is final when the parent is reached
+        if (grids[g].has_tris) continue;
+        int d = 0;
+        for (uint64_t k = 0; k < grids[g].n_indices; ++k) d = std::max(d, depth[indices[idxBase[g] + k]]);
+        depth[g] = d + 1;
+    }
+    const int deepest = std::max(depth[0], std::max(depth[1], depth[2]));
+    if (deepest > PTB_GDEPTH)
+        return fail(c, PTB_ERR_INVALID, "reference grids nest " + std::to_string(deepest) + " deep, the walk's stack holds " + std::to_string(PTB_GDEPTH));
+    devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
+    c->gridBuilt = false;
+    CK(cudaMalloc(&c->dGridHdr, hdr.size() * sizeof(GridHdr)));
+    CK(cudaMalloc(&c->dGridLut, std::max<size_t>(1, lut.size()) * sizeof(GridCell)));
+    CK(cudaMalloc(&c->dGridIdx, std::max<size_t>(1, idx.size()) * sizeof(uint32_t)));
+    CK(cudaMemcpy(c->dGridHdr, hdr.data(), hdr.size() * sizeof(GridHdr), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->dGridLut, lut.data(), lut.size() * sizeof(GridCell), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->dGridIdx, idx.data(), idx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    c->S.grid_hdr = reinterpret_cast<const float4 *>(c->dGridHdr);
+    c->S.grid_lut = c->dGridLut;
+    c->S.grid_idx = c->dGridIdx;
+    c->gridBytes = hdr.size() * sizeof(GridHdr) + lut.size() * sizeof(GridCell) + idx.size() * sizeof(uint32_t);
+    c->gridCounts[0] = hdr.size(); c->gridCounts[1] = lut.size(); c->gridCounts[2] = idx.size();
+    // getMemory2Plane (lightFieldGrid.cpp:60-68) of what was handed over: 288-byte Grid objects + three u32 vectors
+    c->refGridBytes = (uint64_t)n_grids * 288u + 4u * (2u * n_cells + n_indices);
+    c->gridBuilt = true;
+    c->S.ref_grids = 1; // re-traced misses add their (identical) tests again, like the CPU does (tracer.cpp:127-132)
+    return PTB_OK;
+}
+extern "C" uint64_t ptb_ref_subgrid_bytes(const ptb_ctx *c) { return (c && c->gridBuilt && c->S.ref_grids) ? c->refGridBytes : 0; }
+
+// =============================================================================================
 // exception barrier of the entry points that allocate from caller- or file-supplied sizes
 // =============================================================================================
 // C++ exceptions (std::bad_alloc / length_error from a corrupt count, anything a builder throws) must not cross the extern "C"
@@ -1936,4 +2073,8 @@ extern "C" int ptb_trace_rays_static(ptb_ctx *c, const float *od6, uint64_t n, f
     c->counters[PTB_CNT_KERNELS]++;
     c->counters[PTB_CNT_RAYS] += n;
     return PTB_OK;
+}
+extern "C" int ptb_upload_subgrid(ptb_ctx *c, const ptb_ref_grid *grids, uint32_t n_grids, const uint32_t *lut_start, const uint32_t *lut_end,
+                                  uint64_t n_cells, const uint32_t *indices, uint64_t n_indices) {
+    return guarded(c, [&]() { return ptb_upload_subgrid_impl(c, grids, n_grids, lut_start, lut_end, n_cells, indices, n_indices); });
 }

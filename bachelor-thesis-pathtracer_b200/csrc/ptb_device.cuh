@@ -101,6 +101,7 @@ struct SceneDev {
     const int *__restrict__ ref_obj_root;    // Object::root per object
     const uint32_t *__restrict__ ref_tri_pos; // reference triangle id -> leaf position in `tri`
     int ref_root;
+    int ref_grids; // the Subgrid pools hold the reference's own hierarchy (ptb_upload_subgrid): count re-traced misses like the CPU
 };
 
 // ---- Moeller-Trumbore: src/primitives/triangle.cpp:7-52, positions only --------------------

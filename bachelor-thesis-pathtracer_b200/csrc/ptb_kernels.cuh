@@ -795,8 +795,20 @@ __global__ void k_reset(float4 *image, int *samples, uint32_t *rng, int W, int H
     }
 }
 
-// display transform, window.cpp:507-531: Reinhard, pow(c, 0.4545f), clamp, (u8)(c*255)
-__global__ void k_tonemap(const float4 *__restrict__ image, uchar4 *__restrict__ out, uint32_t n, int tone) {
+// display transform, window.cpp:507-531: c / (1 + c), std::powf(c, 0.4545f), fminf(c, 1), (unsigned char)(c * 255).
+// Byte work, so it has to be byte-exact, and CUDA's powf is not glibc's.  For the fixed exponent the byte is a non-decreasing
+// step function of v = c / (1 + c) on [0, 1] (IEEE division, identical on both sides): the host evaluates the reference's
+// expression with its own libm once and hands over, per byte value b, the smallest float whose byte is >= b
+// (ptb_api.cu: tone_thresholds; tests/native/tonemap_check.cpp checks the step function over all 2^30 floats of [0, 1]).
+// The kernel counts thresholds <= v by binary search: no powf on the device.  What the reference does outside [0, 1]:
+// v < 0 or NaN (negative or NaN or infinite radiance) -> powf gives NaN -> fminf(NaN, 1) = 1 -> 255.
+struct ToneTable {
+    float t[256]; // t[0] unused; t[b] = smallest v in [0, 1] with byte(v) >= b
+};
+__global__ void k_tonemap(const float4 *__restrict__ image, uchar4 *__restrict__ out, uint32_t n, int tone, ToneTable T) {
+    __shared__ float th[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) th[i] = T.t[i];
+    __syncthreads();
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         const float4 c4 = image[p];
         float c[3] = {c4.x, c4.y, c4.z};
@@ -805,10 +817,22 @@ __global__ void k_tonemap(const float4 *__restrict__ image, uchar4 *__restrict__
             float v = c[k];
             if (tone) {
                 v = v / (1.0f + v);
-                v = powf(v, 0.4545f);
+                if (!(v >= 0.0f)) { // NaN or negative (-0.0f compares equal to 0 and lands in the search: byte 0, like powf(-0) = 0)
+                    b[k] = 255;
+                    continue;
+                }
+                int lo = 0, hi = 255; // largest b in [0, 255] with th[b] <= v (th[0] = 0)
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (th[mid] <= v) lo = mid;
+                    else hi = mid - 1;
+                }
+                b[k] = (unsigned char)lo;
+            } else {
+                // x86: cvttss2si to int32, low byte kept; radiance is non-negative, so only the clamp and NaN (-> 0) matter
+                v = fminf(v, 1.0f);
+                b[k] = (v == v) ? (unsigned char)(int)(v * 255) : (unsigned char)0;
             }
-            v = fminf(v, 1.0f);
-            b[k] = (unsigned char)(v * 255);
         }
         out[p] = make_uchar4(b[0], b[1], b[2], 255);
     }

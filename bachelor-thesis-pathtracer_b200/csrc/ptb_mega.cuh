@@ -214,13 +214,22 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
                         for (;;) {
                             ps.depth++;
                             if (P.max_depth > 0 && ps.depth >= P.max_depth) break;
+                            // the reference walks its structure again for the unchanged ray: same tests (counted when the structure
+                            // is the reference's own: its tree, MODE 4, or its grids, ptb_upload_subgrid)
+                            const bool recount = COUNT && (MODE == 4 || (MODE == 2 && S.ref_grids));
                             if (roulette(ps.rng, ps.depth, ps.tp)) {
-                                if (MODE == 2 && P.quirks) cRef++;
+                                if (MODE == 2 && P.quirks) { // TWO_PLANE traverses the killed ray once more (A.4)
+                                    cRef++;
+                                    if (recount) {
+                                        cTri += nTri;
+                                        cAS += nAS;
+                                    }
+                                }
                                 ps.depth++;
                                 break;
                             }
                             cRef++;
-                            if (COUNT && MODE == 4) { // the reference walks its tree again for the unchanged ray: same tests
+                            if (recount) {
                                 cTri += nTri;
                                 cAS += nAS;
                             }

@@ -10,8 +10,10 @@ code (unavailable on this box); the PNG here is written by `write_png` below.
 "Rendering Time" brackets what main.cpp:116-125 brackets: initTracer (reset of image / samples / RNG) and the trace;
 structure construction happens before, in initScene (main.cpp:97).  With `ref_tree` (the reference's own BVH as exported
 by its accessors, ptb_upload_ref_bvh) the BVH counters are the CPU tracer's numbers exactly; otherwise they
-count visits of this library's 64-byte nodes.  "Memory Consumption" is the device footprint of the structure
-(ptb_structure_bytes), the counterpart of getMemoryBVH / getMemory2Plane (bvh.cpp:30-32, lightFieldGrid.cpp:60-68).
+count visits of this library's 64-byte nodes.  Likewise with `ref_grids` (the reference's own std::vector<Grid>,
+ptb_upload_subgrid) the Subgrids block carries the CPU tracer's numbers exactly, and its "Memory Consumption" is
+getMemory2Plane of those grids (lightFieldGrid.cpp:60-68).  Otherwise "Memory Consumption" is the device footprint of the
+structure (ptb_structure_bytes), the counterpart of getMemoryBVH / getMemory2Plane (bvh.cpp:30-32).
 """
 import os
 import struct
@@ -69,14 +71,17 @@ def file_name(mode, debug_view, show_tris):  # window.cpp:542-543
 
 
 def run(pt, samples=100, gs=10, os_=5, m=40, two_plane_only=False, width=1280, height=720, debug_scale=10, max_depth=0,
-        out_dir="./render", ref_tree=None, gpu_builders=True, emit=print):
+        out_dir="./render", ref_tree=None, ref_grids=None, gpu_builders=True, emit=print):
     """`pt`: a PathTracer with the scene uploaded.  Returns the per-mode records it printed."""
     os.makedirs(out_dir, exist_ok=True)
     # initScene (main.cpp:97): both structures are built before the clock starts
     pt.build_bvh()
     if ref_tree is not None:
         pt.upload_ref_bvh(*ref_tree)
-    pt.build_subgrid(gs, os_, m, gpu=gpu_builders)
+    if ref_grids is not None:
+        pt.upload_subgrid(*ref_grids)
+    else:
+        pt.build_subgrid(gs, os_, m, gpu=gpu_builders)
     emit("starting test")
     records = []
     for mode in ((MODE_TWO_PLANE,) if two_plane_only else (MODE_BVH, MODE_TWO_PLANE)):
@@ -93,6 +98,8 @@ def run(pt, samples=100, gs=10, os_=5, m=40, two_plane_only=False, width=1280, h
                 c = pt.counters()
                 rec = {"mode": mode, "rendering_time_ms": ms, "device_ms": pt.last_ms(), "tri_tests": c["tri_tests"],
                        "as_tests": c["as_tests"], "memory": pt.structure_bytes(mode), "files": []}
+                if mode == MODE_TWO_PLANE and ref_grids is not None:
+                    rec["memory"] = int(pt.L.ptb_ref_subgrid_bytes(pt.h))
                 emit("Rendering Time: %f" % ms)
                 emit("Triangle Intersections: %d " % c["tri_tests"])
                 emit("AS Intersections: %d " % c["as_tests"])

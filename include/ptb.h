@@ -145,6 +145,28 @@ int ptb_upload_ref_bvh(ptb_ctx *ctx, const ptb_ref_bvh_node *nodes, uint32_t n_n
                        const int32_t *object_roots, uint32_t n_objects, int32_t scene_root);
 int ptb_use_ref_bvh(ptb_ctx *ctx, int on);
 int ptb_build_subgrid(ptb_ctx *ctx, uint32_t gs, uint32_t os, uint32_t m); /* setGridSettings + constructGrid, lightFieldGrid.h:24,26 */
+/* The reference's own Subgrid hierarchy for count-exact traversal: one record per Grid of
+ * std::vector<Grid> (lightFieldGrid.h:10-22, the file-static `grids` of lightFieldGrid.cpp:23; grids 0..2 are the roots per dominant
+ * axis) and its three vectors concatenated in grid order — gridLutStart / gridLutEnd stay relative to the grid's own `indicies`,
+ * which hold reference triangle ids (has_tris) or child grid ids.  The pools replace whatever ptb_build_subgrid[_gpu] built; mode
+ * TWO_PLANE then walks them exactly like intersectGrid (lightFieldGrid.cpp:71-147): same hits and frames, and PTB_CNT_TRI_TESTS /
+ * PTB_CNT_AS_TESTS and the debug_view heat maps are the reference's own numbers (tracer.cpp:127-142), re-traced misses included.
+ * Validated on upload (ranges, links, one axis per hierarchy, nesting depth); a later ptb_build_subgrid[_gpu] replaces them again. */
+typedef struct ptb_ref_grid {
+    float aabb_min[3];
+    uint32_t size;
+    float aabb_max[3];
+    uint32_t has_tris;
+    float min[3];
+    int32_t splitting_axis;
+    float max[3];
+    uint32_t n_cells;   /* gridLutStart.size() == gridLutEnd.size() == size^4 */
+    float inv_delta[3];
+    uint32_t n_indices; /* indicies.size() */
+} ptb_ref_grid;
+int ptb_upload_subgrid(ptb_ctx *ctx, const ptb_ref_grid *grids, uint32_t n_grids, const uint32_t *lut_start, const uint32_t *lut_end,
+                       uint64_t n_cells, const uint32_t *indices, uint64_t n_indices);
+uint64_t ptb_ref_subgrid_bytes(const ptb_ctx *ctx); /* getMemory2Plane (lightFieldGrid.cpp:60-68) of the uploaded grids; 0 if none */
 /* constructGrid with the size^4 channel loop on the device (lightFieldGrid.cpp:381-414,493-583 with
  * the separating-axis tests of src/types/sat.cpp): one GPU thread per (grid, channel), count -> scan -> fill.  Same pools
  * as ptb_build_subgrid byte for byte (both evaluate csrc/ptb_sat.h). */
@@ -200,6 +222,9 @@ int ptb_read_image(ptb_ctx *ctx, float *rgba);                       /* tracerGe
 int ptb_read_state(ptb_ctx *ctx, int32_t *samples, uint32_t *rng);   /* samples[][] / randomStates[][] (tracer.cpp:25-26), y*W+x */
 int ptb_write_state(ptb_ctx *ctx, const float *rgba, const int32_t *samples, const uint32_t *rng); /* resume a dumped render */
 int ptb_read_rgba8(ptb_ctx *ctx, uint8_t *rgba8, int tone_mapping);  /* display transform, window.cpp:507-531 (bytes R,G,B,255) */
+/* The 255 steps of that transform (window.cpp:513-522 per channel, tone mapping on): out[b] = the smallest v = c/(1+c) in [0,1]
+ * whose byte is >= b, found with the host's libm (the reference's powf); out[0] = 0.  What the kernel searches; no context needed. */
+int ptb_tone_thresholds(float out[256]);
 int ptb_read_counters(ptb_ctx *ctx, uint64_t out[PTB_CNT__N]);
 void *ptb_image_device_ptr(ptb_ctx *ctx);                            /* float4[W*H] in HBM, for an NCCL reduce by the caller */
 double ptb_last_render_ms(const ptb_ctx *ctx);                       /* device time of the last ptb_render (CUDA events) */

@@ -28,7 +28,7 @@ def val(name):
 
 secs = val("gpu__time_duration.sum")
 dram = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
-l2 = val("lts__t_bytes.sum")
+l2 = val("lts__t_sectors.sum") * 32.0  # L2 sectors are 32 bytes
 out = {
     "kernel": r[hdr.index("Kernel Name")], "source": f"profiles/{os.path.basename(rep).replace('.ncu-rep', '.txt')} ({cmd})",
     "launch_ms_under_ncu": secs * 1e3, "rays_in_launch": rays,

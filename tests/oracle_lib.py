@@ -102,6 +102,19 @@ class Oracle:
         self.L.pto_export_bvh(self.h, nodes.ctypes.data, idx.ctypes.data, roots.ctypes.data, sizes.ctypes.data, ctypes.byref(root))
         return nodes, idx, roots, int(root.value)
 
+    def export_grids(self):
+        """The oracle's (= the reference's) Subgrid hierarchy as ptb_upload_subgrid takes it:
+        (grids[80-byte records], lut_start, lut_end, indices)."""
+        self.L.pto_export_grids.argtypes = [ctypes.c_void_p] * 6
+        sizes = np.zeros(3, np.uint64)
+        self.L.pto_export_grids(self.h, None, None, None, None, sizes.ctypes.data)
+        grids = np.zeros(int(sizes[0]) * 80, np.uint8)
+        ls = np.zeros(int(sizes[1]), np.uint32)
+        le = np.zeros(int(sizes[1]), np.uint32)
+        idx = np.zeros(int(sizes[2]), np.uint32)
+        self.L.pto_export_grids(self.h, grids.ctypes.data, ls.ctypes.data, le.ctypes.data, idx.ctypes.data, sizes.ctypes.data)
+        return grids, ls, le, idx
+
     def trace_rays(self, od, threads=0):
         od = np.ascontiguousarray(od, np.float32).reshape(-1, 6)
         n = od.shape[0]

@@ -1,12 +1,13 @@
 """The reference's `--testing` protocol, headless (testing_protocol.py; main.cpp:99-141, window.cpp:540-546): the five stdout
-lines per structure in the form showcase/test.py parses, the PNG names, and — with the reference's own tree uploaded —
-the BVH counters of the CPU tracer."""
+lines per structure in the form showcase/test.py parses, the PNG names, and — with the reference's own tree AND its own grids
+uploaded — the counters of the CPU tracer in both blocks, and the PNGs byte for byte what the reference's window would show."""
 import os
 import re
 
 import numpy as np
 import pytest
 
+from conftest import apply_display
 from oracle_lib import MODE_BVH, MODE_TWO_PLANE, Oracle
 
 PATTERN = re.compile(r'(\w+ \w+): (\d{2}:\d{2}:\d{2}|\d+)')  # showcase/test.py:13
@@ -27,13 +28,15 @@ def test_png_round_trip_and_names(tmp_path):
 
 
 @pytest.mark.gpu
-def test_protocol_output_counters_and_files(ptb, cornel_ptbs, tmp_path):
+def test_protocol_output_counters_and_files(ptb, cornel_ptbs, tmp_path, tonemap_checker):
     W, H, S = 160, 90, 3
     o = Oracle(cornel_ptbs)
     o.build(grid=True, gs=10, os_=5, m=40)
     nodes, idx, roots, root = o.export_bvh()
+    grids, lut_s, lut_e, gidx = o.export_grids()
     o.configure(W, H, MODE_TWO_PLANE, nee=0, max_depth=0)
-    grid_img, _, _, _ = o.render(S)
+    grid_img, _, _, gst = o.render(S)
+    ga_cnt, gt_cnt = o.primary_counts()
     o.configure(W, H, MODE_BVH, nee=0, max_depth=0)
     bvh_img, _, _, st = o.render(S)
     a_cnt, t_cnt = o.primary_counts()
@@ -42,7 +45,8 @@ def test_protocol_output_counters_and_files(ptb, cornel_ptbs, tmp_path):
     pt.load_ptbs(cornel_ptbs)
     lines = []
     recs = ptb.testing_protocol.run(pt, samples=S, gs=10, os_=5, m=40, width=W, height=H, out_dir=str(tmp_path / "render"),
-                                    ref_tree=(nodes.view(ptb.REF_BVH_NODE), idx, roots, root), emit=lines.append)
+                                    ref_tree=(nodes.view(ptb.REF_BVH_NODE), idx, roots, root),
+                                    ref_grids=(grids.view(ptb.REF_GRID), lut_s, lut_e, gidx), emit=lines.append)
     assert lines[0] == "starting test" and len(lines) == 11
     parsed = [PATTERN.findall(l)[0] for l in lines[1:]]
     assert [k for k, _ in parsed] == KEYS + KEYS
@@ -51,27 +55,26 @@ def test_protocol_output_counters_and_files(ptb, cornel_ptbs, tmp_path):
     # BVH pass over the reference's tree: the CPU tracer's numbers (tests/test_oracle_pins.py pins the oracle's to ptref's)
     assert (bvh["tri_tests"], bvh["as_tests"]) == (st["tri_tests"], st["as_tests"])
     assert int(parsed[3][1]) == st["tri_tests"] + st["as_tests"]
-    assert int(parsed[4][1]) == pt.structure_bytes(MODE_BVH) and int(parsed[9][1]) == pt.structure_bytes(MODE_TWO_PLANE)
+    # Subgrids pass over the reference's grids: the other half of the protocol's numbers, equally the CPU tracer's
+    assert (grid["tri_tests"], grid["as_tests"]) == (gst["tri_tests"], gst["as_tests"])
+    assert int(parsed[6][1]) == gst["tri_tests"] and int(parsed[7][1]) == gst["as_tests"] and int(parsed[8][1]) == gst["tri_tests"] + gst["as_tests"]
+    # getMemory2Plane of those grids: 288-byte Grid objects + the three u32 vectors (lightFieldGrid.cpp:60-68)
+    assert int(parsed[9][1]) == len(grids) // 80 * 288 + 4 * (2 * len(lut_s) + len(gidx))
+    assert int(parsed[4][1]) == pt.structure_bytes(MODE_BVH)
     names = [os.path.basename(f) for r in recs for f in r["files"]]
     assert names == ["render_BVH.png", "render_heatmap_as_BVH.png", "render_heatmap_tris_BVH.png", "render_Subgrids.png",
                      "render_heatmap_as_Subgrids.png", "render_heatmap_tris_Subgrids.png"]
     tp = ptb.testing_protocol
     imgs = [tp.read_png(f) for r in recs for f in r["files"]]
     assert all(i.shape == (H, W, 4) and (i[..., 3] == 255).all() for i in imgs)
-    # the renders are the CPU tracer's frames through window.cpp:511-521 (c/(1+c), gamma, clamp, *255).  The two structures'
-    # frames differ from each other in the reference as well (1524 of these pixels: the path streams diverge once a ray
-    # leaves the grid's planes differently), so each is compared with its own oracle frame; a few bytes may flip where
-    # powf rounds differently on the two sides
-    def display(img):
-        v = img[..., :3].astype(np.float32)
-        v = v / (np.float32(1) + v)
-        v = np.power(v, np.float32(0.4545))
-        return (np.minimum(v, np.float32(1)) * np.float32(255)).astype(np.uint8).reshape(H, W, 3)
+    # the renders are the CPU tracer's frames through the display transform (window.cpp:507-531), byte for byte: the checker is
+    # the reference's expression compiled with its flags (tests/native/tonemap_check.cpp)
     for png, ref in ((imgs[0], bvh_img), (imgs[3], grid_img)):
-        assert int((png[..., :3] != display(ref)).any(axis=-1).sum()) <= W * H // 100
+        want = apply_display(tonemap_checker, ref, 1, str(tmp_path))
+        assert int((png != want).sum()) == 0
     # BVH heat maps are the reference's: grey = count / 10 below the scale, red above (tracer.cpp:136-142), then
     # the display transform without tone mapping (window.cpp:507-531)
-    for img, cnt in ((imgs[1], a_cnt), (imgs[2], t_cnt)):
+    for img, cnt in ((imgs[1], a_cnt), (imgs[2], t_cnt), (imgs[4], ga_cnt), (imgs[5], gt_cnt)):
         over = (cnt.reshape(H, W) > 10)
         assert (img[over][:, 0] == 255).all() and (img[over][:, 1:3] == 0).all()
         assert (img[~over][:, 0] == img[~over][:, 1]).all() and (img[~over][:, 1] == img[~over][:, 2]).all()
