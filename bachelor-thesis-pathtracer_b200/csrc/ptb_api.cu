@@ -131,6 +131,8 @@ struct ptb_ctx {
     SceneDev S{};
     AttrDev A{};
     float4 *dTri = nullptr, *dNrm = nullptr, *dNodes = nullptr;
+    float4 *dNodes4 = nullptr; // the 4-wide collapse of dNodes (k_collapse4), 128 B per BVH2 node; null unless PTB_WIDE
+    int useWide = 0;           // PTB_WIDE: mode BVH renders walk the 4-wide collapse
     uint32_t *dTriOfId = nullptr, *dIdOfTri = nullptr;
     float *dVtx = nullptr;
     MatDev *dMats = nullptr;
@@ -316,6 +318,7 @@ extern "C" int ptb_create(int device, ptb_ctx **out) {
     if (const char *e = getenv("PTB_MEGA_CTAS")) c->megaCtas = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_LEAF_MAX")) c->leafMax = std::max(1, std::min(16, atoi(e)));
     if (const char *e = getenv("PTB_MEGA_CHUNK")) c->megaChunk = std::max(0, atoi(e));
+    if (const char *e = getenv("PTB_WIDE")) c->useWide = atoi(e) != 0;
     if (const char *e = getenv("PTB_LOGIC_KEEP")) c->logicKeep = std::max(1, std::min(64, atoi(e)));
     if (const char *e = getenv("PTB_WAVES")) c->maxWaves = std::max(1, std::min(16, atoi(e)));
     cudaMalloc(&c->dRings, (size_t)c->maxWaves * 3 * kRing * sizeof(uint32_t));
@@ -365,7 +368,8 @@ extern "C" void ptb_destroy(ptb_ctx *c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_frame(c);
-    devFree(c->dTri); devFree(c->dNrm); devFree(c->dNodes); devFree(c->dTriOfId); devFree(c->dIdOfTri); devFree(c->dVtx);
+    devFree(c->dNodes4);
+    devFree(c->dTri); devFree(c->dNrm); devFree(c->dNodes); devFree(c->dTriOfId); devFree(c->dIdOfTri); devFree(c->dVtx); devFree(c->dNodes4);
     devFree(c->dMats); devFree(c->dLights);
     devFree(c->dGridHdr); devFree(c->dGridLut); devFree(c->dGridIdx);
     devFree(c->dBeam); devFree(c->dBeamIdx);
@@ -692,6 +696,20 @@ extern "C" int ptb_convert_scene_file(const char *scene_file, const char *base_d
 // =============================================================================================
 // structures
 // =============================================================================================
+// the 4-wide collapse of the tree in dNodes (BvhWalk4): one thread per BVH2 node, for host- and GPU-built trees alike.  Not
+// built (mode BVH keeps walking the BVH2) when PTB_WIDE is off or the tree is deeper than the wide walk's stack allows.
+static int build_wide_nodes(ptb_ctx *c, int depth) {
+    devFree(c->dNodes4);
+    c->S.nodes4 = nullptr;
+    if (!c->useWide || c->bvhNodes == 0 || depth > PTB_WIDE_MAX_DEPTH) return PTB_OK;
+    CK(cudaMalloc(&c->dNodes4, (size_t)c->bvhNodes * 8 * sizeof(float4)));
+    k_collapse4<<<(int)std::min<uint64_t>(65535, (c->bvhNodes + 255) / 256), 256, 0, c->stream>>>(c->dNodes, c->dNodes4, (uint32_t)c->bvhNodes);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->stream));
+    c->S.nodes4 = c->dNodes4;
+    return PTB_OK;
+}
+
 static int ptb_build_bvh_impl(ptb_ctx *c) {
     GUARD(c);
     const uint64_t n = c->mat.size();
@@ -749,6 +767,7 @@ static int ptb_build_bvh_impl(ptb_ctx *c) {
     c->bvhOnGpu = false;
     c->bvhNodes = c->bvh.nodes.size();
     c->gridBuilt = c->beamBuilt = false;
+    if (int r = build_wide_nodes(c, c->bvh.max_depth)) return r;
     return upload_uv(c);
 }
 
@@ -806,6 +825,7 @@ static int ptb_build_bvh_gpu_impl(ptb_ctx *c) {
     c->bvhBuilt = c->bvhOnGpu = true;
     c->bvhNodes = R.n_nodes;
     c->lastBuildMs = c->lastBuildDeviceMs = R.ms;
+    if (int r = build_wide_nodes(c, c->bvh.max_depth)) return r;
     return upload_uv(c);
 }
 
@@ -1203,7 +1223,7 @@ int render_mega(ptb_ctx *c, int add) {
     c->targetSamples += add;
     const ParamsDev P = make_params(c);
     // no more paths in flight than owned pixels: a pixel's samples are serial, so pixels bound the parallelism
-    const bool pool = MODE != 4 && c->useMega == 2, duo = MODE != 4 && c->useMega == 3; // the reference tree runs in k_mega only
+    const bool pool = MODE < 4 && c->useMega == 2, duo = MODE < 4 && c->useMega == 3; // the reference tree and the wide tree run in k_mega only
     const uint64_t perCta = pool ? 4ull * PTB_POOL_NP : (duo ? 2ull * kThreads : (uint64_t)kThreads); // paths a CTA keeps in flight
     const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * (pool ? c->poolCtas : (duo ? c->duoCtas : c->megaCtas)),
                                                                    ((uint64_t)c->nSlots + perCta - 1) / perCta));
@@ -1219,7 +1239,9 @@ int render_mega(ptb_ctx *c, int add) {
     chunk = std::min<uint32_t>(chunk, (uint32_t)add);
     const uint32_t nChunks = ((uint32_t)add + chunk - 1) / chunk;
     const bool chunked = c->uniformSamples && (uint64_t)c->nSlots * (uint64_t)nChunks < (1ull << 32);
-    M.chunk_samples = chunked ? chunk : (uint32_t)add;
+    // one item per pixel (non-uniform state): the item runs the pixel up to the target however far behind it is, like trace()
+    // does until samples[x][y] reaches MAX_SAMPLE_COUNT (tracer.cpp:113-160)
+    M.chunk_samples = chunked ? chunk : 0x7fffffffu;
     M.n_items = chunked ? c->nSlots * nChunks : c->nSlots;
     M.first_sample = first;
     M.check_ready = chunked ? 1 : 0;
@@ -1234,7 +1256,7 @@ int render_mega(ptb_ctx *c, int add) {
     CK(cudaEventRecord(c->evStart, c->stream));
     bool launched = false;
 #ifdef PTB_WITH_ALT_SCHEDULERS
-    if constexpr (MODE != 4) {
+    if constexpr (MODE < 4) {
     if (pool) {
         launched = true;
         const bool nee = P.nee && P.n_lights > 0;
@@ -1268,9 +1290,9 @@ int render_mega(ptb_ctx *c, int add) {
         if (tex) k_mega<MODE, COUNT, NEEV, EARLYV, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);     \
         else k_mega<MODE, COUNT, NEEV, EARLYV, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);        \
     } while (0)
-        if (MODE == 1 && M.leaf_keep > 0) { // deep tree: straggler exit in the node loop
-            if (nee) PTB_MEGA_LAUNCH(true, MODE == 1);
-            else PTB_MEGA_LAUNCH(false, MODE == 1);
+        if ((MODE == 1 || MODE == 5) && M.leaf_keep > 0) { // deep tree: straggler exit in the node loop
+            if (nee) PTB_MEGA_LAUNCH(true, (MODE == 1 || MODE == 5));
+            else PTB_MEGA_LAUNCH(false, (MODE == 1 || MODE == 5));
         } else if (nee) PTB_MEGA_LAUNCH(true, false);
         else PTB_MEGA_LAUNCH(false, false);
 #undef PTB_MEGA_LAUNCH
@@ -1314,7 +1336,7 @@ int render_dispatch(ptb_ctx *c, int add) {
     }
     if (c->useMega) switch (c->prm.mode) {
         case PTB_MODE_ALL: return render_mega<0, COUNT>(c, add);
-        case PTB_MODE_BVH: return render_mega<1, COUNT>(c, add);
+        case PTB_MODE_BVH: return (c->S.nodes4 && c->useMega == 1) ? render_mega<5, COUNT>(c, add) : render_mega<1, COUNT>(c, add);
         case PTB_MODE_TWO_PLANE: return render_mega<2, COUNT>(c, add);
         default: return render_mega<3, COUNT>(c, add);
         }

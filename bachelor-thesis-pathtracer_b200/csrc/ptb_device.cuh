@@ -81,6 +81,7 @@ struct Hit {
 struct SceneDev {
     const float4 *__restrict__ tri;     // 3 float4 per triangle: (v0, id), (e1, -), (e2, -); leaf order
     const float4 *__restrict__ nodes;   // BVH2, 4 float4 (64 B) per inner node
+    const float4 *__restrict__ nodes4;  // the same tree collapsed to 4-wide nodes (k_collapse4), 8 float4 (128 B) per BVH2 node index; null = not built
     int bvh_root;                       // node ref (>=0 inner, <0 leaf)
     uint32_t n_tris;
     // Subgrid ("2Plane")
@@ -351,6 +352,160 @@ struct BvhWalk {
     }
 };
 
+// ---- 4-wide BVH ------------------------------------------------------------------------------------------------------
+// The BVH2 collapsed by k_collapse4: node i of the wide tree = BVH2 node i with its (up to four) grandchildren as children —
+// an inner child is replaced by its two children, a leaf child stays.  Same node indices as the BVH2 (only the nodes at even
+// depth are ever reached), so the collapse is one independent thread per node and works for host- and GPU-built trees alike.
+// Layout, 8 x float4 = 128 B (four 32-byte sectors, one cache line): lo.x[4] lo.y[4] lo.z[4] hi.x[4] hi.y[4] hi.z[4] ref[4] pad.
+// Empty slots hold PTB_REF_DONE.  Why: ncu on the BVH2 kernel shows the node loop waiting on its dependent node fetch
+// (stall_long_sb 47 % on the Lucy stand-in, L1 hit 68 %) and ~30 instructions of push / pop / branch per 59 of slab arithmetic;
+// a 4-wide step halves the dependent fetches per ray and amortises the control over four boxes.  Closest hits do not depend on
+// the visit order (ties go to the larger reference id), so frames are bit-identical to the BVH2 walk's.
+// Up to three pushes per visited node: the BVH2 may be at most PTB_WIDE_MAX_DEPTH deep for PTB_STACK entries.
+#define PTB_WIDE_MAX_DEPTH 40 /* 3 * ceil(40 / 2) = 60 < PTB_STACK */
+struct BvhWalk4 {
+    f3 o, d, inv;
+    Hit h;
+    int ref;
+    int sp;
+    bool fast;
+
+    __device__ __forceinline__ void begin(const SceneDev &S, f3 o_, f3 d_, const Hit &h0) {
+        o = o_;
+        d = d_;
+        inv = rcp3(d_);
+        fast = finite3(inv);
+        h = h0;
+        sp = 0;
+        ref = S.n_tris ? S.bvh_root : PTB_REF_DONE;
+    }
+    template <class ST>
+    __device__ __forceinline__ void pop(const ST &stack) {
+        for (;;) {
+            if (sp == 0) {
+                ref = PTB_REF_DONE;
+                return;
+            }
+            sp--;
+            const int2 e = stack.get(sp);
+            if (!(__int_as_float(e.y) > h.t)) {
+                ref = e.x;
+                return;
+            }
+        }
+    }
+    template <bool COUNT, class ST>
+    __device__ __forceinline__ void node_step(const SceneDev &S, const ST &stack, uint32_t &nBox) {
+        const float4 *n = S.nodes4 + 8 * (size_t)ref;
+        const float4 lx = __ldg(n), ly = __ldg(n + 1), lz = __ldg(n + 2), hx = __ldg(n + 3), hy = __ldg(n + 4), hz = __ldg(n + 5);
+        const int4 c = __ldg(reinterpret_cast<const int4 *>(n + 6));
+        if (COUNT) nBox += 4;
+        float k0, k1, k2, k3; // entry distance, +inf where the child is missed or absent
+        bool b0, b1, b2, b3;
+        if (fast) {
+            b0 = slab_fast(mk3(lx.x, ly.x, lz.x), mk3(hx.x, hy.x, hz.x), o, inv, h.t, k0);
+            b1 = slab_fast(mk3(lx.y, ly.y, lz.y), mk3(hx.y, hy.y, hz.y), o, inv, h.t, k1);
+            b2 = slab_fast(mk3(lx.z, ly.z, lz.z), mk3(hx.z, hy.z, hz.z), o, inv, h.t, k2);
+            b3 = slab_fast(mk3(lx.w, ly.w, lz.w), mk3(hx.w, hy.w, hz.w), o, inv, h.t, k3);
+        } else {
+            b0 = slab(mk3(lx.x, ly.x, lz.x), mk3(hx.x, hy.x, hz.x), o, inv, h.t, k0);
+            b1 = slab(mk3(lx.y, ly.y, lz.y), mk3(hx.y, hy.y, hz.y), o, inv, h.t, k1);
+            b2 = slab(mk3(lx.z, ly.z, lz.z), mk3(hx.z, hy.z, hz.z), o, inv, h.t, k2);
+            b3 = slab(mk3(lx.w, ly.w, lz.w), mk3(hx.w, hy.w, hz.w), o, inv, h.t, k3);
+        }
+        // slots 0 and 1 always exist (an inner BVH2 node has two children); 2 and 3 may be empty
+        k0 = b0 ? k0 : PTB_INF;
+        k1 = b1 ? k1 : PTB_INF;
+        k2 = (b2 && c.z != PTB_REF_DONE) ? k2 : PTB_INF;
+        k3 = (b3 && c.w != PTB_REF_DONE) ? k3 : PTB_INF;
+        int r0 = c.x, r1 = c.y, r2 = c.z, r3 = c.w;
+        // ascending by entry distance, misses (+inf) last: 5-comparator network (0,1)(2,3)(0,2)(1,3)(1,2)
+#define PTB_CE(ka, ra, kb, rb)              \
+    do {                                    \
+        const bool sw_ = kb < ka;           \
+        const float tk_ = sw_ ? kb : ka;    \
+        const int tr_ = sw_ ? rb : ra;      \
+        kb = sw_ ? ka : kb;                 \
+        rb = sw_ ? ra : rb;                 \
+        ka = tk_;                           \
+        ra = tr_;                           \
+    } while (0)
+        PTB_CE(k0, r0, k1, r1);
+        PTB_CE(k2, r2, k3, r3);
+        PTB_CE(k0, r0, k2, r2);
+        PTB_CE(k1, r1, k3, r3);
+        PTB_CE(k1, r1, k2, r2);
+#undef PTB_CE
+        if (k0 == PTB_INF) { // nothing hit
+            pop(stack);
+            return;
+        }
+        // the nearest goes on, the others wait farthest-first so the nearer of them pops first
+        if (k3 != PTB_INF) stack.put(sp++, make_int2(r3, __float_as_int(k3)));
+        if (k2 != PTB_INF) stack.put(sp++, make_int2(r2, __float_as_int(k2)));
+        if (k1 != PTB_INF) stack.put(sp++, make_int2(r1, __float_as_int(k1)));
+        ref = r0;
+    }
+    template <bool COUNT, class ST>
+    __device__ __forceinline__ void leaf(const SceneDev &S, const ST &stack, uint32_t &nTri) {
+        int first, count;
+        leaf_decode(ref, first, count);
+        for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
+        pop(stack);
+    }
+    template <bool COUNT, bool EARLY = false, class ST>
+    __device__ __forceinline__ bool round(const SceneDev &S, const ST &stack, uint32_t &nTri, uint32_t &nBox, int minActive = 0) {
+        while (ref >= 0) {
+            node_step<COUNT>(S, stack, nBox);
+            if (EARLY && __popc(__activemask()) < minActive) break;
+        }
+        if ((!EARLY || ref < 0) && ref != PTB_REF_DONE) leaf<COUNT>(S, stack, nTri);
+        return ref != PTB_REF_DONE;
+    }
+};
+
+// one thread per BVH2 node: its wide node (see BvhWalk4).  n2 = BVH2 inner nodes.
+__global__ void k_collapse4(const float4 *__restrict__ nodes, float4 *__restrict__ nodes4, uint32_t n2) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += gridDim.x * blockDim.x) {
+        const float4 *n = nodes + 4 * (size_t)i;
+        const float4 q0 = n[0], q1 = n[1], q2 = n[2];
+        const int4 q3 = *reinterpret_cast<const int4 *>(n + 3);
+        float lo[4][3], hi[4][3];
+        int ref[4] = {PTB_REF_DONE, PTB_REF_DONE, PTB_REF_DONE, PTB_REF_DONE};
+        int k = 0;
+        const float cb[2][6] = {{q0.x, q0.y, q0.z, q0.w, q1.x, q1.y}, {q1.z, q1.w, q2.x, q2.y, q2.z, q2.w}};
+        const int cr[2] = {q3.x, q3.y};
+        for (int s = 0; s < 2; ++s) {
+            if (cr[s] >= 0) { // inner child: its two children take its place
+                const float4 *m = nodes + 4 * (size_t)cr[s];
+                const float4 m0 = m[0], m1 = m[1], m2 = m[2];
+                const int4 m3 = *reinterpret_cast<const int4 *>(m + 3);
+                lo[k][0] = m0.x; lo[k][1] = m0.y; lo[k][2] = m0.z; hi[k][0] = m0.w; hi[k][1] = m1.x; hi[k][2] = m1.y;
+                ref[k++] = m3.x;
+                lo[k][0] = m1.z; lo[k][1] = m1.w; lo[k][2] = m2.x; hi[k][0] = m2.y; hi[k][1] = m2.z; hi[k][2] = m2.w;
+                ref[k++] = m3.y;
+            } else {
+                for (int a = 0; a < 3; ++a) {
+                    lo[k][a] = cb[s][a];
+                    hi[k][a] = cb[s][3 + a];
+                }
+                ref[k++] = cr[s];
+            }
+        }
+        for (; k < 4; ++k)
+            for (int a = 0; a < 3; ++a) lo[k][a] = hi[k][a] = 0.0f;
+        float4 *o = nodes4 + 8 * (size_t)i;
+        o[0] = make_float4(lo[0][0], lo[1][0], lo[2][0], lo[3][0]);
+        o[1] = make_float4(lo[0][1], lo[1][1], lo[2][1], lo[3][1]);
+        o[2] = make_float4(lo[0][2], lo[1][2], lo[2][2], lo[3][2]);
+        o[3] = make_float4(hi[0][0], hi[1][0], hi[2][0], hi[3][0]);
+        o[4] = make_float4(hi[0][1], hi[1][1], hi[2][1], hi[3][1]);
+        o[5] = make_float4(hi[0][2], hi[1][2], hi[2][2], hi[3][2]);
+        *reinterpret_cast<int4 *>(o + 6) = make_int4(ref[0], ref[1], ref[2], ref[3]);
+        o[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+}
+
 template <bool COUNT>
 __device__ __forceinline__ void bvh_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nBox) {
     BvhWalk w;
@@ -588,9 +743,22 @@ __device__ __forceinline__ void subbeam_closest(const SceneDev &S, f3 o, f3 d, H
     }
 }
 
+template <bool COUNT>
+__device__ __forceinline__ void bvh4_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nBox) {
+    BvhWalk4 w;
+    int2 stackMem[PTB_STACK];
+    const LocalStack stack{stackMem};
+    w.begin(S, o, d, h);
+    while (w.round<COUNT>(S, stack, nTri, nBox)) {
+    }
+    h = w.h;
+}
+
+// MODE: ptb_mode 0..3; 4 = mode BVH over the reference's own tree; 5 = mode BVH over the 4-wide collapse of this library's tree
 template <int MODE, bool COUNT>
 __device__ __forceinline__ void closest_hit(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
-    if (MODE == 1) bvh_closest<COUNT>(S, o, d, h, nTri, nAS);
+    if (MODE == 5) bvh4_closest<COUNT>(S, o, d, h, nTri, nAS);
+    else if (MODE == 1) bvh_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 2 && PTB_GRID_SLICES) subgrid_closest_slices<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 2) subgrid_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 3) subbeam_closest<COUNT>(S, o, d, h, nTri, nAS);

@@ -33,6 +33,15 @@
 
 namespace ptb {
 
+template <int MODE>
+struct WalkOf {
+    typedef BvhWalk type;
+};
+template <>
+struct WalkOf<5> {
+    typedef BvhWalk4 type; // mode BVH over the 4-wide collapse (ptb_device.cuh)
+};
+
 enum : int { LANE_IDLE = 0, LANE_WAIT = 1, LANE_LOGIC = 2, LANE_SHADOW = 3, LANE_MAIN = 4, LANE_NEXT = 5 /* next sample of the same pixel */ };
 
 struct ShadowRec { // what nextEventEstimation still needs once the shadow ray is back (shader.cpp:102-112)
@@ -73,12 +82,12 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
     float shadowT = 0.0f;
     int shadowTri = -1;
     float shadowU = 0.0f, shadowV = 0.0f; // TEX only: where the shadow ray ended (a textured light is sampled there)
-    BvhWalk w;
+    typename WalkOf<MODE>::type w;
 #if PTB_SSTACK > 0
     // the first PTB_SSTACK stack entries of every lane live in shared memory (BVH mode; the other modes keep their own stacks)
-    __shared__ int2 sstack[MODE == 1 ? PTB_SSTACK * PTB_CTA : 1];
+    __shared__ int2 sstack[(MODE == 1 || MODE == 5) ? PTB_SSTACK * PTB_CTA : 1];
     int2 stackMem[PTB_STACK - PTB_SSTACK];
-    const HybridStack<PTB_SSTACK> stack{sstack + (MODE == 1 ? threadIdx.x : 0), stackMem};
+    const HybridStack<PTB_SSTACK> stack{sstack + ((MODE == 1 || MODE == 5) ? threadIdx.x : 0), stackMem};
 #else
     int2 stackMem[PTB_STACK];
     const LocalStack stack{stackMem};
@@ -308,9 +317,9 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
             for (;;) {
                 if (phase == LANE_SHADOW || phase == LANE_MAIN) {
                     bool cont;
-                    if (MODE == 1) {
-                        if (COUNT && phase == LANE_MAIN) cont = w.round<true, EARLY>(S, stack, nTri, nAS, minActive);
-                        else cont = w.round<false, EARLY>(S, stack, nTri, nAS, minActive);
+                    if (MODE == 1 || MODE == 5) {
+                        if (COUNT && phase == LANE_MAIN) cont = w.template round<true, EARLY>(S, stack, nTri, nAS, minActive);
+                        else cont = w.template round<false, EARLY>(S, stack, nTri, nAS, minActive);
                     } else {
                         if (COUNT && phase == LANE_MAIN) closest_hit<MODE, true>(S, w.o, w.d, w.h, nTri, nAS);
                         else {

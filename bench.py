@@ -80,7 +80,7 @@ def workload_config(args, wl, world, shard, triangles):
 def choose_shard(args, wl, world):
     shard = args.shard
     if shard == "auto":
-        shard = "tiles" if world == 1 or (wl["W"] * wl["H"]) // world >= 400_000 else "samples"
+        shard = "tiles" if world == 1 or (wl["W"] * wl["H"]) // world >= 600_000 else "samples"
     return shard if world > 1 else "tiles"
 
 
