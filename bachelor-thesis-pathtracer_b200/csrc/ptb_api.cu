@@ -1290,9 +1290,9 @@ int render_mega(ptb_ctx *c, int add) {
         if (tex) k_mega<MODE, COUNT, NEEV, EARLYV, true><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);     \
         else k_mega<MODE, COUNT, NEEV, EARLYV, false><<<grid, kThreads, 0, c->stream>>>(P, c->S, c->A, c->F, M);        \
     } while (0)
-        if ((MODE == 1 || MODE == 5) && M.leaf_keep > 0) { // deep tree: straggler exit in the node loop
-            if (nee) PTB_MEGA_LAUNCH(true, (MODE == 1 || MODE == 5));
-            else PTB_MEGA_LAUNCH(false, (MODE == 1 || MODE == 5));
+        if (PTB_MODE_HAS_ROUNDS(MODE) && M.leaf_keep > 0) { // deep structure: straggler exit in the descend loop
+            if (nee) PTB_MEGA_LAUNCH(true, PTB_MODE_HAS_ROUNDS(MODE));
+            else PTB_MEGA_LAUNCH(false, PTB_MODE_HAS_ROUNDS(MODE));
         } else if (nee) PTB_MEGA_LAUNCH(true, false);
         else PTB_MEGA_LAUNCH(false, false);
 #undef PTB_MEGA_LAUNCH

@@ -689,6 +689,98 @@ __device__ __forceinline__ void subgrid_closest_slices(const SceneDev &S, f3 o, 
     }
 }
 
+// The same walk as a resumable state machine for the path kernel (k_mega<TWO_PLANE>): "while-while" like BvhWalk::round.
+//   phase 1  lanes without pending triangles visit grids (header + slab + LUT cell) until one lands in a triangle cell or
+//            runs out of grids;
+//   phase 2  lanes holding a triangle cell test up to PTB_GRID_TRIS_PER_ROUND of its triangles together.
+// A cell's triangles are all tested BEFORE the next grid is popped (the shrunken tmax culls it), exactly the order of
+// intersectGrid, so hits, AS / triangle test counts and heat maps are unchanged.  Why: ncu on the one-shot walk inside k_mega
+// shows 6.4 of 32 lanes per issued instruction (profiles/r2_ncu_mega_lucy_subgrid.txt) — every lane runs its own mixture of
+// header fetches and triangle loops (cells hold up to m = 50 triangles) to completion while the warp waits for the longest.
+#ifndef PTB_GRID_TRIS_PER_ROUND
+#define PTB_GRID_TRIS_PER_ROUND 4
+#endif
+struct GridWalk {
+    f3 o, d, inv;
+    Hit h;
+    int ref;          // grid to visit next, or PTB_REF_DONE (same convention as BvhWalk: the kernel only compares with DONE)
+    int sp;           // slices on the stack
+    uint32_t ti, te;  // pending triangles of the current cell: grid_idx[ti .. te)
+    int axis;
+
+    __device__ __forceinline__ void begin(const SceneDev &S, f3 o_, f3 d_, const Hit &h0) {
+        o = o_;
+        d = d_;
+        inv = rcp3(d_);
+        h = h0;
+        sp = 0;
+        ti = te = 0u;
+        axis = dominant_axis(d_);
+        ref = axis; // grids 0..2 are the roots per dominant axis
+    }
+    template <class ST>
+    __device__ __forceinline__ void next(const SceneDev &S, const ST &stack) {
+        if (sp == 0) {
+            ref = PTB_REF_DONE;
+            return;
+        }
+        int2 e = stack.get(sp - 1);
+        const bool fromEnd = comp(d, axis) < 0.0f; // ascending pushes pop from the end of the slice (lightFieldGrid.cpp:127-145)
+        ref = (int)__ldg(&S.grid_idx[fromEnd ? (uint32_t)--e.y : (uint32_t)e.x++]);
+        if (e.x == e.y) sp--;
+        else stack.put(sp - 1, e);
+    }
+    template <bool COUNT, class ST>
+    __device__ __forceinline__ void visit(const SceneDev &S, const ST &stack, uint32_t &nAS) {
+        const float4 *hd = S.grid_hdr + 4 * (size_t)ref;
+        const float4 h0 = __ldg(hd), h1 = __ldg(hd + 1);
+        if (COUNT) nAS++;
+        float tn;
+        if (!slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)) return;
+        if (COUNT) nAS++;
+        const float4 h2 = __ldg(hd + 2), h3 = __ldg(hd + 3);
+        const int right = axis == 0 ? 1 : 0, up = axis == 2 ? 1 : 2; // lightFieldGrid.cpp:26-35
+        const float oa = comp(o, axis), ia = comp(inv, axis);
+        const float orr = comp(o, right), dr = comp(d, right), ou = comp(o, up), du = comp(d, up);
+        const f3 gmin = mk3(h2.x, h2.y, h2.z), idl = mk3(h3.x, h3.y, h3.z);
+        const float gmaxA = comp(mk3(h1.x, h1.y, h1.z), axis) + 0.1f;
+        const float d1 = (comp(gmin, axis) - oa) * ia;
+        const float d2 = (gmaxA - oa) * ia;
+        const float inR = ((orr + d1 * dr) - comp(gmin, right)) * comp(idl, right);
+        const float inU = ((ou + d1 * du) - comp(gmin, up)) * comp(idl, up);
+        const float outR = ((orr + d2 * dr) - comp(gmin, right)) * comp(idl, right);
+        const float outU = ((ou + d2 * du) - comp(gmin, up)) * comp(idl, up);
+        const uint32_t sz = __float_as_uint(h0.w) & 0x7fffffffu;
+        const bool hasTris = (__float_as_uint(h0.w) >> 31) != 0u;
+        const float fs = (float)sz;
+        const int iu = (int)(inR * fs), iv = (int)(inU * fs), is = (int)(outR * fs), it = (int)(outU * fs);
+        if ((unsigned)iu >= sz || (unsigned)iv >= sz || (unsigned)is >= sz || (unsigned)it >= sz) return; // outside the planes: no cell (A.12)
+        const uint32_t cell = ((((uint32_t)iu * sz + (uint32_t)iv) * sz + (uint32_t)is) * sz + (uint32_t)it);
+        const uint2 se = __ldg(&S.grid_lut[(size_t)__float_as_uint(h1.w) + cell]);
+        if (se.x >= se.y) return;
+        if (hasTris) {
+            ti = se.x;
+            te = se.y;
+        } else if (sp < PTB_GDEPTH) {
+            stack.put(sp++, make_int2((int)se.x, (int)se.y));
+        }
+    }
+    template <bool COUNT, bool EARLY = false, class ST>
+    __device__ __forceinline__ bool round(const SceneDev &S, const ST &stack, uint32_t &nTri, uint32_t &nAS, int minActive = 0) {
+        while (ti == te && ref != PTB_REF_DONE) {
+            visit<COUNT>(S, stack, nAS);
+            if (ti == te) next(S, stack);
+            if (EARLY && __popc(__activemask()) < minActive) break;
+        }
+        if (ti != te) {
+            const uint32_t stop = min(te, ti + (uint32_t)PTB_GRID_TRIS_PER_ROUND);
+            for (; ti < stop; ++ti) intersect_tri<COUNT>(S.tri, (int)__ldg(&S.grid_idx[ti]), o, d, h, nTri);
+            if (ti == te) next(S, stack);
+        }
+        return ref != PTB_REF_DONE || ti != te;
+    }
+};
+
 // ---- Subbeam closest hit: stands in for intersectSubBeamGrid (SubBeams.cpp:73-170) ---------
 template <bool COUNT>
 __device__ __forceinline__ void subbeam_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {

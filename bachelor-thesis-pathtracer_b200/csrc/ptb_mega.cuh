@@ -37,6 +37,16 @@ template <int MODE>
 struct WalkOf {
     typedef BvhWalk type;
 };
+#ifndef PTB_GRID_ROUNDS
+#define PTB_GRID_ROUNDS 1 /* k_mega<TWO_PLANE> walks the Subgrids in while-while rounds (GridWalk); 0 = one-shot per lane */
+#endif
+#if PTB_GRID_ROUNDS
+template <>
+struct WalkOf<2> {
+    typedef GridWalk type;
+};
+#endif
+#define PTB_MODE_HAS_ROUNDS(M) ((M) == 1 || (M) == 5 || ((M) == 2 && PTB_GRID_ROUNDS))
 template <>
 struct WalkOf<5> {
     typedef BvhWalk4 type; // mode BVH over the 4-wide collapse (ptb_device.cuh)
@@ -317,7 +327,7 @@ __global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, S
             for (;;) {
                 if (phase == LANE_SHADOW || phase == LANE_MAIN) {
                     bool cont;
-                    if (MODE == 1 || MODE == 5) {
+                    if (PTB_MODE_HAS_ROUNDS(MODE)) {
                         if (COUNT && phase == LANE_MAIN) cont = w.template round<true, EARLY>(S, stack, nTri, nAS, minActive);
                         else cont = w.template round<false, EARLY>(S, stack, nTri, nAS, minActive);
                     } else {

@@ -40,6 +40,7 @@
 #include "types/texture.h"
 
 #include "ptb.h"
+#include "facade_internal.h"
 #include "tracer_facade.h"
 
 namespace {
@@ -60,6 +61,7 @@ unsigned gridGs = 10, gridOs = 5, gridM = 40, beamGs = 10, beamM = 40; // main.c
 bool gridBuilt = false, beamBuilt = false;
 int maxDepth = 0;
 bool useReferenceTree = false; // ptbFacadeUseReferenceTree
+bool structuresFronted = false; // structures_facade.cpp is linked (bvh.h / lightFieldGrid*.h forward to the GPU builders too)
 bool texturesUploaded = false;
 int renderedSamples = 0;
 std::vector<float> mirror; // host copy of the frame that tracerGetPixel serves (refreshed per batch)
@@ -177,7 +179,9 @@ bool uploadScene() {
     if (!all([&](ptb_ctx *c) { return ptb_build_bvh(c); }, "ptb_build_bvh")) return false; // constructBVH, scene.cpp:113-120
     gridBuilt = beamBuilt = false;
     uploadedTris = n;
-    if (useReferenceTree && n > 0) {
+    if (useReferenceTree && n > 0 && structuresFronted) {
+        fprintf(stderr, "ptb facade: the reference tree was asked for, but bvh.h is fronted by structures_facade.cpp (no reference tree in this process)\n");
+    } else if (useReferenceTree && n > 0) {
         if (!uploadReferenceTree() || !all([&](ptb_ctx *c) { return ptb_use_ref_bvh(c, 1); }, "ptb_use_ref_bvh")) return false;
     }
     return true;
@@ -281,6 +285,14 @@ void refreshMirror() {
     ptb_group_read_counters(grp, counters);
 }
 } // namespace
+
+// ---- shared with structures_facade.cpp (facade_internal.h) ----------------------------------------
+namespace ptbfacade {
+ptb_ctx *context() { return ensureContext() ? ctx : nullptr; }
+bool sceneOnDevice() { return ensureContext() && (uploadedTris == getTris().size() || uploadScene()); }
+bool structureOnDevice(int mode) { return sceneOnDevice() && ensureStructure(mode); }
+void structuresAreFronted() { structuresFronted = true; }
+} // namespace ptbfacade
 
 // ---- tracer.h ------------------------------------------------------------------------------------
 bool &getfinishedRendering() { return finishedRendering; }

@@ -461,6 +461,9 @@ static void cmdRender(const Opts &o, const char *out) {
     g_maxDepth = o.maxDepth;
 #ifdef PTB_FACADE
     ptbFacadeSetMaxDepth(o.maxDepth);
+#ifndef PTB_FACADE_STRUCTURES
+    // (with structures_facade.cpp linked, setGridSettings / setGridBeamsSettings in main() below ARE the facade's, the
+    // structures were built on the GPU by buildStructures, and the devices were chosen before that)
     ptbFacadeSetGridSettings(o.gs, o.os, o.m);
     ptbFacadeSetGridBeamsSettings(o.bgs, o.bm);
     ptbFacadeUseReferenceTree(o.refTree != 0);
@@ -469,6 +472,7 @@ static void cmdRender(const Opts &o, const char *out) {
         for (int i = 0; i < o.gpus; ++i) devs[i] = o.sameDevice ? 0 : i;
         ptbFacadeSetDevices(devs.data(), o.gpus);
     }
+#endif
 #endif
     setWindowSize(o.W, o.H);
     getMaxSampleCount() = o.spp;
@@ -647,6 +651,13 @@ int main(int argc, char **argv) {
                getObjects().size(), getMaterials()->size(), loadMs);
         return 0;
     }
+#ifdef PTB_FACADE_STRUCTURES
+    if (o.gpus > 1) { // before initScene's constructBVH creates the contexts
+        std::vector<int> devs(o.gpus);
+        for (int i = 0; i < o.gpus; ++i) devs[i] = o.sameDevice ? 0 : i;
+        ptbFacadeSetDevices(devs.data(), o.gpus);
+    }
+#endif
     buildStructures(o, cp, cf, cam.focus, cam.dof);
     fprintf(stderr, "ptref: load %.1f ms, bvh %.1f ms, grid %.1f ms, beams %.1f ms, tris %zu, lights %zu\n", loadMs, g_bvhMs,
             g_gridMs, g_beamMs, getTris().size(), getLights().size());

@@ -194,15 +194,26 @@ def have_facade():
     return os.path.isfile(PTFACADE) and os.access(PTFACADE, os.X_OK)
 
 
-def ptfacade_render(ptbs, W, H, mode, spp, max_depth=0, nee=0, extra=()):
-    """The reference's own objects with src/tracer.cpp replaced by host/tracer_facade.cpp: trace() on the GPU."""
+PTFACADE_GPU = os.path.join(ORACLE_DIR, "_ref", "ptfacade_gpu")
+
+
+def have_facade_gpu():
+    return os.path.isfile(PTFACADE_GPU) and os.access(PTFACADE_GPU, os.X_OK)
+
+
+def ptfacade_render(ptbs, W, H, mode, spp, max_depth=0, nee=0, extra=(), structures=False, want_build=False):
+    """The reference's own objects with src/tracer.cpp replaced by host/tracer_facade.cpp: trace() on the GPU.
+    structures=True: the flavour that also swaps bvh.cpp / lightFieldGrid.cpp / lightFieldGridSubBeams.cpp for
+    host/structures_facade.cpp (oracle/_ref/ptfacade_gpu): initScene's builds run on the GPU too."""
     with tempfile.TemporaryDirectory() as d:
         o = os.path.join(d, "img.bin")
-        out = subprocess.run([PTFACADE] + [str(a) for a in ["--ptbs", ptbs, "--mode", mode, "--width", W, "--height", H, "--spp", spp,
+        out = subprocess.run([PTFACADE_GPU if structures else PTFACADE] + [str(a) for a in ["--ptbs", ptbs, "--mode", mode, "--width", W, "--height", H, "--spp", spp,
                                                            "--max-depth", max_depth, "--nee", nee, *extra, "render", o]],
                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=1800)
         if out.returncode != 0:
             raise RuntimeError("ptfacade failed: " + out.stderr[-2000:])
         recs = [json.loads(l[len("PTREF_JSON "):]) for l in out.stdout.splitlines() if l.startswith("PTREF_JSON ")]
         img = np.fromfile(o, np.float32).reshape(H, W, 4)
+    if want_build:
+        return img, [r for r in recs if r["cmd"] == "render"][0], [r for r in recs if r["cmd"] == "build"][0]
     return img, [r for r in recs if r["cmd"] == "render"][0]
