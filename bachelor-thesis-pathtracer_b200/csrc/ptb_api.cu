@@ -77,7 +77,7 @@ struct ptb_ctx {
     void *dShScratch = nullptr; // NEE shadow records of the pool kernel (grid warps x NP)
     size_t shScratchN = 0;
     int megaCtas = PTB_MEGA_MINBLOCKS; // resident CTAs/SM of k_mega
-    int logicKeep = 26;
+    int logicKeep = -1; // PTB_LOGIC_KEEP: run a logic pass once this many lanes of a warp wait for it; -1 = by scene and mode (render_mega)
     int traceLeafFrac = 0; // PTB_TRACE_LEAF: the same switch for ptb_trace_rays (k_trace_bvh)
     int megaLeafFrac = -1; // PTB_MEGA_LEAF: k_mega leaves the node loop when fewer than walkers*this/32 lanes still descend; -1 = 16 for trees of >= 2^15 triangles, else off
     int leafMax = 3;    // PTB_LEAF_MAX: triangles per BVH leaf (<= 16)
@@ -1245,7 +1245,10 @@ int render_mega(ptb_ctx *c, int add) {
     M.n_items = chunked ? c->nSlots * nChunks : c->nSlots;
     M.first_sample = first;
     M.check_ready = chunked ? 1 : 0;
-    M.logic_keep = duo ? c->duoLogicKeep : c->logicKeep;
+    // profiles/r2_ab4_subgrid_knobs.txt: a small tree (Cornell) wants full shading passes (26 of 32 lanes); on deep structures a
+    // traversal round is long, so waiting lanes cost more than a thinner shading pass: 20 (BVH), 18 (Subgrids: +5 %)
+    const int autoKeep = c->mat.size() >= (1u << 15) ? (MODE == 2 ? 18 : 20) : 26;
+    M.logic_keep = duo ? c->duoLogicKeep : (c->logicKeep > 0 ? c->logicKeep : autoKeep);
     M.sample_keep = c->duoSampleKeep;
     M.walk_min = c->duoWalkMin;
     M.refill_min = c->duoRefillMin;

@@ -341,6 +341,34 @@ struct BvhWalk {
     // that already hold a leaf stop waiting for the last stragglers, which resume next round.  Pays on deep
     // trees (Lucy stand-in +17 %); on a 100-node tree the vote per step costs more than it saves
     // (profiles/r1_sweep_mega_leaf.txt), hence a compile-time switch.
+#ifndef PTB_SPECULATE
+#define PTB_SPECULATE 0
+#endif
+#if PTB_SPECULATE
+    // Speculative variant (Aila & Laine 2009, "postponed leaf"): a lane that reaches a leaf holds it back and keeps descending
+    // to a SECOND leaf before both are tested, so lanes stay in the node loop longer and the leaf phase has more work per
+    // lane.  The held leaf's hit cannot cull the nodes visited meanwhile (a few more box tests); closest hits are unchanged.
+    template <bool COUNT, bool EARLY = false, class ST>
+    __device__ __forceinline__ bool round(const SceneDev &S, const ST &stack, uint32_t &nTri, uint32_t &nBox, int minActive = 0) {
+        int held = 0; // leaf references are negative: 0 = none
+        for (;;) {
+            while (ref >= 0) {
+                node_step<COUNT>(S, stack, nBox);
+                if (EARLY && __popc(__activemask()) < minActive) break;
+            }
+            if (ref >= 0 || ref == PTB_REF_DONE || held != 0) break;
+            held = ref;
+            pop(stack);
+        }
+        if (held != 0) {
+            int first, count;
+            leaf_decode(held, first, count);
+            for (int i = 0; i < count; ++i) intersect_tri<COUNT>(S.tri, first + i, o, d, h, nTri);
+        }
+        if (ref < 0 && ref != PTB_REF_DONE) leaf<COUNT>(S, stack, nTri);
+        return ref != PTB_REF_DONE;
+    }
+#else
     template <bool COUNT, bool EARLY = false, class ST>
     __device__ __forceinline__ bool round(const SceneDev &S, const ST &stack, uint32_t &nTri, uint32_t &nBox, int minActive = 0) {
         while (ref >= 0) {
@@ -350,6 +378,7 @@ struct BvhWalk {
         if ((!EARLY || ref < 0) && ref != PTB_REF_DONE) leaf<COUNT>(S, stack, nTri);
         return ref != PTB_REF_DONE;
     }
+#endif
 };
 
 // ---- 4-wide BVH ------------------------------------------------------------------------------------------------------
@@ -730,6 +759,9 @@ struct GridWalk {
         if (e.x == e.y) sp--;
         else stack.put(sp - 1, e);
     }
+    // (Measured and rejected, profiles/r2_ab5_seek_cell_spec.txt: splitting the visit into "seek the next grid whose box is hit" and
+    // "cell lookup for the lanes that found one" — the cell lookup runs at 4.5 lanes because ~60 % of the popped grids fail their
+    // box test — made the path 15 % SLOWER: the extra divergent loop and the two header float4 carried across it cost more.)
     template <bool COUNT, class ST>
     __device__ __forceinline__ void visit(const SceneDev &S, const ST &stack, uint32_t &nAS) {
         const float4 *hd = S.grid_hdr + 4 * (size_t)ref;

@@ -12,7 +12,7 @@ BVH, 1920x1080, 256 spp, primary + 8 bounces (max_depth 9) — the frame of BASE
 reference's own --testing protocol (src/main.cpp:101).  --workload cornell = configs[1] (Cornell box, BVH, 1024x1024,
 64 spp, 4 bounces: the round-1 default); --workload lucy = the Lucy frame at 16 spp (profiling runs).
 A "step" is one full frame: initTracer (ptb_reset) + trace (ptb_render).  With N > 1 the same frame is sharded over
-the ranks (strong scaling: total work fixed; tiles while every GPU keeps >= 400k pixels, else sample ranges) and the
+the ranks (strong scaling: total work fixed; tiles while every GPU keeps >= 600k pixels, else sample ranges) and the
 radiance is sum-reduced to rank 0 over NCCL inside the timed region.  Outside the timed region the line also gets
 `parity`: primary-ray hit ids / hit distances of this very process against the golden written by the unmodified reference
 (tests/golden/lucy_standin_ref_1080p.npz), and for a tile-sharded run the bitwise comparison of the reduced frame with a
@@ -65,7 +65,7 @@ WORKLOADS = {
 def workload_config(args, wl, world, shard, triangles):
     """`config` of the JSON line: the same keys and values in both arms (ours / reference)."""
     structure = {"bvh": "BVH" + (" (ours: BVH2 built on the GPU, Morton radix tree)" if args.builder == "gpu" else ""),
-                 "subgrid": "Subgrid / 2Plane hierarchy gs 8 os 8 m 50", "subbeams": "Subbeams gs 6 m 50 depth 1"}[args.structure]
+                 "subgrid": "Subgrid / 2Plane hierarchy gs 8 os 8 m 50", "subbeams": "Subbeams gs 6 m 50 depth guard 2"}[args.structure]
     if world == 1:
         par = "1 GPU"
     elif shard == "tiles":
@@ -271,7 +271,7 @@ def run_ours(args):
         pt.build_subbeams(6, 50, max_depth=1)
         mode = 3
     build_s = time.perf_counter() - t0
-    # Sharding: tiles (bit-identical to the 1-GPU frame) while every GPU keeps >= 400k pixels in flight; below
+    # Sharding: tiles (bit-identical to the 1-GPU frame) while every GPU keeps >= 600k pixels in flight; below
     # that the serial samples of a pixel starve the lanes and the frame is sharded by sample ranges instead
     # (every rank renders all pixels, spp/N samples from its own seeds; statistical parity)
     shard = choose_shard(args, wl, world)
@@ -517,7 +517,7 @@ def main():
     ap.add_argument("--cpu-spp", type=int, default=0, help="spp of the bounded cpu_baseline sample (0: 8 for Cornell, 4 for the Lucy frame)")
     ap.add_argument("--ref-spp", type=int, default=4, help="spp per step of the --impl reference arm")
     ap.add_argument("--structure", default="bvh", choices=["bvh", "subgrid", "subbeams"],
-                    help="acceleration structure (subgrid: gs 8 / os 8 / m 50 like the published runs; subbeams: gs 6 / m 50 / depth 1)")
+                    help="acceleration structure (subgrid: gs 8 / os 8 / m 50 like the published runs; subbeams: gs 6 / m 50 / depth guard 2)")
     ap.add_argument("--builder", default="host", choices=["host", "gpu"],
                     help="BVH construction: host binned SAH (default, the better tree) or ptb_build_bvh_gpu (Morton radix tree built in HBM)")
     ap.add_argument("--shard", default="auto", choices=["auto", "tiles", "samples"], help="multi-GPU partition of the frame")
