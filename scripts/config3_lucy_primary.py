@@ -29,8 +29,8 @@ if gold is not None:
         out["reference_cpu"].update(two_plane_ms=float(gold["ref_two_plane_ms"]), two_plane_build_s=float(gold["ref_two_plane_build"]) / 1e3,
                                     two_plane_bytes=int(gold["ref_two_plane_bytes"]),
                                     two_plane_mrays_s=W * H / float(gold["ref_two_plane_ms"]) / 1e3)
-builds = [("BVH", 1, lambda: pt.build_bvh()), ("Subgrid gs8 os8 m50", 2, lambda: pt.build_subgrid(8, 8, 50)),
-          ("Subbeams gs6 m50 depth1", 3, lambda: pt.build_subbeams(6, 50, max_depth=1))]
+builds = [("BVH", 1, lambda: pt.build_bvh()), ("Subgrid gs8 os8 m50", 2, lambda: pt.build_subgrid(8, 8, 50, gpu=True)),
+          ("Subbeams gs6 m50 depth2", 3, lambda: pt.build_subbeams(6, 50, max_depth=2, gpu=True))]
 t_ref = None
 for name, mode, build in builds:
     t0 = time.perf_counter()

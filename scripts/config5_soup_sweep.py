@@ -2,7 +2,12 @@
 """BASELINE config 5: triangle-soup sweep, incoherent rays, traversal Mrays/s and algorithmic GB/s per
 structure.  usage: config5_soup_sweep.py [max_log10_n=7] [log2_rays=24] [min_log10_n=4].  Writes gpurun_out/config5.json.
 Up to 10^7 triangles the BVH is built twice — host binned SAH and on the GPU (ptb_build_bvh_gpu) — and both trees
-must return identical hits; 10^8 is built on the GPU only and cross-checked against brute force on a ray subset."""
+must return identical hits; 10^8 is built on the GPU only and cross-checked against brute force on a ray subset.
+Round 2: the Subgrid and Subbeam rows use the GPU builders (ptb_build_subgrid_gpu / ptb_build_subbeams_gpu), which moves their
+limits from 10^5 / 10^4 to CONFIG5_GRID_MAX_LOG (default 7) / CONFIG5_BEAM_MAX_LOG (default 5) triangles; a structure that does not
+fit or fails to build is recorded as such and the sweep goes on.  CONFIG5_REPS=1 (one timed launch per structure) is for the
+ncu pass that collects dram / L2 bytes per launch:
+  ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_sectors.sum -k regex:k_trace --csv ..."""
 import json
 import os
 import sys
@@ -32,14 +37,19 @@ for lg in range(min_log, max_log + 1):
     sc.upload_scene(pt, scene)
     del scene
     structs = [("BVH", 1, lambda: pt.build_bvh())] if lg <= 7 else []
-    if lg <= 5:
-        structs.append(("Subgrid gs6 os4 m40", 2, lambda: pt.build_subgrid(6, 4, 40)))
-    if lg <= 4:
-        structs.append(("Subbeams gs4 m40 depth2", 3, lambda: pt.build_subbeams(4, 40, max_depth=2)))
+    if lg <= int(os.environ.get("CONFIG5_GRID_MAX_LOG", "7")):
+        structs.append(("Subgrid gs6 os4 m40", 2, lambda: pt.build_subgrid(6, 4, 40, gpu=True)))
+    if lg <= int(os.environ.get("CONFIG5_BEAM_MAX_LOG", "5")):
+        structs.append(("Subbeams gs4 m40 depth2", 3, lambda: pt.build_subbeams(4, 40, max_depth=2, gpu=True)))
     structs.append(("BVH built on the GPU", 1, lambda: pt.build_bvh(gpu=True)))  # last: it replaces the tree the Subgrid derives from
     for name, mode, build in structs:
         t0 = time.perf_counter()
-        build_ms = build()
+        try:
+            build_ms = build()
+        except ptb_b200.PtbError as e:
+            res.append({"n": n, "structure": name, "build_failed": str(e)[:200]})
+            print(res[-1], flush=True)
+            continue
         bs = time.perf_counter() - t0
         pt.set_params(width=64, height=64, mode=mode, count_tests=1)
         sub = min(nrays, 1 << 20)
@@ -48,9 +58,10 @@ for lg in range(min_log, max_log + 1):
         boxes, tris = c["as_tests"] / sub, c["tri_tests"] / sub
         pt.set_params(count_tests=0)
         ms = []
-        for _ in range(4):
+        reps = int(os.environ.get("CONFIG5_REPS", "4"))
+        for _ in range(reps):
             ms.append(pt.trace_rays_device(rays.data_ptr(), nrays, mode, t_out.data_ptr(), tri_out.data_ptr()))
-        best = min(ms[1:])
+        best = min(ms[1:]) if reps > 1 else ms[0]
         bpr = 24 + 8 + 32 * boxes + 36 * tris
         rec = {"n": n, "structure": name, "build_s": bs, "build_ms_reported": build_ms, "bvh_depth": pt.bvh_depth() if mode == 1 else None, "bytes": pt.structure_bytes(mode), "ms": best, "mrays_s": nrays / best / 1e3,
                "as_tests_per_ray": boxes, "tri_tests_per_ray": tris, "algorithmic_bytes_per_ray": bpr,
@@ -71,4 +82,4 @@ for lg in range(min_log, max_log + 1):
         print(rec, flush=True)
     pt.close()
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-json.dump(res, open(os.path.join(ROOT, "gpurun_out", "config5.json"), "w"), indent=1)
+json.dump(res, open(os.path.join(ROOT, "gpurun_out", os.environ.get("CONFIG5_OUT", "config5.json")), "w"), indent=1)
