@@ -515,7 +515,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="lucy256", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-spp", type=int, default=0, help="spp of the bounded cpu_baseline sample (0: 8 for Cornell, 4 for the Lucy frame)")
-    ap.add_argument("--ref-spp", type=int, default=4, help="spp per step of the --impl reference arm")
+    ap.add_argument("--ref-spp", type=int, default=0, help="spp per step of the --impl reference arm (0: 4 for Cornell, 2 for the Lucy frame = 3 s per step)")
     ap.add_argument("--structure", default="bvh", choices=["bvh", "subgrid", "subbeams"],
                     help="acceleration structure (subgrid: gs 8 / os 8 / m 50 like the published runs; subbeams: gs 6 / m 50 / depth guard 2)")
     ap.add_argument("--builder", default="host", choices=["host", "gpu"],
@@ -532,6 +532,8 @@ def main():
         rw, rh = (int(v) for v in args.res.lower().split("x"))
         WORKLOADS[args.workload] = dict(WORKLOADS[args.workload], W=rw, H=rh,
                                         name=WORKLOADS[args.workload]["name"] + f" [frame overridden to {rw}x{rh}]")
+    if args.ref_spp <= 0:
+        args.ref_spp = 4 if args.workload == "cornell" else 2
     if args.cpu_spp <= 0:
         args.cpu_spp = 8 if args.workload == "cornell" else 4
     if args.warmup < 3 and args.impl == "ours":
