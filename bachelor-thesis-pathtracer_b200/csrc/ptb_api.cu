@@ -1683,6 +1683,8 @@ static int ptb_build_subgrid_impl(ptb_ctx *c, uint32_t gs, uint32_t os, uint32_t
     GUARD(c);
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (the Subgrid hierarchy derives from the BVH)");
     if (gs < 1 || gs > 64 || os < 1 || os > 64) return fail(c, PTB_ERR_INVALID, "grid sizes must be 1..64");
+    // one grid level per 4 BVH levels below the root grid: the walk's slice stack must hold the deepest chain
+    if (1 + (c->bvh.max_depth + 3) / 4 > PTB_GDEPTH) return fail(c, PTB_ERR_INVALID, "BVH too deep for the Subgrid walk's stack (PTB_GDEPTH)");
     if (int r = mirror_gpu_bvh(c)) return r;
     std::vector<float> leaf;
     leaf_positions(c, leaf);
@@ -1714,6 +1716,8 @@ static int ptb_build_subgrid_gpu_impl(ptb_ctx *c, uint32_t gs, uint32_t os, uint
     SETTLE(c);
     if (!c->bvhBuilt) return fail(c, PTB_ERR_NOT_BUILT, "ptb_build_bvh first (the Subgrid hierarchy derives from the BVH)");
     if (gs < 1 || gs > 64 || os < 1 || os > 64) return fail(c, PTB_ERR_INVALID, "grid sizes must be 1..64");
+    // one grid level per 4 BVH levels below the root grid: the walk's slice stack must hold the deepest chain
+    if (1 + (c->bvh.max_depth + 3) / 4 > PTB_GDEPTH) return fail(c, PTB_ERR_INVALID, "BVH too deep for the Subgrid walk's stack (PTB_GDEPTH)");
     if (int r = mirror_gpu_bvh(c)) return r;
     const auto t0 = std::chrono::steady_clock::now();
     SubgridTopo T;

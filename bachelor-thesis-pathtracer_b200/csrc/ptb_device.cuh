@@ -611,61 +611,13 @@ __device__ __forceinline__ int dominant_axis(f3 d) {
 // ---- Subgrid ("2Plane"/Hybrid) closest hit: stands in for intersectGrid (lightFieldGrid.cpp:71-147)
 // Grid header (4 float4): (aabb.min, size | hasTris<<31) (aabb.max, lutBase) (min, -) (inv_delta, -)
 // grid.max[axis] is aabb.max[axis] + 0.1f (adjustGridSize, lightFieldGrid.cpp:176-178).
-template <bool COUNT>
-__device__ __forceinline__ void subgrid_closest(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
-    const f3 inv = rcp3(d);
-    const int axis = dominant_axis(d);
-    const int right = axis == 0 ? 1 : 0, up = axis == 2 ? 1 : 2; // lightFieldGrid.cpp:26-35
-    const float oa = comp(o, axis), ia = comp(inv, axis), da = comp(d, axis);
-    const float orr = comp(o, right), dr = comp(d, right), ou = comp(o, up), du = comp(d, up);
-    uint32_t stack[PTB_GSTACK];
-    int sp = 0;
-    stack[sp++] = (uint32_t)axis;
-    while (sp > 0) {
-        const uint32_t g = stack[--sp];
-        const float4 *hd = S.grid_hdr + 4 * (size_t)g;
-        const float4 h0 = __ldg(hd), h1 = __ldg(hd + 1);
-        if (COUNT) nAS++;
-        float tn;
-        if (!slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)) continue;
-        if (COUNT) nAS++;
-        const float4 h2 = __ldg(hd + 2), h3 = __ldg(hd + 3);
-        const f3 gmin = mk3(h2.x, h2.y, h2.z), idl = mk3(h3.x, h3.y, h3.z);
-        const float gmaxA = comp(mk3(h1.x, h1.y, h1.z), axis) + 0.1f;
-        const float d1 = (comp(gmin, axis) - oa) * ia;
-        const float d2 = (gmaxA - oa) * ia;
-        // in = (origin + d1*dir - min) * inv_delta, out likewise (lightFieldGrid.cpp:116-117)
-        const float inR = ((orr + d1 * dr) - comp(gmin, right)) * comp(idl, right);
-        const float inU = ((ou + d1 * du) - comp(gmin, up)) * comp(idl, up);
-        const float outR = ((orr + d2 * dr) - comp(gmin, right)) * comp(idl, right);
-        const float outU = ((ou + d2 * du) - comp(gmin, up)) * comp(idl, up);
-        const uint32_t sz = __float_as_uint(h0.w) & 0x7fffffffu;
-        const bool hasTris = (__float_as_uint(h0.w) >> 31) != 0u;
-        const float fs = (float)sz;
-        const int iu = (int)(inR * fs), iv = (int)(inU * fs), is = (int)(outR * fs), it = (int)(outU * fs);
-        // the reference indexes without a bounds check (A.12); outside the planes means no cell
-        if ((unsigned)iu >= sz || (unsigned)iv >= sz || (unsigned)is >= sz || (unsigned)it >= sz) continue;
-        const uint32_t cell = ((((uint32_t)iu * sz + (uint32_t)iv) * sz + (uint32_t)is) * sz + (uint32_t)it);
-        const uint2 se = __ldg(&S.grid_lut[(size_t)__float_as_uint(h1.w) + cell]);
-        if (hasTris) {
-            for (uint32_t i = se.x; i < se.y; ++i) intersect_tri<COUNT>(S.tri, (int)__ldg(&S.grid_idx[i]), o, d, h, nTri);
-        } else if (da < 0.0f) {
-            for (uint32_t i = se.x; i < se.y && sp < PTB_GSTACK; ++i) stack[sp++] = __ldg(&S.grid_idx[i]);
-        } else {
-            for (uint32_t i = se.y; i > se.x && sp < PTB_GSTACK; --i) stack[sp++] = __ldg(&S.grid_idx[i - 1]);
-        }
-    }
-}
-
 // The reference keeps a LIFO of grid ids and pushes every child of the cell it lands in (lightFieldGrid.cpp:127-145: ascending
 // for a negative dominant direction, descending otherwise, so that pops come back-to-front resp. front-to-back).  A cell's
 // children are one contiguous slice of the index pool, so the same pop order falls out of a LIFO of SLICES consumed from one
 // end: one 8-byte push per visited inner grid instead of one load + store per child (14 % of the issued instructions of the
 // round-1 kernel at 3 active lanes), and a stack as deep as the grid hierarchy — at most 1 + ceil(BVH depth / 4) <= 17 slices,
-// a bound the builders guarantee (PTB_STACK) — instead of 160 ids that could overflow silently.
-#ifndef PTB_GRID_SLICES
-#define PTB_GRID_SLICES 1
-#endif
+// a bound the builders check (ptb_build_subgrid[_gpu]) and ptb_upload_subgrid validates — instead of the 160 ids of round 1's
+// walk, which dropped pushes silently when full.
 #define PTB_GDEPTH 20
 template <bool COUNT>
 __device__ __forceinline__ void subgrid_closest_slices(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
@@ -883,8 +835,7 @@ template <int MODE, bool COUNT>
 __device__ __forceinline__ void closest_hit(const SceneDev &S, f3 o, f3 d, Hit &h, uint32_t &nTri, uint32_t &nAS) {
     if (MODE == 5) bvh4_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 1) bvh_closest<COUNT>(S, o, d, h, nTri, nAS);
-    else if (MODE == 2 && PTB_GRID_SLICES) subgrid_closest_slices<COUNT>(S, o, d, h, nTri, nAS);
-    else if (MODE == 2) subgrid_closest<COUNT>(S, o, d, h, nTri, nAS);
+    else if (MODE == 2) subgrid_closest_slices<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 3) subbeam_closest<COUNT>(S, o, d, h, nTri, nAS);
     else if (MODE == 4) refbvh_closest<COUNT>(S, o, d, h, nTri, nAS); // BVH mode over the reference's own tree
     else brute_closest<COUNT>(S, o, d, h, nTri);
