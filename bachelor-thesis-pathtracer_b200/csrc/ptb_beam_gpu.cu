@@ -146,10 +146,12 @@ cudaError_t subbeams_build_gpu(const float *d_vtx, const uint32_t *d_id_of_tri, 
     const char *what = "";
     if (e == cudaSuccess) {
         DeviceExec x(stream);
-        // PTB_BEAM_DEEP_CHUNK=k (experiments): below the roots, too, one thread per (beam, k entries of the parent's list)
-        // instead of one per beam; same pools (tests/native/subbeam_levels_check.cpp runs both), not the default until measured
+        // Below the roots, too, one thread per (beam, k entries of the parent's list) instead of one per beam: the same pools
+        // (tests/native/subbeam_levels_check.cpp runs both), and on the Lucy stand-in gs 6 / m 50 the build takes 1.40 s instead of
+        // 4.09 s at depth guard 2 and 0.50 s instead of 2.06 s at depth 1 with k = 64 / 256 (profiles/r2_subbeam_deep_chunk.jsonl).
+        // PTB_BEAM_DEEP_CHUNK=k overrides, 0 = one thread per beam.
         const char *deep = getenv("PTB_BEAM_DEEP_CHUNK");
-        const uint32_t deepChunk = deep && atoi(deep) > 0 ? (uint32_t)atoi(deep) : 0u;
+        const uint32_t deepChunk = deep ? (uint32_t)std::max(0, atoi(deep)) : 64u;
         what = build_beam_levels(x, G, (uint32_t)n, d_vtx, d_id_of_tri, m, max_depth, R, deepChunk);
         e = x.status;
         if (e == cudaSuccess && *what) e = cudaErrorInvalidValue; // a size limit of the driver, nothing wrong with the device

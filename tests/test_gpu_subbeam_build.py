@@ -74,10 +74,10 @@ def test_soup_empty_scene_and_device_tree(ptb, cornel_ptbs):
     pt.close()
 
 
-@pytest.mark.xfail(strict=False, reason="opt-in path (PTB_BEAM_DEEP_CHUNK): CPU-checked, written after the round's GPU time was spent")
-def test_deep_chunk_variant_in_its_own_process(cornel_ptbs):
-    """The (beam, chunk of the parent's list) workers below the roots must give the host builder's pools too.  Runs in a
-    child process so that nothing it does can touch this process's CUDA context."""
+def test_one_thread_per_beam_variant_in_its_own_process(cornel_ptbs):
+    """The chunked workers below the roots (one thread per beam and 64 entries of the parent's list) are the default since
+    round 2 — every other test here builds with them; PTB_BEAM_DEEP_CHUNK=0 selects the older one-thread-per-beam steps, which
+    must give the host builder's pools too.  Runs in a child process: the knob is read from the environment."""
     import os
     import subprocess
     import sys
@@ -88,7 +88,7 @@ def test_deep_chunk_variant_in_its_own_process(cornel_ptbs):
         "pt.build_subbeams(4, 8, max_depth=3, gpu=False); h = pt.structure_digest(3)\n"
         "wall, dev = pt.build_subbeams(4, 8, max_depth=3, gpu=True); g = pt.structure_digest(3)\n"
         "print('DEEP', h == g and h != 0, wall, dev)\n" % (root, cornel_ptbs))
-    env = dict(os.environ, PTB_BEAM_DEEP_CHUNK="16")
+    env = dict(os.environ, PTB_BEAM_DEEP_CHUNK="0")
     out = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     print(out.stdout[-2000:])
     assert out.returncode == 0 and "DEEP True" in out.stdout
