@@ -627,6 +627,7 @@ __device__ __forceinline__ void subgrid_closest_slices(const SceneDev &S, f3 o, 
     const float oa = comp(o, axis), ia = comp(inv, axis), da = comp(d, axis);
     const float orr = comp(o, right), dr = comp(d, right), ou = comp(o, up), du = comp(d, up);
     const bool fromEnd = da < 0.0f; // ascending pushes pop from the end of the slice
+    const bool fast = finite3(inv);  // FMNMX slab test: same boolean as the select form for a finite inv_dir (see slab_fast)
     uint2 stack[PTB_GDEPTH];
     int sp = 0;
     uint32_t g = (uint32_t)axis; // grids 0..2 are the roots per dominant axis
@@ -635,7 +636,8 @@ __device__ __forceinline__ void subgrid_closest_slices(const SceneDev &S, f3 o, 
         const float4 h0 = __ldg(hd), h1 = __ldg(hd + 1);
         if (COUNT) nAS++;
         float tn;
-        if (slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)) {
+        if (fast ? slab_fast(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)
+                 : slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)) {
             if (COUNT) nAS++;
             const float4 h2 = __ldg(hd + 2), h3 = __ldg(hd + 3);
             const f3 gmin = mk3(h2.x, h2.y, h2.z), idl = mk3(h3.x, h3.y, h3.z);
@@ -688,6 +690,7 @@ struct GridWalk {
     int sp;           // slices on the stack
     uint32_t ti, te;  // pending triangles of the current cell: grid_idx[ti .. te)
     int axis;
+    bool fast;        // inv_dir finite: the FMNMX slab test gives the same boolean as the select form (see slab_fast)
 
     __device__ __forceinline__ void begin(const SceneDev &S, f3 o_, f3 d_, const Hit &h0) {
         o = o_;
@@ -697,6 +700,7 @@ struct GridWalk {
         sp = 0;
         ti = te = 0u;
         axis = dominant_axis(d_);
+        fast = finite3(inv);
         ref = axis; // grids 0..2 are the roots per dominant axis
     }
     template <class ST>
@@ -720,7 +724,9 @@ struct GridWalk {
         const float4 h0 = __ldg(hd), h1 = __ldg(hd + 1);
         if (COUNT) nAS++;
         float tn;
-        if (!slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)) return;
+        if (!(fast ? slab_fast(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)
+                   : slab(mk3(h0.x, h0.y, h0.z), mk3(h1.x, h1.y, h1.z), o, inv, h.t, tn)))
+            return;
         if (COUNT) nAS++;
         const float4 h2 = __ldg(hd + 2), h3 = __ldg(hd + 3);
         const int right = axis == 0 ? 1 : 0, up = axis == 2 ? 1 : 2; // lightFieldGrid.cpp:26-35
