@@ -208,6 +208,38 @@ void build_bvh(const float *pos9, uint64_t n, int leaf_max, BvhResult &out) {
     const uint32_t used = B.next.load();
     B.nodes.resize(used);
     B.ranges.resize(2 * (size_t)used);
+    // Depth-first relayout.  Indices are handed out before a node's children are built, so a single thread numbers in pre-order
+    // already; but the top levels of a large scene build their subtrees concurrently (count > 200000) and those subtrees'
+    // allocations interleave node by node.  Renumbering in strict pre-order puts a node's first child in the next 64 bytes —
+    // the same 128-byte line every other time — for a walk that waits on its dependent node fetch (PTB_BVH_RELAYOUT=0: off).
+    const char *rl = getenv("PTB_BVH_RELAYOUT");
+    if (out.root >= 0 && used > 1 && !(rl && atoi(rl) == 0)) {
+        std::vector<int32_t> newIdx(used, -1), order;
+        order.reserve(used);
+        std::vector<int32_t> todo{out.root};
+        while (!todo.empty()) {
+            const int32_t i = todo.back();
+            todo.pop_back();
+            newIdx[i] = (int32_t)order.size();
+            order.push_back(i);
+            const BvhNode64 &nd = B.nodes[i];
+            if (nd.c1 >= 0) todo.push_back(nd.c1); // popped second: the right subtree follows the whole left one
+            if (nd.c0 >= 0) todo.push_back(nd.c0);
+        }
+        std::vector<BvhNode64> nn(order.size());
+        std::vector<BvhRange> rr(2 * order.size());
+        for (size_t k = 0; k < order.size(); ++k) {
+            BvhNode64 nd = B.nodes[order[k]];
+            if (nd.c0 >= 0) nd.c0 = newIdx[nd.c0];
+            if (nd.c1 >= 0) nd.c1 = newIdx[nd.c1];
+            nn[k] = nd;
+            rr[2 * k] = B.ranges[2 * (size_t)order[k]];
+            rr[2 * k + 1] = B.ranges[2 * (size_t)order[k] + 1];
+        }
+        out.root = 0;
+        B.nodes.swap(nn);
+        B.ranges.swap(rr);
+    }
     out.nodes.swap(B.nodes);
     out.ranges.swap(B.ranges);
     out.order.swap(B.idx);
