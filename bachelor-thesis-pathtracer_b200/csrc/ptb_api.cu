@@ -1225,8 +1225,14 @@ int render_mega(ptb_ctx *c, int add) {
     // no more paths in flight than owned pixels: a pixel's samples are serial, so pixels bound the parallelism
     const bool pool = MODE < 4 && c->useMega == 2, duo = MODE < 4 && c->useMega == 3; // the reference tree and the wide tree run in k_mega only
     const uint64_t perCta = pool ? 4ull * PTB_POOL_NP : (duo ? 2ull * kThreads : (uint64_t)kThreads); // paths a CTA keeps in flight
-    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * (pool ? c->poolCtas : (duo ? c->duoCtas : c->megaCtas)),
-                                                                   ((uint64_t)c->nSlots + perCta - 1) / perCta));
+    // Scarce pixels (fewer than two per lane of a full grid: small frames, 1/N of a frame per GPU): 8 resident CTAs per SM instead
+    // of 12 and 16-sample items — profiles/r2_tile_share_sweep_bvh.jsonl, one GPU's share of an 8-GPU 1080p frame: 105.7 ms against
+    // 114.1 ms (the rest of the gap to the ideal 75 ms is the spread of per-pixel cost: a pixel's samples are serial, and with ~1
+    // pixel per lane the frame ends when its most expensive pixels do)
+    int ctasPerSm = pool ? c->poolCtas : (duo ? c->duoCtas : c->megaCtas);
+    const bool scarce = !pool && !duo && (uint64_t)c->nSlots < 2ull * (uint64_t)c->sms * ctasPerSm * perCta && !getenv("PTB_MEGA_CTAS");
+    if (scarce) ctasPerSm = std::min(ctasPerSm, 8);
+    const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * ctasPerSm, ((uint64_t)c->nSlots + perCta - 1) / perCta));
     const uint64_t lanes = (uint64_t)grid * perCta;
     MegaArgs M{};
     // Work items are (pixel, chunk of samples); a lane whose pixel's previous chunk is still in flight parks
@@ -1234,7 +1240,7 @@ int render_mega(ptb_ctx *c, int add) {
     // one path of all lanes; when pixels are scarce (small frames, 1/N of a frame per GPU) longer chunks make
     // hand-offs rare at the price of a tail of `chunk` paths.  Non-uniform resumed state: one item per pixel.
     const uint64_t ratio = (uint64_t)c->nSlots / lanes;
-    uint32_t chunk = ratio >= 2 ? 1u : 8u; // profiles/r1_sweep_mega_chunk.txt: 1-sample items keep neighbouring pixels in step (coherent primary rays)
+    uint32_t chunk = ratio >= 2 ? 1u : (scarce ? 16u : 8u); // profiles/r1_sweep_mega_chunk.txt: 1-sample items keep neighbouring pixels in step (coherent primary rays)
     if (c->megaChunk > 0) chunk = (uint32_t)c->megaChunk;
     chunk = std::min<uint32_t>(chunk, (uint32_t)add);
     const uint32_t nChunks = ((uint32_t)add + chunk - 1) / chunk;
