@@ -1229,7 +1229,7 @@ int render_mega(ptb_ctx *c, int add) {
     // of 12 and 16-sample items — profiles/r2_tile_share_sweep_bvh.jsonl, one GPU's share of an 8-GPU 1080p frame: 105.7 ms against
     // 114.1 ms (the rest of the gap to the ideal 75 ms is the spread of per-pixel cost: a pixel's samples are serial, and with ~1
     // pixel per lane the frame ends when its most expensive pixels do)
-    int ctasPerSm = pool ? c->poolCtas : (duo ? c->duoCtas : c->megaCtas);
+    int ctasPerSm = pool ? c->poolCtas : (duo ? c->duoCtas : std::min(c->megaCtas, PTB_MEGA_BLOCKS_FOR(MODE))); // never more than stay resident
     const bool scarce = !pool && !duo && (uint64_t)c->nSlots < 2ull * (uint64_t)c->sms * ctasPerSm * perCta && !getenv("PTB_MEGA_CTAS");
     if (scarce) ctasPerSm = std::min(ctasPerSm, 8);
     const int grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->sms * ctasPerSm, ((uint64_t)c->nSlots + perCta - 1) / perCta));

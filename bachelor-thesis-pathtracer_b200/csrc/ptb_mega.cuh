@@ -30,6 +30,12 @@
 #ifndef PTB_MEGA_MINBLOCKS
 #define PTB_MEGA_MINBLOCKS 12 /* 40 registers/thread: 48 warps/SM beat fewer, fatter warps despite the spills (profiles/r1_sweep_mega.txt) */
 #endif
+// Per mode since round 2 (profiles/r2_ab9_regcap.txt, final tree and thresholds): the BVH walks gain 3 % on the Lucy stand-in with
+// 10 resident CTAs per SM (48 registers, a third fewer spills) and nothing on Cornell; the Subgrid walk loses 3 % with them.
+#ifndef PTB_MEGA_MINBLOCKS_BVH
+#define PTB_MEGA_MINBLOCKS_BVH 10
+#endif
+#define PTB_MEGA_BLOCKS_FOR(M) (((M) == 1 || (M) == 5) ? PTB_MEGA_MINBLOCKS_BVH : PTB_MEGA_MINBLOCKS)
 
 namespace ptb {
 
@@ -77,7 +83,7 @@ struct MegaArgs {
 // own --testing protocol renders with NEE off, main.cpp:101).
 // TEX = true compiles the texture branches of shade_hit in (scenes that bind textures; ptb_upload_textures).
 template <int MODE, bool COUNT, bool NEE, bool EARLY = false, bool TEX = false>
-__global__ void __launch_bounds__(128, PTB_MEGA_MINBLOCKS) k_mega(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, MegaArgs M) {
+__global__ void __launch_bounds__(128, PTB_MEGA_BLOCKS_FOR(MODE)) k_mega(ParamsDev P, SceneDev S, AttrDev A, FrameDev F, MegaArgs M) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     int phase = LANE_IDLE;
