@@ -221,7 +221,7 @@ uint64_t ptb_trace_rays_static_max(void); /* PTB_STATIC_MAX_RAYS of the loaded l
 int ptb_read_image(ptb_ctx *ctx, float *rgba);                       /* tracerGetPixel for every pixel, row-major y*W+x, alpha 1 */
 int ptb_read_state(ptb_ctx *ctx, int32_t *samples, uint32_t *rng);   /* samples[][] / randomStates[][] (tracer.cpp:25-26), y*W+x */
 int ptb_write_state(ptb_ctx *ctx, const float *rgba, const int32_t *samples, const uint32_t *rng); /* resume a dumped render */
-int ptb_read_rgba8(ptb_ctx *ctx, uint8_t *rgba8, int tone_mapping);  /* display transform, window.cpp:507-531 (bytes R,G,B,255) */
+int ptb_read_rgba8(ptb_ctx *ctx, uint8_t *rgba8, int tone_mapping);  /* display transform, window.cpp:507-531 (bytes R,G,B,255), byte-exact: see ptb_tone_thresholds */
 /* The 255 steps of that transform (window.cpp:513-522 per channel, tone mapping on): out[b] = the smallest v = c/(1+c) in [0,1]
  * whose byte is >= b, found with the host's libm (the reference's powf); out[0] = 0.  What the kernel searches; no context needed. */
 int ptb_tone_thresholds(float out[256]);
